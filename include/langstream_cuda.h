@@ -1,0 +1,231 @@
+/*
+ * langstream_cuda.h — C ABI of the langstream-cuda native module (B200 / sm_100a).
+ *
+ * This is the drop-in boundary for LangStream's one data-parallel hot path:
+ *   - the local-model `compute-ai-embeddings` agent (a BERT-family sentence encoder), and
+ *   - the brute-force cosine top-k behind `query-vector-db` (+ the `vector-db-sink` write side).
+ *
+ * The reference has no native code: its Java calls DJL (libtorch CPU through JNI) and HerdDB
+ * (JDBC).  Each entry point below cites the reference interface whose bottom layer it replaces
+ * (paths relative to the reference tree; AI/ = langstream-agents/langstream-ai-agents/src/main/java,
+ * VEC/ = langstream-agents/langstream-vector-agents/src/main/java/ai/langstream/agents/vector,
+ * API/ = langstream-api/src/main/java/ai/langstream/api).
+ *
+ * Conventions
+ *   - plain C: opaque handles, pointers and sizes only; no exceptions cross the boundary;
+ *   - every call returns 0 on success and a negative LSC_E_* code on failure; the message is
+ *     available from lsc_last_error() (thread-local, valid until the next failing call on the
+ *     same thread);
+ *   - the caller owns every input and output buffer; nothing returned aliases native memory;
+ *   - one handle drives one GPU; use one handle (and one process or thread) per GPU;
+ *   - calls on the same handle are serialised internally (thread-safe, not concurrent);
+ *   - there is no CPU fallback: without a usable sm_100 device every create call fails.
+ */
+#ifndef LANGSTREAM_CUDA_H
+#define LANGSTREAM_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LSC_OK 0
+#define LSC_E_INVALID (-1)    /* bad argument (IllegalArgumentException on the Java side) */
+#define LSC_E_CUDA (-2)       /* CUDA runtime / driver error */
+#define LSC_E_NOMEM (-3)      /* host or device allocation failed */
+#define LSC_E_UNSUPPORTED (-4)/* shape outside what the kernels support */
+#define LSC_E_IO (-5)         /* save / load failed */
+#define LSC_E_TOO_LONG (-6)   /* a sequence exceeds max_position (reference: TranslateException
+                                 "Illegal input, maybe the number of tokens is too high",
+                                 AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:197-203) */
+
+typedef struct lsc_encoder lsc_encoder;
+typedef struct lsc_index lsc_index;
+
+/* ---- library ---------------------------------------------------------------------------- */
+
+/* Version string of the native module, e.g. "langstream-cuda 0.1 sm_100a". */
+const char* lsc_version(void);
+/* Last error message of the calling thread ("" if none). */
+const char* lsc_last_error(void);
+/* Number of CUDA devices visible; <0 on error. */
+int lsc_device_count(void);
+
+/* ---- encoder: replaces the DJL/libtorch forward pass ------------------------------------- */
+
+/*
+ * Architecture of the BERT-family encoder (post-LN, absolute positions, exact-erf GELU,
+ * LayerNorm eps as given).  MiniLM-L6: layers 6, hidden 384, heads 12, ffn 1536;
+ * BGE-base: 12 / 768 / 12 / 3072.  hidden / heads must be 32 or 64.
+ */
+typedef struct lsc_encoder_config {
+    int32_t layers;
+    int32_t hidden;
+    int32_t heads;
+    int32_t ffn;
+    int32_t vocab;
+    int32_t max_position;
+    int32_t type_vocab;
+    float ln_eps;
+    int32_t gemm_impl; /* 0 = tcgen05/TMEM/TMA (product path); 1 = CUDA-core validation GEMM
+                          (debug only: used by the tests to cross-check the tensor-core path) */
+    int32_t reserved[7];
+} lsc_encoder_config;
+
+/*
+ * Number of bytes of the fp32 weight blob lsc_encoder_create expects for `cfg`.
+ * Blob layout (all fp32, little endian, row-major, PyTorch shapes), in this order:
+ *   word_embeddings [vocab,hidden], position_embeddings [max_position,hidden],
+ *   token_type_embeddings [type_vocab,hidden], embeddings.LayerNorm weight[hidden], bias[hidden],
+ *   then per layer:
+ *     query.weight [hidden,hidden], query.bias, key.weight, key.bias, value.weight, value.bias,
+ *     attention.output.dense.weight [hidden,hidden], .bias, attention.output.LayerNorm weight, bias,
+ *     intermediate.dense.weight [ffn,hidden], .bias, output.dense.weight [hidden,ffn], .bias,
+ *     output.LayerNorm weight, bias.
+ * This is the state_dict of the HuggingFace BertModel that DJL traces and runs
+ * (AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:132-161).
+ */
+size_t lsc_encoder_weights_nbytes(const lsc_encoder_config* cfg);
+
+/*
+ * Load a model onto GPU `device`.
+ * Replaces: AbstractHuggingFaceEmbeddingService constructor → Criteria.loadModel()
+ * (AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:110-172).
+ */
+int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_t nbytes,
+                       int device, lsc_encoder** out);
+
+/*
+ * Embed n_seq token sequences given in packed (variable-length) form:
+ * token_ids holds cu_seqlens[n_seq] int32 ids, sequence i is token_ids[cu_seqlens[i] .. cu_seqlens[i+1]).
+ * Writes n_seq × hidden fp32, row i = L2-normalised masked mean of sequence i's last hidden
+ * states.  An empty sequence yields a zero row.  Host pointers; blocks until the result is in `out`.
+ * Replaces: the per-text loop `predictor.predict(in)` — tokenised input → BERT forward → mean-pool
+ * → L2-normalise → float[hidden]
+ * (AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:183-207);
+ * the caller widens to List<Double> as
+ * AI/com/datastax/oss/streaming/ai/embeddings/HuggingFaceEmbeddingService.java:52-63 does.
+ */
+int lsc_encoder_embed(lsc_encoder* enc, const int32_t* token_ids, const int32_t* cu_seqlens,
+                      int32_t n_seq, float* out);
+
+/*
+ * Same computation with DEVICE pointers, enqueued on `stream` (a cudaStream_t, may be NULL for
+ * the default stream); returns without synchronising.  `total_tokens` = cu_seqlens[n_seq] and
+ * `max_seqlen` = the longest sequence, both known to the host caller.
+ * Same reference function as lsc_encoder_embed; used when token ids already live in HBM.
+ */
+int lsc_encoder_embed_dev(lsc_encoder* enc, const int32_t* d_token_ids, const int32_t* d_cu_seqlens,
+                          int32_t n_seq, int32_t total_tokens, int32_t max_seqlen, float* d_out,
+                          void* stream);
+
+/* Hidden size of the loaded model (the embedding dimension). */
+int lsc_encoder_dim(const lsc_encoder* enc);
+/* Number of kernels this handle has launched since creation (bench accounting). */
+int64_t lsc_encoder_launch_count(const lsc_encoder* enc);
+/* Replaces: EmbeddingsService.close() (AI/com/datastax/oss/streaming/ai/embeddings/EmbeddingsService.java:34). */
+void lsc_encoder_destroy(lsc_encoder* enc);
+
+/* ---- vector index: replaces the HerdDB table + cosine ORDER BY scan ----------------------- */
+
+/*
+ * Create an empty index of `dim`-dimensional vectors on GPU `device` with room for `capacity`
+ * rows (grows on demand).  dim must be a multiple of 64 and <= 512.
+ * Replaces: JdbcDataSourceImpl.initialize / the `CREATE TABLE … FLOATA` asset
+ * (AI/ai/langstream/ai/agents/datasource/impl/JdbcDataSourceProvider.java:61-65,
+ *  examples/applications/docker-chatbot/crawler.yaml:33).
+ */
+int lsc_index_create(int32_t dim, int64_t capacity, int device, lsc_index** out);
+
+/*
+ * Insert or replace n rows (host fp32, n × dim).  Rows are L2-normalised in fp32 and stored as
+ * bf16; a zero vector stays zero and scores 0 against every query, as
+ * ReRankAgent.cosineSimilarity does (AI/ai/langstream/ai/agents/rerank/ReRankAgent.java:262-273).
+ * Replaces: JdbcVectorDatabaseWriter.upsert — UPDATE, INSERT when no row matched
+ * (VEC/jdbc/JdbcWriter.java:139-179).
+ */
+int lsc_index_upsert(lsc_index* idx, const int64_t* ids, const float* vecs, int32_t n);
+
+/* Device-pointer variant of upsert for rows already in HBM (ids stay on the host). */
+int lsc_index_upsert_dev(lsc_index* idx, const int64_t* ids, const float* d_vecs, int32_t n,
+                         void* stream);
+
+/*
+ * Remove rows by id; unknown ids are ignored.
+ * Replaces: the DELETE branch of JdbcVectorDatabaseWriter.upsert when record.value()==null
+ * (VEC/jdbc/JdbcWriter.java:139-179; contract at API/database/VectorDatabaseWriter.java:30-36).
+ */
+int lsc_index_delete(lsc_index* idx, const int64_t* ids, int32_t n);
+
+/* Number of live rows. */
+int64_t lsc_index_size(const lsc_index* idx);
+
+/*
+ * Brute-force cosine top-k: for each of B queries (host fp32, B × dim) write the k best rows,
+ * best first, as ids (B × k int64, -1 when fewer than k rows exist) and scores (B × k fp32 cosine).
+ * Order: score descending, ties by lower storage slot (= insertion order while nothing was deleted).
+ * Replaces: JdbcDataSourceImpl.fetchData running
+ * `SELECT … ORDER BY cosine_similarity(col, CAST(? AS FLOAT ARRAY)) DESC LIMIT k` on HerdDB
+ * (AI/ai/langstream/ai/agents/datasource/impl/JdbcDataSourceProvider.java:103-124;
+ *  SQL at examples/applications/docker-chatbot/chatbot.yaml:44).  1 <= k <= 128.
+ */
+int lsc_index_search(lsc_index* idx, const float* queries, int32_t B, int32_t k, int64_t* out_ids,
+                     float* out_scores);
+
+/*
+ * Device-pointer variant: queries, out_ids and out_scores are device pointers; enqueued on
+ * `stream`, no synchronisation.  Used by the sharded multi-GPU path, which all-gathers the per-shard
+ * (score,id) candidates and then calls lsc_topk_merge_dev.
+ */
+int lsc_index_search_dev(lsc_index* idx, const float* d_queries, int32_t B, int32_t k,
+                         int64_t* d_out_ids, float* d_out_scores, void* stream);
+
+/*
+ * Debug / verification only: exact fp32 dot products of EVERY stored row with every query, by a
+ * plain CUDA-core kernel (no tensor cores): d_scores[b * size + slot], slots in storage order,
+ * queries normalised and rounded to bf16 exactly as the search does.  The tests use it as the
+ * on-device checker at full size.
+ */
+int lsc_index_scores_naive_dev(lsc_index* idx, const float* d_queries, int32_t B, float* d_scores,
+                               void* stream);
+
+/*
+ * Merge `parts` candidate lists per query (device pointers, layout [parts][B][k], each list sorted
+ * best first, id -1 = empty) into one top-k per query ([B][k]).  This is the step after the NCCL
+ * all-gather in the sharded search; it has no counterpart in the single-node reference.
+ */
+int lsc_topk_merge_dev(const int64_t* d_ids, const float* d_scores, int32_t parts, int32_t B,
+                       int32_t k, int64_t* d_out_ids, float* d_out_scores, void* stream);
+
+/* Number of kernels this handle has launched since creation. */
+int64_t lsc_index_launch_count(const lsc_index* idx);
+
+/*
+ * Persist / restore the index (ids + bf16 rows) — the local stand-in for the external database's
+ * durability (the agent's persistent state directory, API/runner/code/AgentContext.java:64-66).
+ */
+int lsc_index_save(lsc_index* idx, const char* path);
+int lsc_index_load(const char* path, int device, lsc_index** out);
+
+/* Replaces: QueryStepDataSource.close() / VectorDatabaseWriter.close()
+ * (AI/com/datastax/oss/streaming/ai/datasource/QueryStepDataSource.java:36,
+ *  API/database/VectorDatabaseWriter.java:38). */
+void lsc_index_destroy(lsc_index* idx);
+
+/* ---- debug / verification hooks (not part of the product path) --------------------------- */
+
+/*
+ * C[M,N] (bf16) = epilogue(A[M,K] (bf16) · W[N,K]^T (bf16) + bias[N] (fp32)), device pointers.
+ * epilogue: 0 = bias, 1 = bias + exact-erf GELU, 2 = bias + residual[M,N] (bf16).
+ * impl: 0 = tcgen05 kernel, 1 = CUDA-core validation kernel.  Lets the tests check the GEMM alone.
+ */
+int lsc_debug_gemm_dev(const void* d_A, const void* d_W, const float* d_bias, const void* d_residual,
+                       void* d_C, int32_t M, int32_t N, int32_t K, int32_t epilogue, int32_t impl,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LANGSTREAM_CUDA_H */

@@ -1,0 +1,251 @@
+"""ctypes binding of include/langstream_cuda.h.
+
+The library is loaded from langstream_b200/_lib/ (built in-tree by `langstream_b200.build`).
+Nothing here computes anything: a missing library or missing GPU raises, it never falls back.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent / "_lib" / "liblangstream_cuda.so"
+
+LSC_OK = 0
+LSC_E_INVALID = -1
+LSC_E_CUDA = -2
+LSC_E_NOMEM = -3
+LSC_E_UNSUPPORTED = -4
+LSC_E_IO = -5
+LSC_E_TOO_LONG = -6
+
+
+class NativeError(RuntimeError):
+    """A C-ABI call returned a negative code; `.code` is the LSC_E_* value."""
+
+    def __init__(self, code: int, message: str):
+        super().__init__(f"langstream-cuda error {code}: {message}")
+        self.code = code
+        self.message = message
+
+
+class EncoderConfig(C.Structure):
+    _fields_ = [
+        ("layers", C.c_int32),
+        ("hidden", C.c_int32),
+        ("heads", C.c_int32),
+        ("ffn", C.c_int32),
+        ("vocab", C.c_int32),
+        ("max_position", C.c_int32),
+        ("type_vocab", C.c_int32),
+        ("ln_eps", C.c_float),
+        ("gemm_impl", C.c_int32),
+        ("reserved", C.c_int32 * 7),
+    ]
+
+
+_vp = C.c_void_p
+_i32 = C.c_int32
+_i64 = C.c_int64
+
+# name -> (restype, argtypes); mirrors include/langstream_cuda.h one to one.
+SIGNATURES = {
+    "lsc_version": (C.c_char_p, []),
+    "lsc_last_error": (C.c_char_p, []),
+    "lsc_device_count": (C.c_int, []),
+    "lsc_encoder_weights_nbytes": (C.c_size_t, [C.POINTER(EncoderConfig)]),
+    "lsc_encoder_create": (C.c_int, [C.POINTER(EncoderConfig), _vp, C.c_size_t, C.c_int, C.POINTER(_vp)]),
+    "lsc_encoder_embed": (C.c_int, [_vp, _vp, _vp, _i32, _vp]),
+    "lsc_encoder_embed_dev": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
+    "lsc_encoder_dim": (C.c_int, [_vp]),
+    "lsc_encoder_launch_count": (_i64, [_vp]),
+    "lsc_encoder_destroy": (None, [_vp]),
+    "lsc_index_create": (C.c_int, [_i32, _i64, C.c_int, C.POINTER(_vp)]),
+    "lsc_index_upsert": (C.c_int, [_vp, _vp, _vp, _i32]),
+    "lsc_index_upsert_dev": (C.c_int, [_vp, _vp, _vp, _i32, _vp]),
+    "lsc_index_delete": (C.c_int, [_vp, _vp, _i32]),
+    "lsc_index_size": (_i64, [_vp]),
+    "lsc_index_search": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _vp]),
+    "lsc_index_search_dev": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
+    "lsc_index_scores_naive_dev": (C.c_int, [_vp, _vp, _i32, _vp, _vp]),
+    "lsc_topk_merge_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "lsc_index_launch_count": (_i64, [_vp]),
+    "lsc_index_save": (C.c_int, [_vp, C.c_char_p]),
+    "lsc_index_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(_vp)]),
+    "lsc_index_destroy": (None, [_vp]),
+    "lsc_debug_gemm_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the native library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m langstream_b200.build` "
+                "(there is no CPU fallback for this path)"
+            )
+        handle = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def last_error() -> str:
+    return lib().lsc_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int) -> None:
+    if rc != LSC_OK:
+        raise NativeError(rc, last_error())
+
+
+# ---------------------------------------------------------------------------------------------
+# Handle wrappers (numpy for host buffers; raw device pointers + stream for the *_dev calls)
+# ---------------------------------------------------------------------------------------------
+import numpy as _np
+
+
+def _ptr(a) -> int:
+    """Address of a C-contiguous numpy array, or the data_ptr of a torch tensor, or an int."""
+    if a is None:
+        return 0
+    if isinstance(a, int):
+        return a
+    if isinstance(a, _np.ndarray):
+        if not a.flags["C_CONTIGUOUS"]:
+            raise ValueError("array must be C-contiguous")
+        return a.ctypes.data
+    return a.data_ptr()  # torch tensor
+
+
+class Encoder:
+    """One encoder replica on one GPU (lsc_encoder)."""
+
+    def __init__(self, spec, blob, device: int = 0, gemm_impl: int = 0):
+        L = lib()
+        cfg = EncoderConfig(spec.layers, spec.hidden, spec.heads, spec.ffn, spec.vocab, spec.max_position,
+                            spec.type_vocab, spec.ln_eps, gemm_impl)
+        blob = _np.ascontiguousarray(blob, _np.float32)
+        need = L.lsc_encoder_weights_nbytes(C.byref(cfg))
+        if need == 0:
+            raise NativeError(LSC_E_INVALID, last_error())
+        h = _vp()
+        check(L.lsc_encoder_create(C.byref(cfg), blob.ctypes.data, blob.nbytes, device, C.byref(h)))
+        self._h = h
+        self.spec = spec
+        self.device = device
+        self.dim = spec.hidden
+
+    def embed(self, token_ids, cu_seqlens, out=None):
+        """Host API: packed int32 token ids + cu_seqlens -> [n_seq, hidden] fp32 (numpy)."""
+        ids = _np.ascontiguousarray(token_ids, _np.int32)
+        cu = _np.ascontiguousarray(cu_seqlens, _np.int32)
+        n = int(cu.size) - 1
+        if out is None:
+            out = _np.empty((max(n, 0), self.dim), _np.float32)
+        check(lib().lsc_encoder_embed(self._h, _ptr(ids), _ptr(cu), n, _ptr(out)))
+        return out
+
+    def embed_dev(self, d_token_ids, d_cu_seqlens, n_seq, total_tokens, max_seqlen, d_out, stream=0):
+        check(lib().lsc_encoder_embed_dev(self._h, _ptr(d_token_ids), _ptr(d_cu_seqlens), n_seq, total_tokens,
+                                          max_seqlen, _ptr(d_out), stream))
+
+    @property
+    def launch_count(self) -> int:
+        return int(lib().lsc_encoder_launch_count(self._h))
+
+    def close(self):
+        if self._h:
+            lib().lsc_encoder_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Index:
+    """One vector-index shard on one GPU (lsc_index)."""
+
+    def __init__(self, dim: int, capacity: int = 0, device: int = 0, _handle=None):
+        if _handle is None:
+            h = _vp()
+            check(lib().lsc_index_create(dim, capacity, device, C.byref(h)))
+            _handle = h
+        self._h = _handle
+        self.dim = dim
+        self.device = device
+
+    @classmethod
+    def load(cls, path: str, device: int = 0, dim: int | None = None):
+        h = _vp()
+        check(lib().lsc_index_load(str(path).encode(), device, C.byref(h)))
+        ix = cls(dim or 0, device=device, _handle=h)
+        return ix
+
+    def save(self, path: str):
+        check(lib().lsc_index_save(self._h, str(path).encode()))
+
+    def __len__(self) -> int:
+        return int(lib().lsc_index_size(self._h))
+
+    def upsert(self, ids, vecs):
+        ids = _np.ascontiguousarray(ids, _np.int64)
+        vecs = _np.ascontiguousarray(vecs, _np.float32).reshape(ids.size, -1)
+        if vecs.shape[1] != self.dim:
+            raise ValueError(f"vectors have dimension {vecs.shape[1]}, index has {self.dim}")
+        check(lib().lsc_index_upsert(self._h, _ptr(ids), _ptr(vecs), int(ids.size)))
+
+    def upsert_dev(self, ids, d_vecs, n, stream=0):
+        ids = _np.ascontiguousarray(ids, _np.int64)
+        check(lib().lsc_index_upsert_dev(self._h, _ptr(ids), _ptr(d_vecs), int(n), stream))
+
+    def delete(self, ids):
+        ids = _np.ascontiguousarray(ids, _np.int64)
+        check(lib().lsc_index_delete(self._h, _ptr(ids), int(ids.size)))
+
+    def search(self, queries, k: int):
+        q = _np.ascontiguousarray(queries, _np.float32).reshape(-1, self.dim)
+        B = q.shape[0]
+        ids = _np.empty((B, k), _np.int64)
+        scores = _np.empty((B, k), _np.float32)
+        check(lib().lsc_index_search(self._h, _ptr(q), B, k, _ptr(ids), _ptr(scores)))
+        return ids, scores
+
+    def search_dev(self, d_queries, B, k, d_out_ids, d_out_scores, stream=0):
+        check(lib().lsc_index_search_dev(self._h, _ptr(d_queries), B, k, _ptr(d_out_ids), _ptr(d_out_scores), stream))
+
+    def scores_naive_dev(self, d_queries, B, d_scores, stream=0):
+        check(lib().lsc_index_scores_naive_dev(self._h, _ptr(d_queries), B, _ptr(d_scores), stream))
+
+    @property
+    def launch_count(self) -> int:
+        return int(lib().lsc_index_launch_count(self._h))
+
+    def close(self):
+        if self._h:
+            lib().lsc_index_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def topk_merge_dev(d_ids, d_scores, parts, B, k, d_out_ids, d_out_scores, stream=0):
+    check(lib().lsc_topk_merge_dev(_ptr(d_ids), _ptr(d_scores), parts, B, k, _ptr(d_out_ids), _ptr(d_out_scores), stream))
+
+
+def debug_gemm_dev(d_A, d_W, d_bias, d_residual, d_C, M, N, K, epilogue, impl, stream=0):
+    check(lib().lsc_debug_gemm_dev(_ptr(d_A), _ptr(d_W), _ptr(d_bias), _ptr(d_residual), _ptr(d_C), M, N, K,
+                                   epilogue, impl, stream))

@@ -1,0 +1,227 @@
+// Packed variable-length multi-head self-attention (K3): ctx = softmax(Q K^T / sqrt(d)) V per
+// (sequence, head), over the packed qkv [T, 3H] produced by the QKV GEMM.  Replaces libtorch's
+// scaled-dot-product attention with an additive padding mask in the DJL forward pass
+// (AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:194-196):
+// packing makes the mask implicit — only a sequence's own tokens are ever keys.
+//
+// One CTA per (head, sequence); K and V of that head live in shared memory for the CTA's lifetime;
+// each warp owns 16 query rows at a time and streams key blocks of 64 with an online (flash-style)
+// softmax in fp32.  d_head is 32 or 64, so the contraction depth per tile is tiny and the kernel is
+// bound by exp2 / shared-memory traffic, not by the tensor pipe: it uses warp-level
+// mma.sync.m16n8k16 (bf16 in, fp32 accumulate) rather than tcgen05.
+#include "common.h"
+#include "ptx.cuh"
+
+namespace lsc {
+
+namespace {
+
+constexpr int ATT_THREADS = 256;
+constexpr int KEY_BLOCK = 64;
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2,
+                                            uint32_t& r3) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"(addr));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t& r0, uint32_t& r1,
+                                                  uint32_t& r2, uint32_t& r3) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                               uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+        "{%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+template <int D>
+__global__ void __launch_bounds__(ATT_THREADS)
+attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ cu_seqlens, int H,
+                 int heads, __nv_bfloat16* __restrict__ ctx, float scale_log2e) {
+    constexpr int LD = D + 8;  // padded row (elements): conflict-free ldmatrix
+    extern __shared__ __align__(16) uint8_t att_smem[];
+    const int head = blockIdx.x % heads;  // heads of one sequence are adjacent blocks
+    const int seq = blockIdx.x / heads;
+    const int t0 = __ldg(cu_seqlens + seq);
+    const int s = __ldg(cu_seqlens + seq + 1) - t0;
+    if (s <= 0) return;
+    const int s_pad = (s + KEY_BLOCK - 1) / KEY_BLOCK * KEY_BLOCK;
+    __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(att_smem);
+    __nv_bfloat16* sV = sK + static_cast<size_t>(s_pad) * LD;
+    const size_t row_stride = static_cast<size_t>(3) * H;
+    const __nv_bfloat16* qbase = qkv + static_cast<size_t>(t0) * row_stride + head * D;
+
+    // ---- stage K and V (zero-padded to a multiple of the key block) ----
+    constexpr int CPR = D / 8;  // 16-byte chunks per row
+    for (int i = threadIdx.x; i < s_pad * CPR; i += ATT_THREADS) {
+        const int r = i / CPR, c = i % CPR;
+        uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+        if (r < s) {
+            const __nv_bfloat16* rp = qbase + static_cast<size_t>(r) * row_stride + c * 8;
+            kv = __ldg(reinterpret_cast<const uint4*>(rp + H));
+            vv = __ldg(reinterpret_cast<const uint4*>(rp + 2 * H));
+        }
+        *reinterpret_cast<uint4*>(sK + static_cast<size_t>(r) * LD + c * 8) = kv;
+        *reinterpret_cast<uint4*>(sV + static_cast<size_t>(r) * LD + c * 8) = vv;
+    }
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, tq = lane & 3;
+    const uint32_t sK_addr = smem_u32(sK), sV_addr = smem_u32(sV);
+    const int lm = lane >> 3, lr = lane & 7;  // ldmatrix: matrix index / row within matrix
+
+    for (int qb = warp; qb * 16 < s; qb += ATT_THREADS / 32) {
+        // ---- Q fragments (A operand), straight from global ----
+        uint32_t qa[D / 16][4];
+        const int r_lo = qb * 16 + g, r_hi = r_lo + 8;
+#pragma unroll
+        for (int ks = 0; ks < D / 16; ++ks) {
+            const int c = ks * 16 + 2 * tq;
+            const uint32_t* plo = reinterpret_cast<const uint32_t*>(qbase + static_cast<size_t>(r_lo) * row_stride + c);
+            const uint32_t* phi = reinterpret_cast<const uint32_t*>(qbase + static_cast<size_t>(r_hi) * row_stride + c);
+            qa[ks][0] = r_lo < s ? __ldg(plo) : 0u;
+            qa[ks][1] = r_hi < s ? __ldg(phi) : 0u;
+            qa[ks][2] = r_lo < s ? __ldg(plo + 4) : 0u;
+            qa[ks][3] = r_hi < s ? __ldg(phi + 4) : 0u;
+        }
+        float o[D / 8][4];
+#pragma unroll
+        for (int i = 0; i < D / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+        float m_run[2] = {-INFINITY, -INFINITY};
+        float l_run[2] = {0.f, 0.f};
+
+        for (int kb0 = 0; kb0 < s; kb0 += KEY_BLOCK) {
+            float sc[8][4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) sc[i][0] = sc[i][1] = sc[i][2] = sc[i][3] = 0.f;
+            // ---- S = Q K^T ----
+#pragma unroll
+            for (int ks = 0; ks < D / 16; ++ks) {
+#pragma unroll
+                for (int nt = 0; nt < 8; nt += 2) {
+                    const int key = kb0 + (nt + (lm >> 1)) * 8 + lr;
+                    const int dof = ks * 16 + (lm & 1) * 8;
+                    uint32_t b0, b1, b2, b3;
+                    ldmatrix_x4(sK_addr + (key * LD + dof) * 2, b0, b1, b2, b3);
+                    mma_bf16_16816(sc[nt], qa[ks], b0, b1);
+                    mma_bf16_16816(sc[nt + 1], qa[ks], b2, b3);
+                }
+            }
+            // ---- mask the tail, online softmax ----
+            float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int key = kb0 + nt * 8 + 2 * tq + (j & 1);
+                    if (key >= s) sc[nt][j] = -INFINITY;
+                    mx[j >> 1] = fmaxf(mx[j >> 1], sc[nt][j]);
+                }
+            }
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2) {
+                mx[h2] = fmaxf(mx[h2], __shfl_xor_sync(0xffffffffu, mx[h2], 1));
+                mx[h2] = fmaxf(mx[h2], __shfl_xor_sync(0xffffffffu, mx[h2], 2));
+            }
+            float corr[2], mscaled[2];
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2) {
+                const float m_new = fmaxf(m_run[h2], mx[h2]);  // finite: every block has a valid key
+                corr[h2] = exp2f((m_run[h2] - m_new) * scale_log2e);
+                m_run[h2] = m_new;
+                mscaled[h2] = m_new * scale_log2e;
+                l_run[h2] *= corr[h2];
+            }
+#pragma unroll
+            for (int i = 0; i < D / 8; ++i) {
+                o[i][0] *= corr[0];
+                o[i][1] *= corr[0];
+                o[i][2] *= corr[1];
+                o[i][3] *= corr[1];
+            }
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float p = exp2f(sc[nt][j] * scale_log2e - mscaled[j >> 1]);
+                    sc[nt][j] = p;
+                    l_run[j >> 1] += p;
+                }
+            }
+            // ---- O += P V ----
+#pragma unroll
+            for (int kk = 0; kk < KEY_BLOCK / 16; ++kk) {
+                uint32_t pa[4];
+                pa[0] = pack_bf16x2(sc[2 * kk][0], sc[2 * kk][1]);
+                pa[1] = pack_bf16x2(sc[2 * kk][2], sc[2 * kk][3]);
+                pa[2] = pack_bf16x2(sc[2 * kk + 1][0], sc[2 * kk + 1][1]);
+                pa[3] = pack_bf16x2(sc[2 * kk + 1][2], sc[2 * kk + 1][3]);
+#pragma unroll
+                for (int nt = 0; nt < D / 8; nt += 2) {
+                    const int key = kb0 + kk * 16 + (lm & 1) * 8 + lr;
+                    const int dof = (nt + (lm >> 1)) * 8;
+                    uint32_t b0, b1, b2, b3;
+                    ldmatrix_x4_trans(sV_addr + (key * LD + dof) * 2, b0, b1, b2, b3);
+                    mma_bf16_16816(o[nt], pa, b0, b1);
+                    mma_bf16_16816(o[nt + 1], pa, b2, b3);
+                }
+            }
+        }
+        // ---- normalise and store ----
+#pragma unroll
+        for (int h2 = 0; h2 < 2; ++h2) {
+            l_run[h2] += __shfl_xor_sync(0xffffffffu, l_run[h2], 1);
+            l_run[h2] += __shfl_xor_sync(0xffffffffu, l_run[h2], 2);
+        }
+        const float inv0 = 1.0f / l_run[0], inv1 = 1.0f / l_run[1];
+        __nv_bfloat16* obase = ctx + static_cast<size_t>(t0) * H + head * D;
+#pragma unroll
+        for (int nt = 0; nt < D / 8; ++nt) {
+            const int c = nt * 8 + 2 * tq;
+            if (r_lo < s)
+                *reinterpret_cast<uint32_t*>(obase + static_cast<size_t>(r_lo) * H + c) =
+                    pack_bf16x2(o[nt][0] * inv0, o[nt][1] * inv0);
+            if (r_hi < s)
+                *reinterpret_cast<uint32_t*>(obase + static_cast<size_t>(r_hi) * H + c) =
+                    pack_bf16x2(o[nt][2] * inv1, o[nt][3] * inv1);
+        }
+    }
+}
+
+template <int D>
+int launch_d(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int H, int heads,
+             int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream) {
+    const int s_pad = (max_seqlen + KEY_BLOCK - 1) / KEY_BLOCK * KEY_BLOCK;
+    const size_t smem = static_cast<size_t>(2) * s_pad * (D + 8) * sizeof(__nv_bfloat16);
+    if (smem > 227 * 1024) return fail(LSC_E_UNSUPPORTED, "attention: sequence too long for shared memory");
+    auto kern = attention_kernel<D>;
+    if (smem > 48 * 1024) {
+        LSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    }
+    const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(D));
+    const unsigned grid = static_cast<unsigned>(heads) * static_cast<unsigned>(n_seq);
+    kern<<<grid, ATT_THREADS, smem, stream>>>(qkv, cu_seqlens, H, heads, ctx, scale_log2e);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+}  // namespace
+
+int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int H, int heads,
+                     int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream) {
+    if (n_seq <= 0 || max_seqlen <= 0) return 0;
+    const int d = H / heads;
+    if (d * heads != H) return fail(LSC_E_INVALID, "attention: hidden not divisible by heads");
+    if (d == 32) return launch_d<32>(qkv, cu_seqlens, n_seq, H, heads, max_seqlen, ctx, stream);
+    if (d == 64) return launch_d<64>(qkv, cu_seqlens, n_seq, H, heads, max_seqlen, ctx, stream);
+    return fail(LSC_E_UNSUPPORTED, "attention: head dimension must be 32 or 64");
+}
+
+}  // namespace lsc

@@ -1,0 +1,70 @@
+// Host-side plumbing shared by the translation units: error reporting across the C ABI,
+// CUDA call checking, TMA tensor-map encoding (driver entry point fetched at run time, so the
+// library has no link-time dependency on libcuda), and the kernel launchers' prototypes.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include <string>
+
+#include "../../include/langstream_cuda.h"
+
+namespace lsc {
+
+// ---- errors ------------------------------------------------------------------------------
+void set_error(const std::string& msg);
+int fail(int code, const std::string& msg);
+int fail_cuda(cudaError_t e, const char* what, const char* file, int line);
+
+#define LSC_CUDA(expr)                                                        \
+    do {                                                                      \
+        cudaError_t _e = (expr);                                              \
+        if (_e != cudaSuccess) return ::lsc::fail_cuda(_e, #expr, __FILE__, __LINE__); \
+    } while (0)
+
+#define LSC_TRY(expr)             \
+    do {                          \
+        int _rc = (expr);         \
+        if (_rc != LSC_OK) return _rc; \
+    } while (0)
+
+// ---- TMA tensor maps -----------------------------------------------------------------------
+// 2-D bf16 row-major tensor [rows, cols] (cols contiguous), box = [box_rows, 64 cols] with
+// SWIZZLE_128B: the layout tcgen05 K-major SW128 descriptors expect.  Out-of-bounds elements
+// are filled with zeros.
+int make_tmap_bf16_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                         uint32_t box_rows);
+
+// ---- kernel launchers (defined in the .cu files) ---------------------------------------------
+enum GemmEpilogue { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESIDUAL = 2 };
+
+// tcgen05 GEMM: C[M,N] = epi(A[M,K]·W[N,K]^T + bias).  tmapA: box 128 rows; tmapW: box BN rows,
+// where BN = gemm_tc_block_n(N).  Returns number of kernel launches (1) or <0 on error.
+int gemm_tc_block_n(int N);
+int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const float* bias,
+                   const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,
+                   int num_sms, cudaStream_t stream);
+// CUDA-core validation GEMM (debug).
+int gemm_ref_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const float* bias,
+                    const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,
+                    cudaStream_t stream);
+
+// word + position + token-type embedding gather, then LayerNorm -> bf16 [T,H].
+int embed_ln_launch(const int32_t* token_ids, const int32_t* cu_seqlens, int n_seq, int T, int H,
+                    int max_position, int vocab, const float* word, const float* pos,
+                    const float* type0, const float* gamma, const float* beta, float eps,
+                    __nv_bfloat16* out, int32_t* seq_of_token, cudaStream_t stream);
+// LayerNorm over rows of a bf16 [T,H] tensor (input already holds residual + sublayer output).
+int layernorm_launch(const __nv_bfloat16* in, const float* gamma, const float* beta, float eps,
+                     __nv_bfloat16* out, int T, int H, cudaStream_t stream);
+// Packed variable-length multi-head self-attention over qkv [T,3H] -> ctx [T,H].
+int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int H, int heads,
+                     int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream);
+// Masked mean-pool over each sequence's tokens + L2 normalisation -> fp32 [n_seq,H].
+int pool_l2_launch(const __nv_bfloat16* x, const int32_t* cu_seqlens, int n_seq, int H, float* out,
+                   cudaStream_t stream);
+
+}  // namespace lsc

@@ -1,0 +1,401 @@
+// Encoder handle: owns one model replica on one GPU and runs the BERT forward pass
+// (embeddings+LN -> L x [QKV GEMM, attention, out GEMM+residual, LN, FFN-up GEMM+GELU,
+// FFN-down GEMM+residual, LN] -> mean-pool + L2) over a packed, variable-length batch.
+// It is the native replacement of what the reference reaches through DJL:
+//   AbstractHuggingFaceEmbeddingService ctor (model load)  …/embeddings/AbstractHuggingFaceEmbeddingService.java:110-172
+//   compute(): predictor.predict(text) per text            …/embeddings/AbstractHuggingFaceEmbeddingService.java:183-207
+// (paths under langstream-agents/langstream-ai-agents/src/main/java/com/datastax/oss/streaming/ai).
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "common.h"
+
+namespace lsc {
+namespace {
+
+struct LayerW {
+    __nv_bfloat16* w_qkv = nullptr;  // [3H,H]
+    float* b_qkv = nullptr;          // [3H]
+    __nv_bfloat16* w_o = nullptr;    // [H,H]
+    float* b_o = nullptr;
+    float* ln1_g = nullptr;
+    float* ln1_b = nullptr;
+    __nv_bfloat16* w_1 = nullptr;  // [F,H]
+    float* b_1 = nullptr;
+    __nv_bfloat16* w_2 = nullptr;  // [H,F]
+    float* b_2 = nullptr;
+    float* ln2_g = nullptr;
+    float* ln2_b = nullptr;
+    CUtensorMap tm_qkv, tm_o, tm_1, tm_2;
+};
+
+}  // namespace
+}  // namespace lsc
+
+using namespace lsc;
+
+struct lsc_encoder {
+    lsc_encoder_config cfg;
+    int device = 0;
+    int num_sms = 0;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    std::vector<void*> owned;  // every device allocation of the weights
+    float* d_word = nullptr;
+    float* d_pos = nullptr;
+    float* d_type = nullptr;
+    float* d_emb_g = nullptr;
+    float* d_emb_b = nullptr;
+    std::vector<LayerW> layers;
+    // activation workspace, sized for cap_tokens
+    int64_t cap_tokens = 0;
+    __nv_bfloat16 *x = nullptr, *x1 = nullptr, *tmp = nullptr, *qkv = nullptr, *ctx = nullptr, *ffn = nullptr;
+    // staging for the host-pointer API
+    int64_t cap_stage_tokens = 0, cap_stage_seqs = 0;
+    int32_t* d_ids = nullptr;
+    int32_t* d_cu = nullptr;
+    float* d_out = nullptr;
+    std::atomic<int64_t> launches{0};
+};
+
+namespace lsc {
+namespace {
+
+constexpr int64_t kChunkTokens = 1 << 18;  // tokens per forward pass of the host-pointer API
+
+template <typename T>
+int dev_alloc(lsc_encoder* e, T** p, size_t count) {
+    void* q = nullptr;
+    LSC_CUDA(cudaMalloc(&q, count * sizeof(T)));
+    e->owned.push_back(q);
+    *p = static_cast<T*>(q);
+    return LSC_OK;
+}
+
+int upload_f32(lsc_encoder* e, float** dst, const float* src, size_t count) {
+    LSC_TRY(dev_alloc(e, dst, count));
+    LSC_CUDA(cudaMemcpy(*dst, src, count * sizeof(float), cudaMemcpyHostToDevice));
+    return LSC_OK;
+}
+
+int upload_bf16(lsc_encoder* e, __nv_bfloat16** dst, const float* const* parts, const size_t* counts,
+                int nparts) {
+    size_t total = 0;
+    for (int i = 0; i < nparts; ++i) total += counts[i];
+    std::vector<__nv_bfloat16> h(total);
+    size_t o = 0;
+    for (int i = 0; i < nparts; ++i)
+        for (size_t j = 0; j < counts[i]; ++j) h[o++] = __float2bfloat16_rn(parts[i][j]);
+    LSC_TRY(dev_alloc(e, dst, total));
+    LSC_CUDA(cudaMemcpy(*dst, h.data(), total * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+    return LSC_OK;
+}
+
+int check_config(const lsc_encoder_config* c) {
+    if (c == nullptr) return fail(LSC_E_INVALID, "encoder config is null");
+    if (c->layers <= 0 || c->hidden <= 0 || c->heads <= 0 || c->ffn <= 0 || c->vocab <= 0 ||
+        c->max_position <= 0 || c->type_vocab <= 0)
+        return fail(LSC_E_INVALID, "encoder config: all sizes must be positive");
+    if (c->hidden % c->heads != 0) return fail(LSC_E_INVALID, "encoder config: hidden % heads != 0");
+    const int d = c->hidden / c->heads;
+    if (d != 32 && d != 64) return fail(LSC_E_UNSUPPORTED, "encoder config: head dimension must be 32 or 64");
+    const int H = c->hidden;
+    if (!(H == 128 || H == 256 || H == 384 || H == 512 || H == 768 || H == 1024))
+        return fail(LSC_E_UNSUPPORTED, "encoder config: hidden must be one of 128,256,384,512,768,1024");
+    if (c->ffn % 128 != 0) return fail(LSC_E_UNSUPPORTED, "encoder config: ffn must be a multiple of 128");
+    if (c->gemm_impl != 0 && c->gemm_impl != 1) return fail(LSC_E_INVALID, "encoder config: gemm_impl must be 0 or 1");
+    return LSC_OK;
+}
+
+size_t weights_count(const lsc_encoder_config* c) {
+    const size_t H = c->hidden, F = c->ffn;
+    size_t n = (static_cast<size_t>(c->vocab) + c->max_position + c->type_vocab) * H + 2 * H;
+    const size_t per_layer = 3 * (H * H + H) + (H * H + H) + 2 * H + (F * H + F) + (H * F + H) + 2 * H;
+    return n + per_layer * c->layers;
+}
+
+int ensure_workspace(lsc_encoder* e, int64_t T) {
+    if (T <= e->cap_tokens) return LSC_OK;
+    const int64_t cap = std::max<int64_t>(T, 4096);
+    const size_t H = e->cfg.hidden, F = e->cfg.ffn;
+    LSC_CUDA(cudaDeviceSynchronize());  // earlier passes (on any stream) may still use the old buffers
+    __nv_bfloat16** bufs[6] = {&e->x, &e->x1, &e->tmp, &e->qkv, &e->ctx, &e->ffn};
+    for (auto b : bufs) {
+        if (*b) cudaFree(*b);
+        *b = nullptr;
+    }
+    e->cap_tokens = 0;
+    const size_t sizes[6] = {H, H, H, 3 * H, H, F};
+    for (int i = 0; i < 6; ++i) {
+        void* p = nullptr;
+        LSC_CUDA(cudaMalloc(&p, static_cast<size_t>(cap) * sizes[i] * sizeof(__nv_bfloat16)));
+        *bufs[i] = static_cast<__nv_bfloat16*>(p);
+    }
+    e->cap_tokens = cap;
+    return LSC_OK;
+}
+
+int ensure_staging(lsc_encoder* e, int64_t T, int64_t n_seq) {
+    if (T > e->cap_stage_tokens) {
+        if (e->d_ids) cudaFree(e->d_ids);
+        e->d_ids = nullptr;
+        e->cap_stage_tokens = 0;
+        const int64_t cap = std::max<int64_t>(T, 4096);
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->d_ids), cap * sizeof(int32_t)));
+        e->cap_stage_tokens = cap;
+    }
+    if (n_seq > e->cap_stage_seqs) {
+        if (e->d_cu) cudaFree(e->d_cu);
+        if (e->d_out) cudaFree(e->d_out);
+        e->d_cu = nullptr;
+        e->d_out = nullptr;
+        e->cap_stage_seqs = 0;
+        const int64_t cap = std::max<int64_t>(n_seq, 64);
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->d_cu), (cap + 1) * sizeof(int32_t)));
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->d_out), cap * e->cfg.hidden * sizeof(float)));
+        e->cap_stage_seqs = cap;
+    }
+    return LSC_OK;
+}
+
+int gemm(lsc_encoder* e, const CUtensorMap& tmA, const __nv_bfloat16* A, const CUtensorMap& tmW,
+         const __nv_bfloat16* W, const float* bias, const __nv_bfloat16* residual, __nv_bfloat16* C, int M,
+         int N, int K, int epi, cudaStream_t st) {
+    if (e->cfg.gemm_impl == 1) return gemm_ref_launch(A, W, bias, residual, C, M, N, K, epi, st);
+    return gemm_tc_launch(tmA, tmW, bias, residual, C, M, N, K, epi, e->num_sms, st);
+}
+
+#define LSC_LAUNCH(expr)              \
+    do {                              \
+        int _n = (expr);              \
+        if (_n < 0) return _n;        \
+        nlaunch += _n;                \
+    } while (0)
+
+// The forward pass proper; everything is enqueued on `st`, nothing synchronises.
+int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int n_seq, int T,
+            int max_seqlen, float* d_out, cudaStream_t st) {
+    const lsc_encoder_config& c = e->cfg;
+    const int H = c.hidden, F = c.ffn;
+    int64_t nlaunch = 0;
+    if (T > 0) {
+        LSC_TRY(ensure_workspace(e, T));
+        CUtensorMap tm_x, tm_x1, tm_ctx, tm_ffn;
+        if (c.gemm_impl == 0) {
+            LSC_TRY(make_tmap_bf16_sw128(&tm_x, e->x, T, H, 128));
+            LSC_TRY(make_tmap_bf16_sw128(&tm_x1, e->x1, T, H, 128));
+            LSC_TRY(make_tmap_bf16_sw128(&tm_ctx, e->ctx, T, H, 128));
+            LSC_TRY(make_tmap_bf16_sw128(&tm_ffn, e->ffn, T, F, 128));
+        }
+        LSC_LAUNCH(embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word,
+                                   e->d_pos, e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, st));
+        for (int l = 0; l < c.layers; ++l) {
+            const LayerW& w = e->layers[l];
+            LSC_LAUNCH(gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.b_qkv, nullptr, e->qkv, T, 3 * H, H, EPI_BIAS, st));
+            LSC_LAUNCH(attention_launch(e->qkv, d_cu, n_seq, H, c.heads, max_seqlen, e->ctx, st));
+            LSC_LAUNCH(gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, st));
+            LSC_LAUNCH(layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
+            LSC_LAUNCH(gemm(e, tm_x1, e->x1, w.tm_1, w.w_1, w.b_1, nullptr, e->ffn, T, F, H, EPI_BIAS_GELU, st));
+            LSC_LAUNCH(gemm(e, tm_ffn, e->ffn, w.tm_2, w.w_2, w.b_2, e->x1, e->tmp, T, H, F, EPI_BIAS_RESIDUAL, st));
+            LSC_LAUNCH(layernorm_launch(e->tmp, w.ln2_g, w.ln2_b, c.ln_eps, e->x, T, H, st));
+        }
+    }
+    LSC_LAUNCH(pool_l2_launch(e->x, d_cu, n_seq, H, d_out, st));
+    e->launches += nlaunch;
+    return LSC_OK;
+}
+
+}  // namespace
+}  // namespace lsc
+
+extern "C" {
+
+size_t lsc_encoder_weights_nbytes(const lsc_encoder_config* cfg) {
+    if (check_config(cfg) != LSC_OK) return 0;
+    return weights_count(cfg) * sizeof(float);
+}
+
+void lsc_encoder_destroy(lsc_encoder* e) {
+    if (e == nullptr) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    for (void* p : e->owned) cudaFree(p);
+    void* ws[] = {e->x, e->x1, e->tmp, e->qkv, e->ctx, e->ffn, e->d_ids, e->d_cu, e->d_out};
+    for (void* p : ws)
+        if (p) cudaFree(p);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_t nbytes, int device,
+                       lsc_encoder** out) {
+    if (out == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_create: out is null");
+    *out = nullptr;
+    LSC_TRY(check_config(cfg));
+    if (weights == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_create: weights is null");
+    if (nbytes != weights_count(cfg) * sizeof(float))
+        return fail(LSC_E_INVALID, "lsc_encoder_create: weight blob size does not match the config");
+    int ndev = 0;
+    LSC_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(LSC_E_INVALID, "lsc_encoder_create: no such device");
+    LSC_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    LSC_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(LSC_E_UNSUPPORTED, "langstream-cuda needs a Blackwell (sm_100) GPU; there is no fallback path");
+
+    lsc_encoder* e = new lsc_encoder();
+    e->cfg = *cfg;
+    e->device = device;
+    e->num_sms = prop.multiProcessorCount;
+    int rc = LSC_OK;
+    auto body = [&]() -> int {
+        LSC_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+        const size_t H = cfg->hidden, F = cfg->ffn;
+        const float* p = static_cast<const float*>(weights);
+        LSC_TRY(upload_f32(e, &e->d_word, p, static_cast<size_t>(cfg->vocab) * H));
+        p += static_cast<size_t>(cfg->vocab) * H;
+        LSC_TRY(upload_f32(e, &e->d_pos, p, static_cast<size_t>(cfg->max_position) * H));
+        p += static_cast<size_t>(cfg->max_position) * H;
+        LSC_TRY(upload_f32(e, &e->d_type, p, static_cast<size_t>(cfg->type_vocab) * H));
+        p += static_cast<size_t>(cfg->type_vocab) * H;
+        LSC_TRY(upload_f32(e, &e->d_emb_g, p, H));
+        p += H;
+        LSC_TRY(upload_f32(e, &e->d_emb_b, p, H));
+        p += H;
+        e->layers.resize(cfg->layers);
+        for (int l = 0; l < cfg->layers; ++l) {
+            LayerW& w = e->layers[l];
+            const float* qw = p;            const float* qb = qw + H * H;
+            const float* kw = qb + H;       const float* kb = kw + H * H;
+            const float* vw = kb + H;       const float* vb = vw + H * H;
+            p = vb + H;
+            const float* wparts[3] = {qw, kw, vw};
+            const size_t wcounts[3] = {H * H, H * H, H * H};
+            LSC_TRY(upload_bf16(e, &w.w_qkv, wparts, wcounts, 3));
+            std::vector<float> bq(3 * H);
+            memcpy(bq.data(), qb, H * sizeof(float));
+            memcpy(bq.data() + H, kb, H * sizeof(float));
+            memcpy(bq.data() + 2 * H, vb, H * sizeof(float));
+            LSC_TRY(upload_f32(e, &w.b_qkv, bq.data(), 3 * H));
+            const size_t hh = H * H, fh = F * H;
+            LSC_TRY(upload_bf16(e, &w.w_o, &p, &hh, 1));
+            p += hh;
+            LSC_TRY(upload_f32(e, &w.b_o, p, H));
+            p += H;
+            LSC_TRY(upload_f32(e, &w.ln1_g, p, H));
+            p += H;
+            LSC_TRY(upload_f32(e, &w.ln1_b, p, H));
+            p += H;
+            LSC_TRY(upload_bf16(e, &w.w_1, &p, &fh, 1));
+            p += fh;
+            LSC_TRY(upload_f32(e, &w.b_1, p, F));
+            p += F;
+            LSC_TRY(upload_bf16(e, &w.w_2, &p, &fh, 1));
+            p += fh;
+            LSC_TRY(upload_f32(e, &w.b_2, p, H));
+            p += H;
+            LSC_TRY(upload_f32(e, &w.ln2_g, p, H));
+            p += H;
+            LSC_TRY(upload_f32(e, &w.ln2_b, p, H));
+            p += H;
+            if (cfg->gemm_impl == 0) {
+                const int bn3 = gemm_tc_block_n(3 * static_cast<int>(H));
+                const int bnh = gemm_tc_block_n(static_cast<int>(H));
+                const int bnf = gemm_tc_block_n(static_cast<int>(F));
+                if (bn3 == 0 || bnh == 0 || bnf == 0)
+                    return fail(LSC_E_UNSUPPORTED, "encoder: hidden and ffn must be multiples of 128");
+                LSC_TRY(make_tmap_bf16_sw128(&w.tm_qkv, w.w_qkv, 3 * H, H, bn3));
+                LSC_TRY(make_tmap_bf16_sw128(&w.tm_o, w.w_o, H, H, bnh));
+                LSC_TRY(make_tmap_bf16_sw128(&w.tm_1, w.w_1, F, H, bnf));
+                LSC_TRY(make_tmap_bf16_sw128(&w.tm_2, w.w_2, H, F, bnh));
+            }
+        }
+        return LSC_OK;
+    };
+    rc = body();
+    if (rc != LSC_OK) {
+        std::string msg = lsc_last_error();
+        lsc_encoder_destroy(e);
+        set_error(msg);
+        return rc;
+    }
+    *out = e;
+    return LSC_OK;
+}
+
+int lsc_encoder_dim(const lsc_encoder* e) { return e ? e->cfg.hidden : LSC_E_INVALID; }
+
+int64_t lsc_encoder_launch_count(const lsc_encoder* e) { return e ? e->launches.load() : 0; }
+
+int lsc_encoder_embed_dev(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu_seqlens,
+                          int32_t n_seq, int32_t total_tokens, int32_t max_seqlen, float* d_out,
+                          void* stream) {
+    if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed_dev: encoder is null");
+    if (n_seq < 0 || total_tokens < 0 || max_seqlen < 0) return fail(LSC_E_INVALID, "lsc_encoder_embed_dev: negative size");
+    if (n_seq == 0) return LSC_OK;
+    if (d_cu_seqlens == nullptr || d_out == nullptr || (total_tokens > 0 && d_token_ids == nullptr))
+        return fail(LSC_E_INVALID, "lsc_encoder_embed_dev: null pointer");
+    if (max_seqlen > e->cfg.max_position)
+        return fail(LSC_E_TOO_LONG, "Illegal input, maybe the number of tokens is too high");
+    std::lock_guard<std::mutex> lock(e->mu);
+    LSC_CUDA(cudaSetDevice(e->device));
+    return forward(e, d_token_ids, d_cu_seqlens, n_seq, total_tokens, max_seqlen, d_out,
+                   static_cast<cudaStream_t>(stream));
+}
+
+int lsc_encoder_embed(lsc_encoder* e, const int32_t* token_ids, const int32_t* cu_seqlens, int32_t n_seq,
+                      float* out) {
+    if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed: encoder is null");
+    if (n_seq < 0) return fail(LSC_E_INVALID, "lsc_encoder_embed: negative n_seq");
+    if (n_seq == 0) return LSC_OK;
+    if (cu_seqlens == nullptr || out == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed: null pointer");
+    if (cu_seqlens[0] != 0) return fail(LSC_E_INVALID, "lsc_encoder_embed: cu_seqlens[0] must be 0");
+    const int H = e->cfg.hidden;
+    for (int i = 0; i < n_seq; ++i) {
+        const int len = cu_seqlens[i + 1] - cu_seqlens[i];
+        if (len < 0) return fail(LSC_E_INVALID, "lsc_encoder_embed: cu_seqlens must be non-decreasing");
+        if (len > e->cfg.max_position)
+            return fail(LSC_E_TOO_LONG, "Illegal input, maybe the number of tokens is too high");
+    }
+    const int64_t total = cu_seqlens[n_seq];
+    if (total > 0 && token_ids == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed: token_ids is null");
+    for (int64_t t = 0; t < total; ++t)
+        if (token_ids[t] < 0 || token_ids[t] >= e->cfg.vocab)
+            return fail(LSC_E_INVALID, "lsc_encoder_embed: token id outside the vocabulary");
+
+    std::lock_guard<std::mutex> lock(e->mu);
+    LSC_CUDA(cudaSetDevice(e->device));
+    // Chunk the batch so one pass holds at most kChunkTokens tokens.
+    std::vector<int32_t> cu_local;
+    int s0 = 0;
+    while (s0 < n_seq) {
+        int s1 = s0;
+        int maxlen = 0;
+        while (s1 < n_seq && (s1 == s0 || cu_seqlens[s1 + 1] - cu_seqlens[s0] <= kChunkTokens)) {
+            maxlen = std::max(maxlen, cu_seqlens[s1 + 1] - cu_seqlens[s1]);
+            ++s1;
+        }
+        const int ns = s1 - s0;
+        const int T = cu_seqlens[s1] - cu_seqlens[s0];
+        cu_local.resize(ns + 1);
+        for (int i = 0; i <= ns; ++i) cu_local[i] = cu_seqlens[s0 + i] - cu_seqlens[s0];
+        LSC_TRY(ensure_staging(e, T, ns));
+        if (T > 0)
+            LSC_CUDA(cudaMemcpyAsync(e->d_ids, token_ids + cu_seqlens[s0], static_cast<size_t>(T) * sizeof(int32_t),
+                                     cudaMemcpyHostToDevice, e->stream));
+        LSC_CUDA(cudaMemcpyAsync(e->d_cu, cu_local.data(), static_cast<size_t>(ns + 1) * sizeof(int32_t),
+                                 cudaMemcpyHostToDevice, e->stream));
+        LSC_TRY(forward(e, e->d_ids, e->d_cu, ns, T, maxlen, e->d_out, e->stream));
+        LSC_CUDA(cudaMemcpyAsync(out + static_cast<size_t>(s0) * H, e->d_out, static_cast<size_t>(ns) * H * sizeof(float),
+                                 cudaMemcpyDeviceToHost, e->stream));
+        LSC_CUDA(cudaStreamSynchronize(e->stream));  // cu_local and staging are reused by the next chunk
+        s0 = s1;
+    }
+    return LSC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,418 @@
+// Vector index handle: a dense slab of L2-normalised bf16 rows in HBM plus the host-side id <-> slot
+// map.  It is the native stand-in for the HerdDB table the reference reaches through JDBC:
+//   write side  JdbcVectorDatabaseWriter.upsert (UPDATE / INSERT / DELETE on null value)
+//               langstream-agents/langstream-vector-agents/src/main/java/ai/langstream/agents/vector/jdbc/JdbcWriter.java:139-179
+//   read side   JdbcDataSourceImpl.fetchData running the cosine ORDER BY … LIMIT k scan
+//               langstream-agents/langstream-ai-agents/src/main/java/ai/langstream/ai/agents/datasource/impl/JdbcDataSourceProvider.java:103-124
+// Deleting swaps the last row into the freed slot, so the slab stays dense and the scan needs no
+// tombstone test.
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+#include <vector>
+
+#include "common.h"
+#include "topk.h"
+
+using namespace lsc;
+
+struct lsc_index {
+    int device = 0;
+    int num_sms = 0;
+    int dim = 0;
+    int64_t capacity = 0;
+    int64_t n = 0;
+    __nv_bfloat16* d_rows = nullptr;
+    int64_t* d_ids = nullptr;
+    std::vector<int64_t> ids;                      // host mirror of d_ids[0..n)
+    std::unordered_map<int64_t, int64_t> slot_of;  // id -> slot
+    CUtensorMap tmapC;
+    // query / scratch buffers (grow on demand)
+    int64_t cap_q = 0;      // padded query rows the buffers hold
+    int64_t cap_cand = 0;   // candidate entries the scratch holds
+    float* d_q32 = nullptr;            // staging for host queries / host upserts
+    int64_t cap_q32 = 0;               // floats
+    __nv_bfloat16* d_qbf = nullptr;    // [cap_q, dim]
+    CUtensorMap tmapQ;
+    float* d_cand_scores = nullptr;
+    int32_t* d_cand_idx = nullptr;
+    int64_t* d_out_ids = nullptr;      // staging for host results
+    float* d_out_scores = nullptr;
+    int64_t cap_out = 0;
+    int64_t* d_slots = nullptr;        // upsert target slots
+    int64_t cap_slots = 0;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    std::atomic<int64_t> launches{0};
+};
+
+namespace lsc {
+namespace {
+
+int grow_rows(lsc_index* ix, int64_t need) {
+    if (need <= ix->capacity) return LSC_OK;
+    int64_t cap = std::max<int64_t>(ix->capacity * 2, std::max<int64_t>(need, 1024));
+    if (cap > 0x7fffff00LL) cap = 0x7fffff00LL;  // slots are int32 inside the scan
+    if (need > cap) return fail(LSC_E_UNSUPPORTED, "index: more than 2^31 rows per shard");
+    LSC_CUDA(cudaDeviceSynchronize());
+    __nv_bfloat16* rows = nullptr;
+    int64_t* ids = nullptr;
+    LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&rows), static_cast<size_t>(cap) * ix->dim * sizeof(__nv_bfloat16)));
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&ids), static_cast<size_t>(cap) * sizeof(int64_t));
+    if (e != cudaSuccess) {
+        cudaFree(rows);
+        return fail_cuda(e, "cudaMalloc(ids)", __FILE__, __LINE__);
+    }
+    if (ix->n > 0) {
+        LSC_CUDA(cudaMemcpy(rows, ix->d_rows, static_cast<size_t>(ix->n) * ix->dim * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice));
+        LSC_CUDA(cudaMemcpy(ids, ix->d_ids, static_cast<size_t>(ix->n) * sizeof(int64_t), cudaMemcpyDeviceToDevice));
+    }
+    if (ix->d_rows) cudaFree(ix->d_rows);
+    if (ix->d_ids) cudaFree(ix->d_ids);
+    ix->d_rows = rows;
+    ix->d_ids = ids;
+    ix->capacity = cap;
+    return make_tmap_bf16_sw128(&ix->tmapC, ix->d_rows, static_cast<uint64_t>(cap), ix->dim, 256);
+}
+
+template <typename T>
+int grow_buf(T** p, int64_t* cap, int64_t need, int64_t floor_) {
+    if (need <= *cap) return LSC_OK;
+    LSC_CUDA(cudaDeviceSynchronize());
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    const int64_t c = std::max<int64_t>(need, floor_);
+    LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(p), static_cast<size_t>(c) * sizeof(T)));
+    *cap = c;
+    return LSC_OK;
+}
+
+int ensure_query_buffers(lsc_index* ix, int B, int k) {
+    const int64_t bpad = (static_cast<int64_t>(B) + TK_QROWS - 1) / TK_QROWS * TK_QROWS;
+    if (bpad > ix->cap_q) {
+        LSC_CUDA(cudaDeviceSynchronize());
+        if (ix->d_qbf) cudaFree(ix->d_qbf);
+        ix->d_qbf = nullptr;
+        ix->cap_q = 0;
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_qbf), static_cast<size_t>(bpad) * ix->dim * sizeof(__nv_bfloat16)));
+        ix->cap_q = bpad;
+        LSC_TRY(make_tmap_bf16_sw128(&ix->tmapQ, ix->d_qbf, static_cast<uint64_t>(bpad), ix->dim, TK_QROWS));
+    }
+    const int64_t cand = (bpad / TK_QROWS) * ix->num_sms * TK_QROWS * static_cast<int64_t>(k);
+    if (cand > ix->cap_cand) {
+        int64_t c1 = ix->cap_cand, c2 = ix->cap_cand;
+        LSC_TRY(grow_buf(&ix->d_cand_scores, &c1, cand, 1 << 16));
+        LSC_TRY(grow_buf(&ix->d_cand_idx, &c2, cand, 1 << 16));
+        ix->cap_cand = std::min(c1, c2);
+    }
+    return LSC_OK;
+}
+
+#define LSC_LAUNCH(expr)              \
+    do {                              \
+        int _n = (expr);              \
+        if (_n < 0) return _n;        \
+        nlaunch += _n;                \
+    } while (0)
+
+// queries (device fp32 [B,dim]) -> top-k ids/scores (device), all on `st`.
+int search_dev(lsc_index* ix, const float* d_queries, int B, int k, int64_t* d_out_ids, float* d_out_scores,
+               cudaStream_t st) {
+    int64_t nlaunch = 0;
+    if (ix->n == 0) {
+        LSC_LAUNCH(fill_empty_launch(d_out_ids, d_out_scores, static_cast<size_t>(B) * k, st));
+        ix->launches += nlaunch;
+        return LSC_OK;
+    }
+    LSC_TRY(ensure_query_buffers(ix, B, k));
+    const int bpad = (B + TK_QROWS - 1) / TK_QROWS * TK_QROWS;
+    LSC_LAUNCH(normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st));
+    const int n_rows = static_cast<int>(ix->n);
+    const int grid = topk_scan_grid(n_rows, ix->num_sms);
+    for (int qb = 0; qb * TK_QROWS < B; ++qb) {
+        const int nq = std::min(TK_QROWS, B - qb * TK_QROWS);
+        const size_t off = static_cast<size_t>(qb) * grid * TK_QROWS * k;
+        LSC_LAUNCH(topk_scan_launch(ix->tmapQ, ix->tmapC, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
+                                    ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+    }
+    LSC_LAUNCH(topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, d_out_ids,
+                                      d_out_scores, st));
+    ix->launches += nlaunch;
+    return LSC_OK;
+}
+
+int upsert_dev(lsc_index* ix, const int64_t* ids, const float* d_vecs, int n, cudaStream_t st) {
+    // Resolve target slots on the host: existing id -> its slot, new id -> appended slot; an id that
+    // occurs twice in the batch keeps only its last row.
+    std::vector<int64_t> slots(n);
+    std::unordered_map<int64_t, int> last_in_batch;
+    last_in_batch.reserve(static_cast<size_t>(n) * 2);
+    for (int i = 0; i < n; ++i) last_in_batch[ids[i]] = i;
+    int64_t new_n = ix->n;
+    std::vector<int64_t> new_ids;
+    for (int i = 0; i < n; ++i) {
+        if (last_in_batch[ids[i]] != i) {
+            slots[i] = -1;
+            continue;
+        }
+        auto it = ix->slot_of.find(ids[i]);
+        if (it != ix->slot_of.end()) {
+            slots[i] = it->second;
+        } else {
+            slots[i] = new_n++;
+            new_ids.push_back(ids[i]);
+        }
+    }
+    LSC_TRY(grow_rows(ix, new_n));
+    LSC_TRY(grow_buf(&ix->d_slots, &ix->cap_slots, n, 1024));
+    LSC_CUDA(cudaMemcpyAsync(ix->d_slots, slots.data(), static_cast<size_t>(n) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+    if (!new_ids.empty())
+        LSC_CUDA(cudaMemcpyAsync(ix->d_ids + ix->n, new_ids.data(), new_ids.size() * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+    int64_t nlaunch = 0;
+    LSC_LAUNCH(normalize_rows_launch(d_vecs, n, n, ix->dim, ix->d_slots, ix->d_rows, st));
+    LSC_CUDA(cudaStreamSynchronize(st));  // host vectors `slots` / `new_ids` go out of scope
+    for (int64_t id : new_ids) {
+        ix->slot_of[id] = static_cast<int64_t>(ix->ids.size());
+        ix->ids.push_back(id);
+    }
+    ix->n = new_n;
+    ix->launches += nlaunch;
+    return LSC_OK;
+}
+
+}  // namespace
+}  // namespace lsc
+
+extern "C" {
+
+void lsc_index_destroy(lsc_index* ix) {
+    if (ix == nullptr) return;
+    cudaSetDevice(ix->device);
+    cudaDeviceSynchronize();
+    void* bufs[] = {ix->d_rows, ix->d_ids, ix->d_q32, ix->d_qbf, ix->d_cand_scores, ix->d_cand_idx,
+                    ix->d_out_ids, ix->d_out_scores, ix->d_slots};
+    for (void* p : bufs)
+        if (p) cudaFree(p);
+    if (ix->stream) cudaStreamDestroy(ix->stream);
+    delete ix;
+}
+
+int lsc_index_create(int32_t dim, int64_t capacity, int device, lsc_index** out) {
+    if (out == nullptr) return fail(LSC_E_INVALID, "lsc_index_create: out is null");
+    *out = nullptr;
+    if (dim <= 0 || dim % 64 != 0 || dim > 512)
+        return fail(LSC_E_UNSUPPORTED, "lsc_index_create: dim must be a multiple of 64 and <= 512");
+    if (capacity < 0) return fail(LSC_E_INVALID, "lsc_index_create: negative capacity");
+    int ndev = 0;
+    LSC_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(LSC_E_INVALID, "lsc_index_create: no such device");
+    LSC_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    LSC_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(LSC_E_UNSUPPORTED, "langstream-cuda needs a Blackwell (sm_100) GPU; there is no fallback path");
+    lsc_index* ix = new lsc_index();
+    ix->device = device;
+    ix->num_sms = prop.multiProcessorCount;
+    ix->dim = dim;
+    int rc = LSC_OK;
+    cudaError_t ce = cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking);
+    if (ce != cudaSuccess) rc = fail_cuda(ce, "cudaStreamCreateWithFlags", __FILE__, __LINE__);
+    if (rc == LSC_OK) rc = grow_rows(ix, std::max<int64_t>(capacity, 1));
+    if (rc != LSC_OK) {
+        std::string msg = lsc_last_error();
+        lsc_index_destroy(ix);
+        set_error(msg);
+        return rc;
+    }
+    *out = ix;
+    return LSC_OK;
+}
+
+int64_t lsc_index_size(const lsc_index* ix) { return ix ? ix->n : 0; }
+
+int64_t lsc_index_launch_count(const lsc_index* ix) { return ix ? ix->launches.load() : 0; }
+
+int lsc_index_upsert_dev(lsc_index* ix, const int64_t* ids, const float* d_vecs, int32_t n, void* stream) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_upsert_dev: index is null");
+    if (n < 0) return fail(LSC_E_INVALID, "lsc_index_upsert_dev: negative n");
+    if (n == 0) return LSC_OK;
+    if (ids == nullptr || d_vecs == nullptr) return fail(LSC_E_INVALID, "lsc_index_upsert_dev: null pointer");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    return upsert_dev(ix, ids, d_vecs, n, static_cast<cudaStream_t>(stream));
+}
+
+int lsc_index_upsert(lsc_index* ix, const int64_t* ids, const float* vecs, int32_t n) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_upsert: index is null");
+    if (n < 0) return fail(LSC_E_INVALID, "lsc_index_upsert: negative n");
+    if (n == 0) return LSC_OK;
+    if (ids == nullptr || vecs == nullptr) return fail(LSC_E_INVALID, "lsc_index_upsert: null pointer");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    const int64_t chunk = 1 << 18;  // rows per staging pass
+    for (int64_t o = 0; o < n; o += chunk) {
+        const int m = static_cast<int>(std::min<int64_t>(chunk, n - o));
+        LSC_TRY(grow_buf(&ix->d_q32, &ix->cap_q32, static_cast<int64_t>(m) * ix->dim, 1 << 16));
+        LSC_CUDA(cudaMemcpyAsync(ix->d_q32, vecs + o * ix->dim, static_cast<size_t>(m) * ix->dim * sizeof(float),
+                                 cudaMemcpyHostToDevice, ix->stream));
+        LSC_TRY(upsert_dev(ix, ids + o, ix->d_q32, m, ix->stream));
+    }
+    return LSC_OK;
+}
+
+int lsc_index_delete(lsc_index* ix, const int64_t* ids, int32_t n) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_delete: index is null");
+    if (n < 0) return fail(LSC_E_INVALID, "lsc_index_delete: negative n");
+    if (n == 0) return LSC_OK;
+    if (ids == nullptr) return fail(LSC_E_INVALID, "lsc_index_delete: null pointer");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    LSC_CUDA(cudaDeviceSynchronize());
+    const size_t row_bytes = static_cast<size_t>(ix->dim) * sizeof(__nv_bfloat16);
+    for (int i = 0; i < n; ++i) {
+        auto it = ix->slot_of.find(ids[i]);
+        if (it == ix->slot_of.end()) continue;
+        const int64_t slot = it->second;
+        const int64_t last = ix->n - 1;
+        ix->slot_of.erase(it);
+        if (slot != last) {
+            const int64_t moved = ix->ids[last];
+            LSC_CUDA(cudaMemcpy(ix->d_rows + slot * ix->dim, ix->d_rows + last * ix->dim, row_bytes, cudaMemcpyDeviceToDevice));
+            LSC_CUDA(cudaMemcpy(ix->d_ids + slot, &moved, sizeof(int64_t), cudaMemcpyHostToDevice));
+            ix->ids[slot] = moved;
+            ix->slot_of[moved] = slot;
+        }
+        ix->ids.pop_back();
+        ix->n = last;
+    }
+    return LSC_OK;
+}
+
+int lsc_index_search_dev(lsc_index* ix, const float* d_queries, int32_t B, int32_t k, int64_t* d_out_ids,
+                         float* d_out_scores, void* stream) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_search_dev: index is null");
+    if (B < 0) return fail(LSC_E_INVALID, "lsc_index_search_dev: negative B");
+    if (k < 1 || k > TK_KMAX) return fail(LSC_E_INVALID, "lsc_index_search_dev: k must be in [1,128]");
+    if (B == 0) return LSC_OK;
+    if (d_queries == nullptr || d_out_ids == nullptr || d_out_scores == nullptr)
+        return fail(LSC_E_INVALID, "lsc_index_search_dev: null pointer");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    return search_dev(ix, d_queries, B, k, d_out_ids, d_out_scores, static_cast<cudaStream_t>(stream));
+}
+
+int lsc_index_search(lsc_index* ix, const float* queries, int32_t B, int32_t k, int64_t* out_ids,
+                     float* out_scores) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_search: index is null");
+    if (B < 0) return fail(LSC_E_INVALID, "lsc_index_search: negative B");
+    if (k < 1 || k > TK_KMAX) return fail(LSC_E_INVALID, "lsc_index_search: k must be in [1,128]");
+    if (B == 0) return LSC_OK;
+    if (queries == nullptr || out_ids == nullptr || out_scores == nullptr)
+        return fail(LSC_E_INVALID, "lsc_index_search: null pointer");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    LSC_TRY(grow_buf(&ix->d_q32, &ix->cap_q32, static_cast<int64_t>(B) * ix->dim, 1 << 16));
+    const int64_t nout = static_cast<int64_t>(B) * k;
+    if (nout > ix->cap_out) {
+        int64_t c1 = ix->cap_out, c2 = ix->cap_out;
+        LSC_TRY(grow_buf(&ix->d_out_ids, &c1, nout, 4096));
+        LSC_TRY(grow_buf(&ix->d_out_scores, &c2, nout, 4096));
+        ix->cap_out = std::min(c1, c2);
+    }
+    LSC_CUDA(cudaMemcpyAsync(ix->d_q32, queries, static_cast<size_t>(B) * ix->dim * sizeof(float), cudaMemcpyHostToDevice, ix->stream));
+    LSC_TRY(search_dev(ix, ix->d_q32, B, k, ix->d_out_ids, ix->d_out_scores, ix->stream));
+    LSC_CUDA(cudaMemcpyAsync(out_ids, ix->d_out_ids, static_cast<size_t>(nout) * sizeof(int64_t), cudaMemcpyDeviceToHost, ix->stream));
+    LSC_CUDA(cudaMemcpyAsync(out_scores, ix->d_out_scores, static_cast<size_t>(nout) * sizeof(float), cudaMemcpyDeviceToHost, ix->stream));
+    LSC_CUDA(cudaStreamSynchronize(ix->stream));
+    return LSC_OK;
+}
+
+int lsc_index_scores_naive_dev(lsc_index* ix, const float* d_queries, int32_t B, float* d_scores, void* stream) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_scores_naive_dev: index is null");
+    if (B <= 0 || d_queries == nullptr || d_scores == nullptr) return fail(LSC_E_INVALID, "lsc_index_scores_naive_dev: bad argument");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    LSC_TRY(ensure_query_buffers(ix, B, 1));
+    const int bpad = (B + TK_QROWS - 1) / TK_QROWS * TK_QROWS;
+    int rc = normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st);
+    if (rc < 0) return rc;
+    rc = scores_naive_launch(ix->d_rows, ix->n, ix->dim, ix->d_qbf, B, d_scores, st);
+    return rc < 0 ? rc : LSC_OK;
+}
+
+int lsc_topk_merge_dev(const int64_t* d_ids, const float* d_scores, int32_t parts, int32_t B, int32_t k,
+                       int64_t* d_out_ids, float* d_out_scores, void* stream) {
+    if (d_ids == nullptr || d_scores == nullptr || d_out_ids == nullptr || d_out_scores == nullptr)
+        return fail(LSC_E_INVALID, "lsc_topk_merge_dev: null pointer");
+    if (parts < 1 || B < 0 || k < 1 || k > TK_KMAX) return fail(LSC_E_INVALID, "lsc_topk_merge_dev: bad size");
+    int rc = topk_merge_shards_launch(d_scores, d_ids, parts, B, k, d_out_ids, d_out_scores, static_cast<cudaStream_t>(stream));
+    return rc < 0 ? rc : LSC_OK;
+}
+
+// File format: "LSCIDX01", int32 dim, int64 n, n int64 ids, n*dim bf16 rows (slot order).
+int lsc_index_save(lsc_index* ix, const char* path) {
+    if (ix == nullptr || path == nullptr) return fail(LSC_E_INVALID, "lsc_index_save: null argument");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    LSC_CUDA(cudaDeviceSynchronize());
+    std::vector<__nv_bfloat16> rows(static_cast<size_t>(ix->n) * ix->dim);
+    if (ix->n > 0)
+        LSC_CUDA(cudaMemcpy(rows.data(), ix->d_rows, rows.size() * sizeof(__nv_bfloat16), cudaMemcpyDeviceToHost));
+    FILE* f = fopen(path, "wb");
+    if (f == nullptr) return fail(LSC_E_IO, std::string("lsc_index_save: cannot open ") + path);
+    const int32_t dim = ix->dim;
+    const int64_t n = ix->n;
+    bool ok = fwrite("LSCIDX01", 1, 8, f) == 8 && fwrite(&dim, sizeof(dim), 1, f) == 1 && fwrite(&n, sizeof(n), 1, f) == 1;
+    if (ok && n > 0)
+        ok = fwrite(ix->ids.data(), sizeof(int64_t), static_cast<size_t>(n), f) == static_cast<size_t>(n) &&
+             fwrite(rows.data(), sizeof(__nv_bfloat16), rows.size(), f) == rows.size();
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) return fail(LSC_E_IO, std::string("lsc_index_save: short write to ") + path);
+    return LSC_OK;
+}
+
+int lsc_index_load(const char* path, int device, lsc_index** out) {
+    if (path == nullptr || out == nullptr) return fail(LSC_E_INVALID, "lsc_index_load: null argument");
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (f == nullptr) return fail(LSC_E_IO, std::string("lsc_index_load: cannot open ") + path);
+    char magic[8];
+    int32_t dim = 0;
+    int64_t n = 0;
+    bool ok = fread(magic, 1, 8, f) == 8 && memcmp(magic, "LSCIDX01", 8) == 0 && fread(&dim, sizeof(dim), 1, f) == 1 &&
+              fread(&n, sizeof(n), 1, f) == 1 && n >= 0 && dim > 0;
+    if (!ok) {
+        fclose(f);
+        return fail(LSC_E_IO, "lsc_index_load: not a langstream-cuda index file");
+    }
+    std::vector<int64_t> ids(static_cast<size_t>(n));
+    std::vector<__nv_bfloat16> rows(static_cast<size_t>(n) * dim);
+    if (n > 0)
+        ok = fread(ids.data(), sizeof(int64_t), ids.size(), f) == ids.size() &&
+             fread(rows.data(), sizeof(__nv_bfloat16), rows.size(), f) == rows.size();
+    fclose(f);
+    if (!ok) return fail(LSC_E_IO, "lsc_index_load: truncated index file");
+    lsc_index* ix = nullptr;
+    LSC_TRY(lsc_index_create(dim, n, device, &ix));
+    if (n > 0) {
+        cudaError_t e1 = cudaMemcpy(ix->d_rows, rows.data(), rows.size() * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice);
+        cudaError_t e2 = cudaMemcpy(ix->d_ids, ids.data(), ids.size() * sizeof(int64_t), cudaMemcpyHostToDevice);
+        if (e1 != cudaSuccess || e2 != cudaSuccess) {
+            lsc_index_destroy(ix);
+            return fail_cuda(e1 != cudaSuccess ? e1 : e2, "cudaMemcpy(index load)", __FILE__, __LINE__);
+        }
+        ix->ids = ids;
+        for (int64_t i = 0; i < n; ++i) ix->slot_of[ids[i]] = i;
+        ix->n = n;
+    }
+    *out = ix;
+    return LSC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,466 @@
+// Brute-force cosine top-k (K8/K9): the scan HerdDB runs for
+//   SELECT … ORDER BY cosine_similarity(col, CAST(? AS FLOAT ARRAY)) DESC LIMIT k
+// (reference call site AI/ai/langstream/ai/agents/datasource/impl/JdbcDataSourceProvider.java:103-124,
+//  SQL at examples/applications/docker-chatbot/chatbot.yaml:44), with the cosine defined as in
+// ReRankAgent.cosineSimilarity (AI/ai/langstream/ai/agents/rerank/ReRankAgent.java:262-273).
+// Rows are stored L2-normalised in bf16, so cosine = dot product.
+//
+// topk_scan_kernel — persistent, one CTA per SM, HBM-bound for small query batches:
+//   warp 0     TMA producer: the (<=128) queries once, then corpus tiles of 256 rows x 64 dims
+//              (SWIZZLE_128B, L2 evict-first) through a 4-stage smem ring
+//   warp 1     tcgen05.mma, M = 128 query rows (zero padded), N = 256 corpus rows, fp32 scores in
+//              TMEM, two accumulator stages
+//   warps 2-5  selection: thread q owns query q (TMEM lane q) and walks the 256 scores of the tile
+//              keeping its k best in a private sorted list; a chunk of 32 scores is skipped with one
+//              max-reduction when nothing beats the current k-th score
+// Each CTA then writes its [128][k] candidates to scratch and topk_merge_kernel merges the per-CTA
+// lists (a k-way merge over sorted heads) into the final [B][k] ids and scores.
+#include "common.h"
+#include "ptx.cuh"
+#include "topk.h"
+
+namespace lsc {
+
+namespace {
+
+constexpr int TK_THREADS = 192;
+constexpr int TK_BN = 256;
+constexpr int TK_BK = 64;
+constexpr int TK_ACC_STRIDE = 256;
+constexpr int TK_TMEM_COLS = 512;
+constexpr int TK_STAGE_BYTES = TK_BN * TK_BK * 2;  // 32 KB
+constexpr int TK_QBLK_BYTES = TK_QROWS * TK_BK * 2;  // 16 KB per 64-dim slice of the query block
+constexpr int TK_MAX_STAGES = 6;
+
+template <int KCAP>
+__device__ __noinline__ void list_insert(float* ls, int32_t* li, int& cnt, float& thr, int k, float s,
+                                         int32_t idx) {
+    int pos = cnt < k ? cnt : k - 1;
+    while (pos > 0 && ls[pos - 1] < s) {
+        ls[pos] = ls[pos - 1];
+        li[pos] = li[pos - 1];
+        --pos;
+    }
+    ls[pos] = s;
+    li[pos] = idx;
+    if (cnt < k) ++cnt;
+    thr = cnt == k ? ls[k - 1] : -INFINITY;
+}
+
+template <int KCAP>
+__global__ void __launch_bounds__(TK_THREADS, 1)
+topk_scan_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constant__ CUtensorMap tmapC,
+                 int q_row0, int nq, int n_rows, int dim, int k, int stages,
+                 float* __restrict__ cand_scores, int32_t* __restrict__ cand_idx) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    const int num_kb = dim / TK_BK;
+    const uint32_t sQ = smem_u32(smem);
+    const uint32_t sC = sQ + num_kb * TK_QBLK_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + num_kb * TK_QBLK_BYTES + stages * TK_STAGE_BYTES);
+    const uint32_t bar_full = smem_u32(bars);
+    const uint32_t bar_empty = bar_full + 8 * TK_MAX_STAGES;
+    const uint32_t bar_tfull = bar_empty + 8 * TK_MAX_STAGES;
+    const uint32_t bar_tempty = bar_tfull + 16;
+    const uint32_t bar_q = bar_tempty + 16;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(bars + 2 * TK_MAX_STAGES + 5);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmapQ);
+        tma_prefetch_desc(&tmapC);
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(bar_full + 8 * s, 1);
+            mbar_init(bar_empty + 8 * s, 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(bar_tfull + 8 * a, 1);
+            mbar_init(bar_tempty + 8 * a, 4);
+        }
+        mbar_init(bar_q, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), TK_TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int num_tiles = (n_rows + TK_BN - 1) / TK_BN;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            mbar_arrive_expect_tx(bar_q, num_kb * TK_QBLK_BYTES);
+            for (int kb = 0; kb < num_kb; ++kb)
+                tma_load_2d(sQ + kb * TK_QBLK_BYTES, &tmapQ, bar_q, kb * TK_BK, q_row0);
+            const uint64_t pol = policy_evict_first();
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    mbar_arrive_expect_tx(bar_full + 8 * stage, TK_STAGE_BYTES);
+                    tma_load_2d_hint(sC + stage * TK_STAGE_BYTES, &tmapC, bar_full + 8 * stage,
+                                     kb * TK_BK, tile * TK_BN, pol);
+                    if (++stage == stages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr uint32_t idesc = umma_idesc_bf16(TK_QROWS, TK_BN);
+            mbar_wait(bar_q, 0);
+            tc_fence_after();
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(bar_tempty + 8 * acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * TK_ACC_STRIDE;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(bar_full + 8 * stage, phase);
+                    tc_fence_after();
+                    const uint64_t da = umma_desc_sw128(sQ + kb * TK_QBLK_BYTES);
+                    const uint64_t db = umma_desc_sw128(sC + stage * TK_STAGE_BYTES);
+#pragma unroll
+                    for (int kk = 0; kk < TK_BK / 16; ++kk)
+                        umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
+                    umma_commit(bar_empty + 8 * stage);
+                    if (++stage == stages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(bar_tfull + 8 * acc);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+    } else {
+        const int quad = warp & 3;
+        const int q = quad * 32 + lane;        // query (TMEM lane) owned by this thread
+        const bool active = q < nq;
+        const bool warp_active = quad * 32 < nq;
+        float ls[KCAP];
+        int32_t li[KCAP];
+        int cnt = 0;
+        float thr = -INFINITY;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            mbar_wait(bar_tfull + 8 * acc, acc_phase);
+            tc_fence_after();
+            if (warp_active) {
+                const int row_base = tile * TK_BN;
+#pragma unroll 1
+                for (int c = 0; c < TK_BN / 32; ++c) {
+                    uint32_t v[32];
+                    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
+                                           acc * TK_ACC_STRIDE + c * 32;
+                    tmem_ld_32x32(taddr, v);
+                    tmem_ld_wait();
+                    const int r0 = row_base + c * 32;
+                    const int nvalid = n_rows - r0;  // rows past n_rows are not candidates
+                    if (active && nvalid > 0) {
+                        float mx = -INFINITY;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            mx = fmaxf(mx, j < nvalid ? __uint_as_float(v[j]) : -INFINITY);
+                        if (mx > thr) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const float s = __uint_as_float(v[j]);
+                                if (j < nvalid && s > thr)
+                                    list_insert<KCAP>(ls, li, cnt, thr, k, s, r0 + j);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            tc_fence_before();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+        if (active) {
+            const size_t base = (static_cast<size_t>(blockIdx.x) * TK_QROWS + q) * k;
+            for (int i = 0; i < k; ++i) {
+                cand_scores[base + i] = i < cnt ? ls[i] : -INFINITY;
+                cand_idx[base + i] = i < cnt ? li[i] : -1;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TK_TMEM_COLS);
+    }
+}
+
+// ---- k-way merge of sorted candidate lists -------------------------------------------------------
+// One CTA per query, thread p holds the head of part p's list.  Each round a block-wide argmax picks
+// the best head (score descending; ties by `tie` ascending), emits it and advances that list.
+struct Head {
+    float s;
+    long long tie;
+    int part;
+};
+__device__ __forceinline__ bool better(const Head& a, const Head& b) {
+    if (a.s != b.s) return a.s > b.s;
+    if (a.tie != b.tie) return a.tie < b.tie;
+    return a.part < b.part;
+}
+__device__ __forceinline__ Head shfl_head(const Head& h, int o) {
+    Head r;
+    r.s = __shfl_xor_sync(0xffffffffu, h.s, o);
+    r.tie = __shfl_xor_sync(0xffffffffu, h.tie, o);
+    r.part = __shfl_xor_sync(0xffffffffu, h.part, o);
+    return r;
+}
+
+// LAYOUT 0: scan scratch  [qblock][parts][128][k], idx = int32 storage slot, ids mapped through
+//           `slot_ids`; ties by slot.
+// LAYOUT 1: shard lists   [parts][B][k], idx = int64 id; ties by part (shards hold ascending
+//           contiguous row ranges) then by position.
+template <int LAYOUT>
+__global__ void __launch_bounds__(256)
+topk_merge_kernel(const float* __restrict__ sc, const void* __restrict__ ix, int parts, int B, int k,
+                  const int64_t* __restrict__ slot_ids, int64_t* __restrict__ out_ids,
+                  float* __restrict__ out_scores) {
+    __shared__ Head red[8];
+    __shared__ Head winner;
+    const int q = blockIdx.x;
+    const int p = threadIdx.x;
+    size_t base = 0;
+    if (p < parts) {
+        if (LAYOUT == 0)
+            base = ((static_cast<size_t>(q / TK_QROWS) * parts + p) * TK_QROWS + (q % TK_QROWS)) * k;
+        else
+            base = (static_cast<size_t>(p) * B + q) * k;
+    }
+    int pos = 0;
+    auto load_head = [&](int at) {
+        Head h;
+        h.part = p;
+        h.s = -INFINITY;
+        h.tie = 0x7fffffffffffffffLL;
+        if (p < parts && at < k) {
+            long long id;
+            if (LAYOUT == 0) id = static_cast<const int32_t*>(ix)[base + at];
+            else id = static_cast<const int64_t*>(ix)[base + at];
+            if (id >= 0) {
+                h.s = sc[base + at];
+                h.tie = LAYOUT == 0 ? id : static_cast<long long>(at);
+            }
+        }
+        return h;
+    };
+    Head mine = load_head(0);
+    for (int round = 0; round < k; ++round) {
+        Head best = mine;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const Head other = shfl_head(best, o);
+            if (better(other, best)) best = other;
+        }
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = best;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            Head b = red[0];
+            for (int w = 1; w < 8; ++w)
+                if (better(red[w], b)) b = red[w];
+            winner = b;
+        }
+        __syncthreads();
+        const Head w = winner;
+        if (w.s == -INFINITY && w.tie == 0x7fffffffffffffffLL) {
+            // every list exhausted: fewer than k rows exist
+            if (threadIdx.x == 0) {
+                for (int r = round; r < k; ++r) {
+                    out_ids[static_cast<size_t>(q) * k + r] = -1;
+                    out_scores[static_cast<size_t>(q) * k + r] = -INFINITY;
+                }
+            }
+            return;
+        }
+        if (p == w.part) {
+            long long id;
+            if (LAYOUT == 0) {
+                const int32_t slot = static_cast<const int32_t*>(ix)[base + pos];
+                id = slot_ids != nullptr ? slot_ids[slot] : slot;
+            } else {
+                id = static_cast<const int64_t*>(ix)[base + pos];
+            }
+            out_ids[static_cast<size_t>(q) * k + round] = id;
+            out_scores[static_cast<size_t>(q) * k + round] = w.s;
+            ++pos;
+            mine = load_head(pos);
+        }
+        // `winner`/`red` are rewritten only after the next round's first __syncthreads
+    }
+}
+
+// ---- small row kernels -----------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// fp32 rows -> L2-normalised bf16 rows at dst_rows[i] (or row i when dst_rows == nullptr);
+// rows in [n, n_pad) are written as zeros (query padding).  A zero vector stays zero.
+__global__ void __launch_bounds__(256)
+normalize_rows_kernel(const float* __restrict__ src, int n, int n_pad, int dim,
+                      const int64_t* __restrict__ dst_rows, __nv_bfloat16* __restrict__ dst) {
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (r >= n_pad) return;
+    long long out_row = r;
+    if (dst_rows != nullptr) {
+        if (r >= n) return;
+        out_row = dst_rows[r];
+        if (out_row < 0) return;  // superseded duplicate inside one upsert batch
+    }
+    __nv_bfloat16* o = dst + static_cast<size_t>(out_row) * dim;
+    if (r >= n) {
+        for (int c = lane * 2; c < dim; c += 64) *reinterpret_cast<uint32_t*>(o + c) = 0u;
+        return;
+    }
+    const float* s = src + static_cast<size_t>(r) * dim;
+    float q = 0.f;
+    for (int c = lane * 2; c < dim; c += 64) {
+        const float2 v = *reinterpret_cast<const float2*>(s + c);
+        q += v.x * v.x + v.y * v.y;
+    }
+    const float norm = sqrtf(warp_sum(q));
+    const float inv = norm > 0.f ? 1.0f / norm : 0.f;
+    for (int c = lane * 2; c < dim; c += 64) {
+        const float2 v = *reinterpret_cast<const float2*>(s + c);
+        *reinterpret_cast<uint32_t*>(o + c) = pack_bf16x2(v.x * inv, v.y * inv);
+    }
+}
+
+// Debug / verification: exact fp32 dot products of every stored row with every (bf16) query.
+__global__ void __launch_bounds__(256)
+scores_naive_kernel(const __nv_bfloat16* __restrict__ rows, long long n, int dim,
+                    const __nv_bfloat16* __restrict__ q, int B, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const long long r = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (r >= n) return;
+    const uint32_t* rp = reinterpret_cast<const uint32_t*>(rows + static_cast<size_t>(r) * dim);
+    for (int b = 0; b < B; ++b) {
+        const uint32_t* qp = reinterpret_cast<const uint32_t*>(q + static_cast<size_t>(b) * dim);
+        float a = 0.f;
+        for (int c = lane; c < dim / 2; c += 32) {
+            const uint32_t x = __ldg(rp + c), y = __ldg(qp + c);
+            a = fmaf(bf16_lo(x), bf16_lo(y), a);
+            a = fmaf(bf16_hi(x), bf16_hi(y), a);
+        }
+        a = warp_sum(a);
+        if (lane == 0) out[static_cast<size_t>(b) * n + r] = a;
+    }
+}
+
+__global__ void fill_empty_kernel(int64_t* ids, float* scores, size_t n) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) {
+        ids[i] = -1;
+        scores[i] = -INFINITY;
+    }
+}
+
+template <int KCAP>
+int scan_inst(const CUtensorMap& tmapQ, const CUtensorMap& tmapC, int q_row0, int nq, int n_rows,
+              int dim, int k, int stages, size_t smem, int grid, float* cand_scores, int32_t* cand_idx,
+              cudaStream_t stream) {
+    auto kern = topk_scan_kernel<KCAP>;
+    LSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    kern<<<grid, TK_THREADS, smem, stream>>>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, cand_scores,
+                                             cand_idx);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+}  // namespace
+
+int topk_scan_grid(int n_rows, int num_sms) {
+    const int tiles = (n_rows + TK_BN - 1) / TK_BN;
+    return tiles < num_sms ? tiles : num_sms;
+}
+
+int topk_scan_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC, int q_row0, int nq, int n_rows,
+                     int dim, int k, int grid, float* cand_scores, int32_t* cand_idx,
+                     cudaStream_t stream) {
+    if (dim % TK_BK != 0 || dim <= 0 || dim > 512)
+        return fail(LSC_E_UNSUPPORTED, "top-k: dim must be a multiple of 64 and <= 512");
+    if (k < 1 || k > TK_KMAX) return fail(LSC_E_INVALID, "top-k: k must be in [1,128]");
+    const int q_bytes = (dim / TK_BK) * TK_QBLK_BYTES;
+    int stages = (227 * 1024 - 1024 - 256 - q_bytes) / TK_STAGE_BYTES;
+    if (stages > TK_MAX_STAGES) stages = TK_MAX_STAGES;
+    if (stages < 2) return fail(LSC_E_UNSUPPORTED, "top-k: dim too large for the shared-memory ring");
+    const size_t smem = static_cast<size_t>(q_bytes) + static_cast<size_t>(stages) * TK_STAGE_BYTES + 256 + 1024;
+    if (k <= 16) return scan_inst<16>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+    if (k <= 32) return scan_inst<32>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+    return scan_inst<128>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+}
+
+int topk_merge_scan_launch(const float* cand_scores, const int32_t* cand_idx, int parts, int B, int k,
+                           const int64_t* slot_ids, int64_t* out_ids, float* out_scores,
+                           cudaStream_t stream) {
+    if (B <= 0) return 0;
+    if (parts > 256) return fail(LSC_E_UNSUPPORTED, "top-k merge: more than 256 partial lists");
+    topk_merge_kernel<0><<<B, 256, 0, stream>>>(cand_scores, cand_idx, parts, B, k, slot_ids, out_ids, out_scores);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+int topk_merge_shards_launch(const float* scores, const int64_t* ids, int parts, int B, int k,
+                             int64_t* out_ids, float* out_scores, cudaStream_t stream) {
+    if (B <= 0) return 0;
+    if (parts > 256) return fail(LSC_E_UNSUPPORTED, "top-k merge: more than 256 partial lists");
+    topk_merge_kernel<1><<<B, 256, 0, stream>>>(scores, ids, parts, B, k, nullptr, out_ids, out_scores);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+int normalize_rows_launch(const float* src, int n, int n_pad, int dim, const int64_t* dst_rows,
+                          __nv_bfloat16* dst, cudaStream_t stream) {
+    if (n_pad <= 0) return 0;
+    const int wpb = 8;
+    normalize_rows_kernel<<<(n_pad + wpb - 1) / wpb, 256, 0, stream>>>(src, n, n_pad, dim, dst_rows, dst);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+int scores_naive_launch(const __nv_bfloat16* rows, int64_t n, int dim, const __nv_bfloat16* q, int B,
+                        float* out, cudaStream_t stream) {
+    if (n <= 0 || B <= 0) return 0;
+    const int wpb = 8;
+    const int64_t grid = (n + wpb - 1) / wpb;
+    scores_naive_kernel<<<static_cast<unsigned>(grid), 256, 0, stream>>>(rows, n, dim, q, B, out);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+int fill_empty_launch(int64_t* ids, float* scores, size_t n, cudaStream_t stream) {
+    if (n == 0) return 0;
+    fill_empty_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(ids, scores, n);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+}  // namespace lsc

@@ -1,0 +1,37 @@
+// Launchers of the top-k kernels (topk.cu), used by the index host code (index.cu).
+#pragma once
+#include "common.h"
+
+namespace lsc {
+
+constexpr int TK_QROWS = 128;  // queries per scan pass (UMMA M)
+constexpr int TK_KMAX = 128;   // largest supported k
+
+// Number of CTAs the scan uses for n_rows rows on a device with num_sms SMs.
+int topk_scan_grid(int n_rows, int num_sms);
+
+// Scan all rows for the query block [q_row0, q_row0 + nq) of the bf16 query matrix behind tmapQ.
+// Scratch written: cand_scores / cand_idx [grid][128][k] (only rows q < nq).
+int topk_scan_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC, int q_row0, int nq, int n_rows,
+                     int dim, int k, int grid, float* cand_scores, int32_t* cand_idx,
+                     cudaStream_t stream);
+
+// Merge the scan scratch [qblocks][parts][128][k] into [B][k]; slots are mapped through slot_ids.
+int topk_merge_scan_launch(const float* cand_scores, const int32_t* cand_idx, int parts, int B, int k,
+                           const int64_t* slot_ids, int64_t* out_ids, float* out_scores,
+                           cudaStream_t stream);
+
+// Merge shard lists [parts][B][k] (int64 ids) into [B][k].
+int topk_merge_shards_launch(const float* scores, const int64_t* ids, int parts, int B, int k,
+                             int64_t* out_ids, float* out_scores, cudaStream_t stream);
+
+// fp32 rows -> L2-normalised bf16 rows (see topk.cu).
+int normalize_rows_launch(const float* src, int n, int n_pad, int dim, const int64_t* dst_rows,
+                          __nv_bfloat16* dst, cudaStream_t stream);
+
+int scores_naive_launch(const __nv_bfloat16* rows, int64_t n, int dim, const __nv_bfloat16* q, int B,
+                        float* out, cudaStream_t stream);
+
+int fill_empty_launch(int64_t* ids, float* scores, size_t n, cudaStream_t stream);
+
+}  // namespace lsc

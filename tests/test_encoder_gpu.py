@@ -1,0 +1,151 @@
+"""Encoder forward through the C ABI against the fp32 CPU oracle.
+Tolerance (BASELINE.json north_star): per-vector cosine >= 0.999 and max-abs error <= 2e-3."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+GOLDEN = Path(__file__).parent / "golden"
+COS_MIN = 0.999
+MAX_ABS = 2e-3
+
+
+def _check(got, want):
+    assert got.shape == want.shape
+    assert np.isfinite(got).all()
+    for i in range(want.shape[0]):
+        nw = np.linalg.norm(want[i])
+        if nw == 0:
+            assert np.abs(got[i]).max() == 0
+            continue
+        cos = float(got[i] @ want[i] / (np.linalg.norm(got[i]) * nw))
+        assert cos >= COS_MIN, f"row {i}: cosine {cos}"
+        assert abs(np.linalg.norm(got[i]) - 1.0) < 1e-3
+    assert np.abs(got - want).max() <= MAX_ABS, f"max-abs {np.abs(got - want).max()}"
+
+
+@pytest.mark.parametrize("gemm_impl", [1, 0])
+def test_tiny_golden(native_lib, cuda_device, gemm_impl):
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+
+    fx = np.load(GOLDEN / "encoder_tiny.npz")
+    blob = W.random_init(W.TINY, seed=int(fx["seed"]), perturb=bool(fx["perturb"]))
+    enc = Encoder(W.TINY, blob, gemm_impl=gemm_impl)
+    got = enc.embed(fx["token_ids"], fx["cu_seqlens"])
+    _check(got, fx["expected"])
+    enc.close()
+
+
+@pytest.mark.parametrize("gemm_impl", [1, 0])
+def test_minilm_golden(native_lib, cuda_device, gemm_impl):
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+
+    fx = np.load(GOLDEN / "encoder_minilm.npz")
+    blob = W.random_init(W.MINILM_L6, seed=int(fx["seed"]), perturb=bool(fx["perturb"]))
+    enc = Encoder(W.MINILM_L6, blob, gemm_impl=gemm_impl)
+    got = enc.embed(fx["token_ids"], fx["cu_seqlens"])
+    _check(got, fx["expected"])
+    enc.close()
+
+
+def test_minilm_config1_live_oracle(native_lib, cuda_device):
+    """BASELINE config 1 shape: 32 x 128 tokens, perturbed weights, live HuggingFace oracle run one
+    text per forward like the reference."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+    from oracle.encoder_oracle import HFOracle
+
+    spec = W.MINILM_L6
+    blob = W.random_init(spec, seed=3, perturb=True)
+    ids, cu = W.synthetic_token_ids(32, 128, seed=1234)
+    want = HFOracle(spec, blob).embed_one_by_one(ids, cu)
+    enc = Encoder(spec, blob)
+    got = enc.embed(ids, cu)
+    _check(got, want)
+    enc.close()
+
+
+def test_minilm_ragged_and_batch_invariance(native_lib, cuda_device):
+    """Packed variable-length batch: each sequence's embedding does not depend on its neighbours
+    (the reference embeds texts independently), checked against the oracle on a subset."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+    from oracle.encoder_oracle import HFOracle
+
+    spec = W.MINILM_L6
+    blob = W.random_init(spec, seed=5, perturb=True)
+    ids, cu = W.synthetic_token_ids(300, 128, seed=77, min_len=1)
+    enc = Encoder(spec, blob)
+    all_out = enc.embed(ids, cu)
+    pick = [0, 1, 17, 150, 299]
+    sub_ids = np.concatenate([ids[cu[i]:cu[i + 1]] for i in pick])
+    sub_cu = np.concatenate([[0], np.cumsum([cu[i + 1] - cu[i] for i in pick])]).astype(np.int32)
+    sub_out = enc.embed(sub_ids, sub_cu)
+    assert np.abs(sub_out - all_out[pick]).max() <= 1e-6  # same kernels, same per-sequence math
+    want = HFOracle(spec, blob).embed_one_by_one(sub_ids, sub_cu)
+    _check(sub_out, want)
+    enc.close()
+
+
+def test_base_shape_subset(native_lib, cuda_device):
+    """12L/768-d (BGE-base shape), 512-token and ragged sequences, oracle on 6 sequences."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+    from oracle.encoder_oracle import HFOracle
+
+    spec = W.BERT_BASE
+    blob = W.random_init(spec, seed=1, perturb=True)
+    ids_a, cu_a = W.synthetic_token_ids(2, 512, seed=1)
+    ids_b, cu_b = W.synthetic_token_ids(4, 512, seed=2, min_len=64)
+    ids = np.concatenate([ids_a, ids_b])
+    cu = np.concatenate([cu_a, cu_a[-1] + cu_b[1:]]).astype(np.int32)
+    want = HFOracle(spec, blob).embed_batched(ids, cu, batch=2)
+    enc = Encoder(spec, blob)
+    got = enc.embed(ids, cu)
+    _check(got, want)
+    enc.close()
+
+
+def test_edge_cases(native_lib, cuda_device):
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder, NativeError, LSC_E_TOO_LONG
+
+    spec = W.TINY
+    enc = Encoder(spec, W.random_init(spec, 0, True))
+    # empty batch, and a batch of empty sequences
+    assert enc.embed(np.zeros(0, np.int32), np.zeros(1, np.int32)).shape == (0, spec.hidden)
+    out = enc.embed(np.zeros(0, np.int32), np.zeros(4, np.int32))
+    assert out.shape == (3, spec.hidden) and (out == 0).all()
+    # maximum length is accepted, one more token is the reference's "too many tokens" error
+    ids, cu = W.synthetic_token_ids(1, spec.max_position, vocab=spec.vocab)
+    assert np.isfinite(enc.embed(ids, cu)).all()
+    ids, cu = W.synthetic_token_ids(1, spec.max_position + 1, vocab=spec.vocab)
+    with pytest.raises(NativeError) as ei:
+        enc.embed(ids, cu)
+    assert ei.value.code == LSC_E_TOO_LONG and "number of tokens is too high" in ei.value.message
+    with pytest.raises(NativeError):
+        enc.embed(np.array([spec.vocab], np.int32), np.array([0, 1], np.int32))  # id out of range
+    enc.close()
+
+
+def test_device_api_matches_host_api(native_lib, cuda_device):
+    import torch
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+
+    spec = W.MINILM_L6
+    enc = Encoder(spec, W.random_init(spec, 0))
+    ids, cu = W.synthetic_token_ids(64, 128, seed=4, min_len=16)
+    host = enc.embed(ids, cu)
+    d_ids = torch.from_numpy(ids).to(cuda_device)
+    d_cu = torch.from_numpy(cu).to(cuda_device)
+    d_out = torch.empty(64, spec.hidden, device=cuda_device)
+    enc.embed_dev(d_ids, d_cu, 64, int(cu[-1]), int(np.diff(cu).max()), d_out,
+                  torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy(), host)
+    assert enc.launch_count > 0
+    enc.close()
