@@ -121,6 +121,16 @@ int lsc_encoder_embed_dev(lsc_encoder* enc, const int32_t* d_token_ids, const in
                           int32_t n_seq, int32_t total_tokens, int32_t max_seqlen, float* d_out,
                           void* stream);
 
+/*
+ * Measurement aid (no reference counterpart): when enabled, every kernel launch of this handle is
+ * bracketed by CUDA events on its stream.  lsc_encoder_read_profile waits for them and returns the
+ * milliseconds and launch counts accumulated since the previous read, per kernel class:
+ * 0 embedding gather+LayerNorm, 1 GEMM, 2 attention, 3 LayerNorm, 4 mean-pool+L2.
+ */
+int lsc_encoder_set_profiling(lsc_encoder* enc, int enabled);
+int lsc_encoder_read_profile(lsc_encoder* enc, float* ms_by_class, int64_t* launches_by_class,
+                             int32_t nclass);
+
 /* Hidden size of the loaded model (the embedding dimension). */
 int lsc_encoder_dim(const lsc_encoder* enc);
 /* Number of kernels this handle has launched since creation (bench accounting). */
@@ -198,6 +208,12 @@ int lsc_index_scores_naive_dev(lsc_index* idx, const float* d_queries, int32_t B
  */
 int lsc_topk_merge_dev(const int64_t* d_ids, const float* d_scores, int32_t parts, int32_t B,
                        int32_t k, int64_t* d_out_ids, float* d_out_scores, void* stream);
+
+/* Same measurement aid as lsc_encoder_set_profiling; classes: 0 normalise (queries / upserted rows),
+ * 1 scan, 2 merge. */
+int lsc_index_set_profiling(lsc_index* idx, int enabled);
+int lsc_index_read_profile(lsc_index* idx, float* ms_by_class, int64_t* launches_by_class,
+                           int32_t nclass);
 
 /* Number of kernels this handle has launched since creation. */
 int64_t lsc_index_launch_count(const lsc_index* idx);

@@ -56,6 +56,8 @@ SIGNATURES = {
     "lsc_encoder_create": (C.c_int, [C.POINTER(EncoderConfig), _vp, C.c_size_t, C.c_int, C.POINTER(_vp)]),
     "lsc_encoder_embed": (C.c_int, [_vp, _vp, _vp, _i32, _vp]),
     "lsc_encoder_embed_dev": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
+    "lsc_encoder_set_profiling": (C.c_int, [_vp, C.c_int]),
+    "lsc_encoder_read_profile": (C.c_int, [_vp, _vp, _vp, _i32]),
     "lsc_encoder_dim": (C.c_int, [_vp]),
     "lsc_encoder_launch_count": (_i64, [_vp]),
     "lsc_encoder_destroy": (None, [_vp]),
@@ -68,6 +70,8 @@ SIGNATURES = {
     "lsc_index_search_dev": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "lsc_index_scores_naive_dev": (C.c_int, [_vp, _vp, _i32, _vp, _vp]),
     "lsc_topk_merge_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "lsc_index_set_profiling": (C.c_int, [_vp, C.c_int]),
+    "lsc_index_read_profile": (C.c_int, [_vp, _vp, _vp, _i32]),
     "lsc_index_launch_count": (_i64, [_vp]),
     "lsc_index_save": (C.c_int, [_vp, C.c_char_p]),
     "lsc_index_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(_vp)]),
@@ -160,6 +164,19 @@ class Encoder:
     def launch_count(self) -> int:
         return int(lib().lsc_encoder_launch_count(self._h))
 
+    PROFILE_CLASSES = ("embed_ln", "gemm", "attention", "layernorm", "pool_l2")
+
+    def set_profiling(self, enabled: bool):
+        check(lib().lsc_encoder_set_profiling(self._h, int(enabled)))
+
+    def read_profile(self):
+        """{class: (milliseconds, launches)} accumulated since the previous read."""
+        n = len(self.PROFILE_CLASSES)
+        ms = _np.zeros(n, _np.float32)
+        cnt = _np.zeros(n, _np.int64)
+        check(lib().lsc_encoder_read_profile(self._h, _ptr(ms), _ptr(cnt), n))
+        return {c: (float(ms[i]), int(cnt[i])) for i, c in enumerate(self.PROFILE_CLASSES)}
+
     def close(self):
         if self._h:
             lib().lsc_encoder_destroy(self._h)
@@ -229,6 +246,18 @@ class Index:
     @property
     def launch_count(self) -> int:
         return int(lib().lsc_index_launch_count(self._h))
+
+    PROFILE_CLASSES = ("normalize", "scan", "merge")
+
+    def set_profiling(self, enabled: bool):
+        check(lib().lsc_index_set_profiling(self._h, int(enabled)))
+
+    def read_profile(self):
+        n = len(self.PROFILE_CLASSES)
+        ms = _np.zeros(n, _np.float32)
+        cnt = _np.zeros(n, _np.int64)
+        check(lib().lsc_index_read_profile(self._h, _ptr(ms), _ptr(cnt), n))
+        return {c: (float(ms[i]), int(cnt[i])) for i, c in enumerate(self.PROFILE_CLASSES)}
 
     def close(self):
         if self._h:

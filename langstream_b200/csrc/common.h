@@ -9,6 +9,7 @@
 #include <stddef.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/langstream_cuda.h"
 
@@ -30,6 +31,51 @@ int fail_cuda(cudaError_t e, const char* what, const char* file, int line);
         int _rc = (expr);         \
         if (_rc != LSC_OK) return _rc; \
     } while (0)
+
+// ---- optional per-kernel-class timing (CUDA events on the launching stream) -------------------
+// Used by bench.py to attribute the step time to kernels; off by default (zero cost).
+struct Profiler {
+    static constexpr int kMaxClasses = 8;
+    bool enabled = false;
+    struct Rec { cudaEvent_t a, b; int cls; };
+    std::vector<Rec> recs;
+    std::vector<cudaEvent_t> pool;
+    cudaEvent_t get() {
+        if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+        cudaEvent_t e = nullptr;
+        cudaEventCreate(&e);
+        return e;
+    }
+    void begin(int cls, cudaStream_t st) {
+        if (!enabled) return;
+        Rec r{get(), get(), cls};
+        cudaEventRecord(r.a, st);
+        recs.push_back(r);
+    }
+    void end(cudaStream_t st) {
+        if (!enabled || recs.empty()) return;
+        cudaEventRecord(recs.back().b, st);
+    }
+    // Accumulated milliseconds and launch counts per class since the last read; waits for the events.
+    int read(float* ms, int64_t* counts, int nclass) {
+        for (int i = 0; i < nclass; ++i) { ms[i] = 0.f; counts[i] = 0; }
+        for (auto& r : recs) {
+            cudaError_t e = cudaEventSynchronize(r.b);
+            if (e != cudaSuccess) return fail_cuda(e, "cudaEventSynchronize", __FILE__, __LINE__);
+            float t = 0.f;
+            cudaEventElapsedTime(&t, r.a, r.b);
+            if (r.cls >= 0 && r.cls < nclass) { ms[r.cls] += t; counts[r.cls] += 1; }
+            pool.push_back(r.a);
+            pool.push_back(r.b);
+        }
+        recs.clear();
+        return LSC_OK;
+    }
+    ~Profiler() {
+        for (auto& r : recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+        for (auto e : pool) cudaEventDestroy(e);
+    }
+};
 
 // ---- TMA tensor maps -----------------------------------------------------------------------
 // 2-D bf16 row-major tensor [rows, cols] (cols contiguous), box = [box_rows, 64 cols] with

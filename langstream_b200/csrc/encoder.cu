@@ -59,6 +59,7 @@ struct lsc_encoder {
     int32_t* d_cu = nullptr;
     float* d_out = nullptr;
     std::atomic<int64_t> launches{0};
+    Profiler prof;  // classes: 0 embed+LN, 1 GEMM, 2 attention, 3 LayerNorm, 4 pool
 };
 
 namespace lsc {
@@ -168,9 +169,11 @@ int gemm(lsc_encoder* e, const CUtensorMap& tmA, const __nv_bfloat16* A, const C
     return gemm_tc_launch(tmA, tmW, bias, residual, C, M, N, K, epi, e->num_sms, st);
 }
 
-#define LSC_LAUNCH(expr)              \
+#define LSC_LAUNCH(cls, expr)         \
     do {                              \
+        e->prof.begin(cls, st);       \
         int _n = (expr);              \
+        e->prof.end(st);              \
         if (_n < 0) return _n;        \
         nlaunch += _n;                \
     } while (0)
@@ -190,20 +193,20 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
             LSC_TRY(make_tmap_bf16_sw128(&tm_ctx, e->ctx, T, H, 128));
             LSC_TRY(make_tmap_bf16_sw128(&tm_ffn, e->ffn, T, F, 128));
         }
-        LSC_LAUNCH(embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word,
+        LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word,
                                    e->d_pos, e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, st));
         for (int l = 0; l < c.layers; ++l) {
             const LayerW& w = e->layers[l];
-            LSC_LAUNCH(gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.b_qkv, nullptr, e->qkv, T, 3 * H, H, EPI_BIAS, st));
-            LSC_LAUNCH(attention_launch(e->qkv, d_cu, n_seq, H, c.heads, max_seqlen, e->ctx, st));
-            LSC_LAUNCH(gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, st));
-            LSC_LAUNCH(layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
-            LSC_LAUNCH(gemm(e, tm_x1, e->x1, w.tm_1, w.w_1, w.b_1, nullptr, e->ffn, T, F, H, EPI_BIAS_GELU, st));
-            LSC_LAUNCH(gemm(e, tm_ffn, e->ffn, w.tm_2, w.w_2, w.b_2, e->x1, e->tmp, T, H, F, EPI_BIAS_RESIDUAL, st));
-            LSC_LAUNCH(layernorm_launch(e->tmp, w.ln2_g, w.ln2_b, c.ln_eps, e->x, T, H, st));
+            LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.b_qkv, nullptr, e->qkv, T, 3 * H, H, EPI_BIAS, st));
+            LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, H, c.heads, max_seqlen, e->ctx, st));
+            LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, st));
+            LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
+            LSC_LAUNCH(1, gemm(e, tm_x1, e->x1, w.tm_1, w.w_1, w.b_1, nullptr, e->ffn, T, F, H, EPI_BIAS_GELU, st));
+            LSC_LAUNCH(1, gemm(e, tm_ffn, e->ffn, w.tm_2, w.w_2, w.b_2, e->x1, e->tmp, T, H, F, EPI_BIAS_RESIDUAL, st));
+            LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln2_g, w.ln2_b, c.ln_eps, e->x, T, H, st));
         }
     }
-    LSC_LAUNCH(pool_l2_launch(e->x, d_cu, n_seq, H, d_out, st));
+    LSC_LAUNCH(4, pool_l2_launch(e->x, d_cu, n_seq, H, d_out, st));
     e->launches += nlaunch;
     return LSC_OK;
 }
@@ -325,6 +328,21 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
     }
     *out = e;
     return LSC_OK;
+}
+
+int lsc_encoder_set_profiling(lsc_encoder* e, int enabled) {
+    if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_set_profiling: encoder is null");
+    std::lock_guard<std::mutex> lock(e->mu);
+    e->prof.enabled = enabled != 0;
+    return LSC_OK;
+}
+
+int lsc_encoder_read_profile(lsc_encoder* e, float* ms_by_class, int64_t* launches_by_class, int32_t nclass) {
+    if (e == nullptr || ms_by_class == nullptr || launches_by_class == nullptr || nclass < 1 || nclass > Profiler::kMaxClasses)
+        return fail(LSC_E_INVALID, "lsc_encoder_read_profile: bad argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    LSC_CUDA(cudaSetDevice(e->device));
+    return e->prof.read(ms_by_class, launches_by_class, nclass);
 }
 
 int lsc_encoder_dim(const lsc_encoder* e) { return e ? e->cfg.hidden : LSC_E_INVALID; }

@@ -47,6 +47,7 @@ struct lsc_index {
     cudaStream_t stream = nullptr;
     std::mutex mu;
     std::atomic<int64_t> launches{0};
+    Profiler prof;  // classes: 0 normalise rows/queries, 1 scan, 2 merge
 };
 
 namespace lsc {
@@ -112,9 +113,11 @@ int ensure_query_buffers(lsc_index* ix, int B, int k) {
     return LSC_OK;
 }
 
-#define LSC_LAUNCH(expr)              \
+#define LSC_LAUNCH(cls, expr)         \
     do {                              \
+        ix->prof.begin(cls, st);      \
         int _n = (expr);              \
+        ix->prof.end(st);             \
         if (_n < 0) return _n;        \
         nlaunch += _n;                \
     } while (0)
@@ -124,22 +127,22 @@ int search_dev(lsc_index* ix, const float* d_queries, int B, int k, int64_t* d_o
                cudaStream_t st) {
     int64_t nlaunch = 0;
     if (ix->n == 0) {
-        LSC_LAUNCH(fill_empty_launch(d_out_ids, d_out_scores, static_cast<size_t>(B) * k, st));
+        LSC_LAUNCH(2, fill_empty_launch(d_out_ids, d_out_scores, static_cast<size_t>(B) * k, st));
         ix->launches += nlaunch;
         return LSC_OK;
     }
     LSC_TRY(ensure_query_buffers(ix, B, k));
     const int bpad = (B + TK_QROWS - 1) / TK_QROWS * TK_QROWS;
-    LSC_LAUNCH(normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st));
+    LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st));
     const int n_rows = static_cast<int>(ix->n);
     const int grid = topk_scan_grid(n_rows, ix->num_sms);
     for (int qb = 0; qb * TK_QROWS < B; ++qb) {
         const int nq = std::min(TK_QROWS, B - qb * TK_QROWS);
         const size_t off = static_cast<size_t>(qb) * grid * TK_QROWS * k;
-        LSC_LAUNCH(topk_scan_launch(ix->tmapQ, ix->tmapC, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
+        LSC_LAUNCH(1, topk_scan_launch(ix->tmapQ, ix->tmapC, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
                                     ix->d_cand_scores + off, ix->d_cand_idx + off, st));
     }
-    LSC_LAUNCH(topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, d_out_ids,
+    LSC_LAUNCH(2, topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, d_out_ids,
                                       d_out_scores, st));
     ix->launches += nlaunch;
     return LSC_OK;
@@ -173,7 +176,7 @@ int upsert_dev(lsc_index* ix, const int64_t* ids, const float* d_vecs, int n, cu
     if (!new_ids.empty())
         LSC_CUDA(cudaMemcpyAsync(ix->d_ids + ix->n, new_ids.data(), new_ids.size() * sizeof(int64_t), cudaMemcpyHostToDevice, st));
     int64_t nlaunch = 0;
-    LSC_LAUNCH(normalize_rows_launch(d_vecs, n, n, ix->dim, ix->d_slots, ix->d_rows, st));
+    LSC_LAUNCH(0, normalize_rows_launch(d_vecs, n, n, ix->dim, ix->d_slots, ix->d_rows, st));
     LSC_CUDA(cudaStreamSynchronize(st));  // host vectors `slots` / `new_ids` go out of scope
     for (int64_t id : new_ids) {
         ix->slot_of[id] = static_cast<int64_t>(ix->ids.size());
@@ -231,6 +234,21 @@ int lsc_index_create(int32_t dim, int64_t capacity, int device, lsc_index** out)
     }
     *out = ix;
     return LSC_OK;
+}
+
+int lsc_index_set_profiling(lsc_index* ix, int enabled) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_set_profiling: index is null");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    ix->prof.enabled = enabled != 0;
+    return LSC_OK;
+}
+
+int lsc_index_read_profile(lsc_index* ix, float* ms_by_class, int64_t* launches_by_class, int32_t nclass) {
+    if (ix == nullptr || ms_by_class == nullptr || launches_by_class == nullptr || nclass < 1 || nclass > Profiler::kMaxClasses)
+        return fail(LSC_E_INVALID, "lsc_index_read_profile: bad argument");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    return ix->prof.read(ms_by_class, launches_by_class, nclass);
 }
 
 int64_t lsc_index_size(const lsc_index* ix) { return ix ? ix->n : 0; }
