@@ -209,6 +209,28 @@ int lsc_index_scores_naive_dev(lsc_index* idx, const float* d_queries, int32_t B
 int lsc_topk_merge_dev(const int64_t* d_ids, const float* d_scores, int32_t parts, int32_t B,
                        int32_t k, int64_t* d_out_ids, float* d_out_scores, void* stream);
 
+/*
+ * Top-k search that allocates nothing (no counterpart in the reference: it exists for the way this
+ * library is deployed, not for anything LangStream's Java does).
+ * Meant for callers that cannot let the library call cudaMalloc at query time: agents sharing the GPU
+ * with a framework that reserved nearly all of HBM at start-up (a late allocation would fail), and
+ * latency-bound query threads (cudaMalloc / cudaFree synchronise the whole device).
+ * The caller passes everything as device pointers: `d_rows_bf16` = n_rows x dim L2-normalised bf16
+ * rows (16-byte aligned, e.g. produced once at load time), `d_row_ids` = n_rows int64 ids or NULL to
+ * get row numbers back, `d_queries` = B x dim fp32, outputs B x k.  Same kernels, ordering and scores
+ * as lsc_index_search_dev; the scratch they need lives in a fixed ~5.4 MB array inside the library
+ * (held by every GPU that loads the library until the process exits), hence the limits
+ * B <= 128, k <= 32, dim a multiple of 64 and <= 512; anything larger is rejected with
+ * LSC_E_UNSUPPORTED.  The first call on a device resolves the array's address and configures the
+ * kernels: make it at start-up, before any stream capture on that device.  All calls share the array
+ * (it keeps the last call's contents; nothing needs to be zeroed between calls), so calls whose GPU
+ * work overlaps — different streams or threads — race: keep them on one stream.  Enqueues on `stream`
+ * and returns without synchronising.
+ */
+int lsc_topk_search_static_dev(const void* d_rows_bf16, const int64_t* d_row_ids, int64_t n_rows,
+                               int32_t dim, const float* d_queries, int32_t B, int32_t k,
+                               int64_t* d_out_ids, float* d_out_scores, void* stream);
+
 /* Same measurement aid as lsc_encoder_set_profiling; classes: 0 normalise (queries / upserted rows),
  * 1 scan, 2 merge. */
 int lsc_index_set_profiling(lsc_index* idx, int enabled);

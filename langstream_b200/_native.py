@@ -70,6 +70,7 @@ SIGNATURES = {
     "lsc_index_search_dev": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "lsc_index_scores_naive_dev": (C.c_int, [_vp, _vp, _i32, _vp, _vp]),
     "lsc_topk_merge_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "lsc_topk_search_static_dev": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _i32, _i32, _vp, _vp, _vp]),
     "lsc_index_set_profiling": (C.c_int, [_vp, C.c_int]),
     "lsc_index_read_profile": (C.c_int, [_vp, _vp, _vp, _i32]),
     "lsc_index_launch_count": (_i64, [_vp]),
@@ -273,6 +274,16 @@ class Index:
 
 def topk_merge_dev(d_ids, d_scores, parts, B, k, d_out_ids, d_out_scores, stream=0):
     check(lib().lsc_topk_merge_dev(_ptr(d_ids), _ptr(d_scores), parts, B, k, _ptr(d_out_ids), _ptr(d_out_scores), stream))
+
+
+def topk_search_static_dev(d_rows_bf16, d_row_ids, n_rows, dim, d_queries, B, k, d_out_ids, d_out_scores, stream=0):
+    """Top-k for callers that must not trigger a device allocation (GPU memory fully reserved by a
+    co-tenant framework, or a latency budget that rules out cudaMalloc's device-wide sync): scratch
+    comes from a fixed array inside the library.  B <= 128, k <= 32, dim <= 512; one call at a time
+    per GPU (calls share the scratch)."""
+    check(lib().lsc_topk_search_static_dev(_ptr(d_rows_bf16), _ptr(d_row_ids), int(n_rows), int(dim),
+                                           _ptr(d_queries), int(B), int(k), _ptr(d_out_ids),
+                                           _ptr(d_out_scores), stream))
 
 
 def debug_gemm_dev(d_A, d_W, d_bias, d_residual, d_C, M, N, K, epilogue, impl, stream=0):
