@@ -8,8 +8,8 @@
 //   warp 0      TMA producer: 128x64 A tiles and BNx64 W tiles, SWIZZLE_128B, into a smem ring
 //   warp 1      allocates TMEM and issues tcgen05.mma (one elected thread), fp32 accumulators in
 //               TMEM, two accumulator stages so the epilogue of tile i overlaps the MMAs of tile i+1
-//   warps 2-5   epilogue: tcgen05.ld -> bias (+GELU | +residual) in fp32 -> bf16 -> swizzled smem
-//               staging -> coalesced 16-byte global stores
+//   warps 2-9   epilogue: tcgen05.ld -> fp32 staging in swizzled smem -> bias (+GELU | +residual) in a
+//               column-per-lane layout -> bf16 -> coalesced 16-byte global stores
 // Three mbarrier pipelines: smem full/empty (TMA <-> MMA) and TMEM full/empty (MMA <-> epilogue).
 #include "common.h"
 #include "ptx.cuh"
@@ -20,20 +20,70 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int GEMM_THREADS = 192;
+constexpr int EPI_WARPS = 8;
+constexpr int GEMM_THREADS = 64 + EPI_WARPS * 32;  // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 constexpr int TMEM_COLS = 512;
 constexpr int ACC_STRIDE = 256;  // TMEM columns between the two accumulator stages
-constexpr int STAGING_BYTES = 4 * 32 * 128;
+constexpr int STAGING_BYTES = EPI_WARPS * 32 * 128;  // per warp: 32 rows x 32 fp32 columns
 
 template <int BN>
 struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BN <= 128) ? 6 : (BN <= 192 ? 5 : 4);
+    static constexpr int STAGES = (BN <= 128) ? 5 : 4;
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + STAGING_BYTES;
     static constexpr int SMEM_BYTES = BAR_OFFSET + 256 + 1024;  // + barriers + alignment slack
 };
+
+// ---- packed fp32x2 arithmetic (sm_100 FFMA2 / FMUL2): halves the issue slots of the epilogue ----
+__device__ __forceinline__ uint64_t pk2(float a, float b) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ void upk2(uint64_t v, float& a, float& b) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// Exact-erf GELU, x * Phi(x), evaluated without erff():
+//   gelu(x) = max(x,0) - |x| * tail(|x|),  tail(a) = Phi(-a) = 0.5 - a * P(a^2)  on a <= 4,
+// P = 9-term minimax fit (Lawson, weighted for the absolute error of gelu), tail clamped to >= 0 and
+// shifted so that tail(4) = 0.  Max abs error 1.3e-4 over all x (fp32 evaluation), i.e. an order of
+// magnitude below the bf16 rounding of the result; two elements per FFMA2.
+__device__ __forceinline__ void gelu2(float& x0, float& x1) {
+    const float a0 = fabsf(x0), a1 = fabsf(x1);
+    const float c0 = fminf(a0, 4.0f), c1 = fminf(a1, 4.0f);
+    const uint64_t ac = pk2(c0, c1);
+    const uint64_t u = mul2(ac, ac);
+    uint64_t p = pk2(6.740397823e-11f, 6.740397823e-11f);
+    p = fma2(p, u, pk2(-6.066908309e-09f, -6.066908309e-09f));
+    p = fma2(p, u, pk2(2.440845606e-07f, 2.440845606e-07f));
+    p = fma2(p, u, pk2(-5.860600595e-06f, -5.860600595e-06f));
+    p = fma2(p, u, pk2(9.494025289e-05f, 9.494025289e-05f));
+    p = fma2(p, u, pk2(-1.112856087e-03f, -1.112856087e-03f));
+    p = fma2(p, u, pk2(9.815800935e-03f, 9.815800935e-03f));
+    p = fma2(p, u, pk2(-6.632363051e-02f, -6.632363051e-02f));
+    p = fma2(p, u, pk2(3.988810182e-01f, 3.988810182e-01f));
+    // t = half - ac * p
+    const uint64_t t = fma2(pk2(-c0, -c1), p, pk2(4.999701977e-01f, 4.999701977e-01f));
+    float t0, t1;
+    upk2(t, t0, t1);
+    t0 = fmaxf(t0, 0.f);
+    t1 = fmaxf(t1, 0.f);
+    x0 = fmaf(-a0, t0, fmaxf(x0, 0.f));
+    x1 = fmaf(-a1, t1, fmaxf(x1, 0.f));
+}
 
 __device__ __forceinline__ float gelu_erf(float x) {
     return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
@@ -70,7 +120,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
-            mbar_init(bar_tempty + 8 * a, 4);  // one arrive per epilogue warp
+            mbar_init(bar_tempty + 8 * a, EPI_WARPS);  // one arrive per epilogue warp
         }
         fence_mbar_init();
     }
@@ -145,84 +195,87 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         }
     } else {
         // ===== epilogue warps =====
+        // Warp e owns TMEM lane quadrant (warp & 3) = 32 tile rows and one half of the tile's columns,
+        // in chunks of 32 columns.  Phase 1 (thread = row): tcgen05.ld -> raw fp32 accumulators into a
+        // swizzled per-warp smem staging block.  Phase 2 (lane = 8 consecutive columns of one row, 8 rows
+        // per instruction): bias / GELU / residual in fp32, bf16 pack, 16-byte coalesced stores.  All
+        // per-column operands (bias) sit in registers in phase 2; the residual is read coalesced.
+        constexpr int NCH = BN / 2 / 32;
         const int ew = warp - 2;
-        const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+        const int quad = warp & 3;
+        const int half = ew >> 2;
         uint8_t* stg = staging + ew * (32 * 128);
+        const int piece = lane & 3;   // which 8-column piece of the 32-column chunk (phase 2)
+        const int rsub = lane >> 2;   // row within a group of 8 (phase 2)
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
+            const int row0 = m_blk * BM + quad * 32;
+            const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC_STRIDE +
+                                   half * (BN / 2);
             mbar_wait(bar_tfull + 8 * acc, acc_phase);
             tc_fence_after();
-            const int row0 = m_blk * BM + quad * 32;
-            const int my_row = row0 + lane;
+            uint32_t v[32];
+            tmem_ld_32x32(tbase, v);
 #pragma unroll 1
-            for (int c = 0; c < BN / 64; ++c) {
-                uint32_t v0[32], v1[32];
-                const uint32_t taddr =
-                    tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC_STRIDE + c * 64;
-                tmem_ld_32x32(taddr, v0);
-                tmem_ld_32x32(taddr + 32, v1);
-                tmem_ld_wait();
-                const int col0 = n_blk * BN + c * 64;
-                uint4 res[8];
+            for (int c = 0; c < NCH; ++c) {
+                const int gcol = n_blk * BN + half * (BN / 2) + c * 32 + piece * 8;
+                // operands of phase 2 that do not depend on the accumulator: issue their loads early
+                const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + gcol));
+                const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + gcol) + 1);
+                uint4 res[4];
                 if (EPI == EPI_BIAS_RESIDUAL) {
-                    if (my_row < M) {
-                        const uint4* rp = reinterpret_cast<const uint4*>(
-                            residual + static_cast<size_t>(my_row) * N + col0);
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) res[i] = __ldg(rp + i);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) res[i] = make_uint4(0, 0, 0, 0);
+                    for (int it = 0; it < 4; ++it) {
+                        const int grow = row0 + it * 8 + rsub;
+                        res[it] = grow < M ? __ldg(reinterpret_cast<const uint4*>(
+                                                 residual + static_cast<size_t>(grow) * N + gcol))
+                                           : make_uint4(0, 0, 0, 0);
                     }
                 }
-                const float4* bp = reinterpret_cast<const float4*>(bias + col0);
+                tmem_ld_wait();
+                // ---- phase 1: registers -> swizzled staging (row = lane, 8 chunks of 4 floats) ----
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {  // 8 chunks of 8 columns (16 bytes of bf16)
-                    float x[8];
-                    const float4 b0 = __ldg(bp + 2 * i), b1 = __ldg(bp + 2 * i + 1);
-                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                for (int i = 0; i < 8; ++i) {
+                    *reinterpret_cast<uint4*>(stg + lane * 128 + ((i ^ (lane & 7)) * 16)) =
+                        make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                }
+                __syncwarp();
+                if (c + 1 < NCH) tmem_ld_32x32(tbase + (c + 1) * 32, v);  // overlaps phase 2
+                // ---- phase 2 ----
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const int col = i * 8 + j;
-                        const uint32_t raw = col < 32 ? v0[col] : v1[col - 32];
-                        x[j] = __uint_as_float(raw) + bb[j];
-                    }
+                for (int it = 0; it < 4; ++it) {
+                    const int r = it * 8 + rsub;
+                    const float4 f0 = *reinterpret_cast<const float4*>(stg + r * 128 + (((2 * piece) ^ (r & 7)) * 16));
+                    const float4 f1 = *reinterpret_cast<const float4*>(stg + r * 128 + (((2 * piece + 1) ^ (r & 7)) * 16));
+                    float x[8] = {f0.x + b0.x, f0.y + b0.y, f0.z + b0.z, f0.w + b0.w,
+                                  f1.x + b1.x, f1.y + b1.y, f1.z + b1.z, f1.w + b1.w};
                     if (EPI == EPI_BIAS_GELU) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) x[j] = gelu_erf(x[j]);
+                        for (int j = 0; j < 8; j += 2) gelu2(x[j], x[j + 1]);
                     }
                     if (EPI == EPI_BIAS_RESIDUAL) {
-                        const uint32_t rw[4] = {res[i].x, res[i].y, res[i].z, res[i].w};
+                        const uint32_t rw[4] = {res[it].x, res[it].y, res[it].z, res[it].w};
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             x[2 * j] += bf16_lo(rw[j]);
                             x[2 * j + 1] += bf16_hi(rw[j]);
                         }
                     }
-                    uint4 o;
-                    o.x = pack_bf16x2(x[0], x[1]);
-                    o.y = pack_bf16x2(x[2], x[3]);
-                    o.z = pack_bf16x2(x[4], x[5]);
-                    o.w = pack_bf16x2(x[6], x[7]);
-                    *reinterpret_cast<uint4*>(stg + lane * 128 + ((i ^ (lane & 7)) * 16)) = o;
-                }
-                __syncwarp();
-#pragma unroll
-                for (int it = 0; it < 8; ++it) {
-                    const int r = it * 4 + (lane >> 3);
-                    const int ch = lane & 7;
-                    const uint4 val =
-                        *reinterpret_cast<const uint4*>(stg + r * 128 + ((ch ^ (r & 7)) * 16));
                     const int grow = row0 + r;
                     if (grow < M) {
-                        *reinterpret_cast<uint4*>(C + static_cast<size_t>(grow) * N + col0 + ch * 8) =
-                            val;
+                        uint4 o;
+                        o.x = pack_bf16x2(x[0], x[1]);
+                        o.y = pack_bf16x2(x[2], x[3]);
+                        o.z = pack_bf16x2(x[4], x[5]);
+                        o.w = pack_bf16x2(x[6], x[7]);
+                        *reinterpret_cast<uint4*>(C + static_cast<size_t>(grow) * N + gcol) = o;
                     }
                 }
                 __syncwarp();
             }
+            // all of this warp's TMEM reads of the tile have completed (last tmem_ld_wait above)
             tc_fence_before();
             if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
             acc ^= 1;
