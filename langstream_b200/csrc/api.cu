@@ -41,21 +41,21 @@ int fail_cuda(cudaError_t e, const char* what, const char* file, int line) {
     return e == cudaErrorMemoryAllocation ? LSC_E_NOMEM : LSC_E_CUDA;
 }
 
-int make_tmap_bf16_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
-                         uint32_t box_rows) {
+static int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                          uint32_t box_cols, CUtensorMapSwizzle swizzle) {
     std::call_once(g_encode_once, load_encode);
     if (g_encode == nullptr)
         return fail(LSC_E_CUDA, "cuTensorMapEncodeTiled is not available from the CUDA driver");
-    if (rows == 0 || cols == 0 || cols % 64 != 0 || box_rows == 0 || box_rows > 256)
+    if (rows == 0 || cols == 0 || cols % box_cols != 0 || box_rows == 0 || box_rows > 256)
         return fail(LSC_E_INVALID, "tensor map: bad shape");
     if ((reinterpret_cast<uintptr_t>(base) & 15) != 0)
         return fail(LSC_E_INVALID, "tensor map: base pointer must be 16-byte aligned");
     const cuuint64_t gdim[2] = {cols, rows};
     const cuuint64_t gstride[1] = {cols * 2};  // bytes between rows
-    const cuuint32_t box[2] = {64, box_rows};
+    const cuuint32_t box[2] = {box_cols, box_rows};
     const cuuint32_t estride[2] = {1, 1};
     CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride,
-                          box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                          box, estride, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         char buf[128];
@@ -63,6 +63,15 @@ int make_tmap_bf16_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint
         return fail(LSC_E_CUDA, buf);
     }
     return LSC_OK;
+}
+
+int make_tmap_bf16_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
+                         uint32_t box_rows) {
+    return make_tmap_bf16(out, base, rows, cols, box_rows, 64, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int make_tmap_bf16_store32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols) {
+    return make_tmap_bf16(out, base, rows, cols, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B);
 }
 
 }  // namespace lsc
@@ -105,10 +114,11 @@ int lsc_debug_gemm_dev(const void* d_A, const void* d_W, const float* d_bias, co
     int dev = 0, sms = 0;
     LSC_CUDA(cudaGetDevice(&dev));
     LSC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    CUtensorMap ta, tw;
+    CUtensorMap ta, tw, tc;
     LSC_TRY(make_tmap_bf16_sw128(&ta, A, M, K, 128));
     LSC_TRY(make_tmap_bf16_sw128(&tw, W, N, K, bn));
-    int rc = gemm_tc_launch(ta, tw, d_bias, R, C, M, N, K, epilogue, sms, st);
+    LSC_TRY(make_tmap_bf16_store32(&tc, C, M, N));
+    int rc = gemm_tc_launch(ta, tw, tc, d_bias, R, M, N, K, epilogue, sms, st);
     return rc < 0 ? rc : LSC_OK;
 }
 

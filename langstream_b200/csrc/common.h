@@ -83,15 +83,18 @@ struct Profiler {
 // are filled with zeros.
 int make_tmap_bf16_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols,
                          uint32_t box_rows);
+// Store map of a bf16 row-major [rows, cols] output: box = [32 rows, 32 cols], SWIZZLE_64B (the GEMM
+// epilogue stages 32x32 blocks in shared memory and writes them with TMA; rows past `rows` are clipped).
+int make_tmap_bf16_store32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols);
 
 // ---- kernel launchers (defined in the .cu files) ---------------------------------------------
-enum GemmEpilogue { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESIDUAL = 2 };
+enum GemmEpilogue { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESIDUAL = 2, EPI_DISCARD = 3 /* debug */, EPI_LOADONLY = 4 /* debug */ };
 
 // tcgen05 GEMM: C[M,N] = epi(A[M,K]·W[N,K]^T + bias).  tmapA: box 128 rows; tmapW: box BN rows,
 // where BN = gemm_tc_block_n(N).  Returns number of kernel launches (1) or <0 on error.
 int gemm_tc_block_n(int N);
-int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const float* bias,
-                   const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,
+int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
+                   const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,
                    int num_sms, cudaStream_t stream);
 // CUDA-core validation GEMM (debug).
 int gemm_ref_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const float* bias,

@@ -8,9 +8,11 @@
 //   warp 0      TMA producer: 128x64 A tiles and BNx64 W tiles, SWIZZLE_128B, into a smem ring
 //   warp 1      allocates TMEM and issues tcgen05.mma (one elected thread), fp32 accumulators in
 //               TMEM, two accumulator stages so the epilogue of tile i overlaps the MMAs of tile i+1
-//   warps 2-9   epilogue: tcgen05.ld -> fp32 staging in swizzled smem -> bias (+GELU | +residual) in a
-//               column-per-lane layout -> bf16 -> coalesced 16-byte global stores
+//   warps 2-9   epilogue: tcgen05.ld (thread = row) -> bias (+GELU | +residual) in fp32 -> bf16 ->
+//               32x32 blocks in swizzled smem -> TMA stores
 // Three mbarrier pipelines: smem full/empty (TMA <-> MMA) and TMEM full/empty (MMA <-> epilogue).
+#include <cstdlib>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -24,14 +26,14 @@ constexpr int EPI_WARPS = 8;
 constexpr int GEMM_THREADS = 64 + EPI_WARPS * 32;  // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 constexpr int TMEM_COLS = 512;
 constexpr int ACC_STRIDE = 256;  // TMEM columns between the two accumulator stages
-constexpr int STAGING_BYTES = EPI_WARPS * 32 * 128;  // per warp: 32 rows x 32 fp32 columns
+constexpr int STAGING_BYTES = EPI_WARPS * 2 * 2048;  // per warp: two 32x32 bf16 blocks (TMA store sources)
 
 template <int BN>
 struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BN <= 128) ? 5 : 4;
+    static constexpr int STAGES = (BN <= 128) ? 6 : 4;
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + STAGING_BYTES;
     static constexpr int SMEM_BYTES = BAR_OFFSET + 256 + 1024;  // + barriers + alignment slack
 };
@@ -54,6 +56,18 @@ __device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
     uint64_t d;
     asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
     return d;
+}
+
+// 256-bit global accesses (sm_100: LDG/STG.E.ENL2.256): one whole 32-byte sector per thread.
+__device__ __forceinline__ void ldg256(const void* p, uint32_t* r) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void stg256(void* p, const uint32_t* r) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+                 "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
 }
 
 // Exact-erf GELU, x * Phi(x), evaluated without erff():
@@ -92,15 +106,15 @@ __device__ __forceinline__ float gelu_erf(float x) {
 template <int BN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
-               const float* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
-               __nv_bfloat16* __restrict__ C, int M, int N, int K) {
+               const __grid_constant__ CUtensorMap tmapC, const float* __restrict__ bias,
+               const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int dbg) {
     using cfg = Cfg<BN>;
     constexpr int STAGES = cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
     const uint32_t smem_base = smem_u32(smem);
-    uint8_t* staging = smem + STAGES * cfg::STAGE_BYTES;
+    uint8_t* staging = smem + STAGES * cfg::STAGE_BYTES;  // 1024-byte aligned
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + cfg::BAR_OFFSET);
     const uint32_t bar_full = smem_u32(bars);
     const uint32_t bar_empty = bar_full + 8 * STAGES;
@@ -114,6 +128,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmapA);
         tma_prefetch_desc(&tmapW);
+        tma_prefetch_desc(&tmapC);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(bar_full + 8 * s, 1);
             mbar_init(bar_empty + 8 * s, 1);
@@ -196,91 +211,121 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     } else {
         // ===== epilogue warps =====
         // Warp e owns TMEM lane quadrant (warp & 3) = 32 tile rows and one half of the tile's columns,
-        // in chunks of 32 columns.  Phase 1 (thread = row): tcgen05.ld -> raw fp32 accumulators into a
-        // swizzled per-warp smem staging block.  Phase 2 (lane = 8 consecutive columns of one row, 8 rows
-        // per instruction): bias / GELU / residual in fp32, bf16 pack, 16-byte coalesced stores.  All
-        // per-column operands (bias) sit in registers in phase 2; the residual is read coalesced.
+        // in chunks of 32 columns; thread = row.  Per chunk: tcgen05.ld -> bias (+GELU | +residual) in
+        // fp32 -> bf16 -> a 32x32 block in shared memory (SWIZZLE_64B, conflict-free 16-byte stores) ->
+        // one TMA store issued by lane 0.  The stores bypass the LSU, clip the M tail in hardware and
+        // cost 2 KB of smem write + 2 KB of smem read per chunk (the MMA main loop itself runs at the
+        // shared-memory bandwidth limit, so the epilogue's smem traffic is kept to that minimum).
+        // The TMEM load of chunk c+1 is in flight while chunk c is processed; two staging blocks per
+        // warp let a TMA store drain while the next block is filled.
         constexpr int NCH = BN / 2 / 32;
         const int ew = warp - 2;
         const int quad = warp & 3;
         const int half = ew >> 2;
-        uint8_t* stg = staging + ew * (32 * 128);
-        const int piece = lane & 3;   // which 8-column piece of the 32-column chunk (phase 2)
-        const int rsub = lane >> 2;   // row within a group of 8 (phase 2)
+        uint8_t* stg = staging + ew * 4096;
+        const uint32_t stg_addr = smem_u32(stg);
+        const uint32_t sw = (static_cast<uint32_t>(lane) >> 1) & 3;  // SWIZZLE_64B: chunk ^= (row >> 1) & 3
+        int buf = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
             const int row0 = m_blk * BM + quad * 32;
+            const int grow = row0 + lane;
+            const bool row_ok = grow < M;
+            const int col_base = n_blk * BN + half * (BN / 2);
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC_STRIDE +
                                    half * (BN / 2);
+            const __nv_bfloat16* rrow =
+                EPI == EPI_BIAS_RESIDUAL ? residual + static_cast<size_t>(row_ok ? grow : 0) * N + col_base : nullptr;
             mbar_wait(bar_tfull + 8 * acc, acc_phase);
             tc_fence_after();
-            uint32_t v[32];
-            tmem_ld_32x32(tbase, v);
-#pragma unroll 1
-            for (int c = 0; c < NCH; ++c) {
-                const int gcol = n_blk * BN + half * (BN / 2) + c * 32 + piece * 8;
-                // operands of phase 2 that do not depend on the accumulator: issue their loads early
-                const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + gcol));
-                const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + gcol) + 1);
-                uint4 res[4];
-                if (EPI == EPI_BIAS_RESIDUAL) {
+            uint32_t va[32], vb[32];
+            if (EPI == EPI_DISCARD) {  // debug: measure the TMA + MMA main loop alone
+                __syncwarp();
+                tc_fence_before();
+                if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+                continue;
+            }
+            tmem_ld_32x32(tbase, va);
+            if (EPI == EPI_LOADONLY) {  // debug: main loop + TMEM reads, nothing else
+                uint32_t keep = 0;
 #pragma unroll
-                    for (int it = 0; it < 4; ++it) {
-                        const int grow = row0 + it * 8 + rsub;
-                        res[it] = grow < M ? __ldg(reinterpret_cast<const uint4*>(
-                                                 residual + static_cast<size_t>(grow) * N + gcol))
-                                           : make_uint4(0, 0, 0, 0);
-                    }
+                for (int c = 0; c < NCH; ++c) {
+                    uint32_t(&v)[32] = (c & 1) ? vb : va;
+                    uint32_t(&vnext)[32] = (c & 1) ? va : vb;
+                    tmem_ld_wait();
+                    if (c + 1 < NCH) tmem_ld_32x32(tbase + (c + 1) * 32, vnext);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) keep ^= v[i];
+                }
+                if (keep == 0x12345678u && bias != nullptr) *const_cast<float*>(bias) = 0.f;  // never true in practice
+                __syncwarp();
+                tc_fence_before();
+                if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+                continue;
+            }
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) {
+                uint32_t(&v)[32] = (c & 1) ? vb : va;
+                uint32_t(&vnext)[32] = (c & 1) ? va : vb;
+                uint32_t res[16];
+                if (EPI == EPI_BIAS_RESIDUAL) {
+                    ldg256(rrow + c * 32, res);
+                    ldg256(rrow + c * 32 + 16, res + 8);
                 }
                 tmem_ld_wait();
-                // ---- phase 1: registers -> swizzled staging (row = lane, 8 chunks of 4 floats) ----
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    *reinterpret_cast<uint4*>(stg + lane * 128 + ((i ^ (lane & 7)) * 16)) =
-                        make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                }
+                if (c + 1 < NCH) tmem_ld_32x32(tbase + (c + 1) * 32, vnext);
+                const float4* bp = reinterpret_cast<const float4*>(bias + ((dbg & 4) ? 0 : col_base + c * 32));
+                // the block we are about to fill was the source of the TMA store issued two chunks ago
+                if (lane == 0) tma_store_wait_read<1>();
                 __syncwarp();
-                if (c + 1 < NCH) tmem_ld_32x32(tbase + (c + 1) * 32, v);  // overlaps phase 2
-                // ---- phase 2 ----
+                uint8_t* blk = stg + buf * 2048 + lane * 64;
 #pragma unroll
-                for (int it = 0; it < 4; ++it) {
-                    const int r = it * 8 + rsub;
-                    const float4 f0 = *reinterpret_cast<const float4*>(stg + r * 128 + (((2 * piece) ^ (r & 7)) * 16));
-                    const float4 f1 = *reinterpret_cast<const float4*>(stg + r * 128 + (((2 * piece + 1) ^ (r & 7)) * 16));
-                    float x[8] = {f0.x + b0.x, f0.y + b0.y, f0.z + b0.z, f0.w + b0.w,
-                                  f1.x + b1.x, f1.y + b1.y, f1.z + b1.z, f1.w + b1.w};
+                for (int i = 0; i < 4; ++i) {  // 4 x 16 bytes = 8 columns each
+                    const float4 b0 = __ldg(bp + 2 * i), b1 = __ldg(bp + 2 * i + 1);
+                    float x[8] = {__uint_as_float(v[8 * i]) + b0.x,     __uint_as_float(v[8 * i + 1]) + b0.y,
+                                  __uint_as_float(v[8 * i + 2]) + b0.z, __uint_as_float(v[8 * i + 3]) + b0.w,
+                                  __uint_as_float(v[8 * i + 4]) + b1.x, __uint_as_float(v[8 * i + 5]) + b1.y,
+                                  __uint_as_float(v[8 * i + 6]) + b1.z, __uint_as_float(v[8 * i + 7]) + b1.w};
                     if (EPI == EPI_BIAS_GELU) {
 #pragma unroll
                         for (int j = 0; j < 8; j += 2) gelu2(x[j], x[j + 1]);
                     }
                     if (EPI == EPI_BIAS_RESIDUAL) {
-                        const uint32_t rw[4] = {res[it].x, res[it].y, res[it].z, res[it].w};
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            x[2 * j] += bf16_lo(rw[j]);
-                            x[2 * j + 1] += bf16_hi(rw[j]);
+                            x[2 * j] += bf16_lo(res[4 * i + j]);
+                            x[2 * j + 1] += bf16_hi(res[4 * i + j]);
                         }
                     }
-                    const int grow = row0 + r;
-                    if (grow < M) {
-                        uint4 o;
-                        o.x = pack_bf16x2(x[0], x[1]);
-                        o.y = pack_bf16x2(x[2], x[3]);
-                        o.z = pack_bf16x2(x[4], x[5]);
-                        o.w = pack_bf16x2(x[6], x[7]);
-                        *reinterpret_cast<uint4*>(C + static_cast<size_t>(grow) * N + gcol) = o;
-                    }
+                    uint4 o;
+                    o.x = pack_bf16x2(x[0], x[1]);
+                    o.y = pack_bf16x2(x[2], x[3]);
+                    o.z = pack_bf16x2(x[4], x[5]);
+                    o.w = pack_bf16x2(x[6], x[7]);
+                    if (!(dbg & 2) || o.x == 0x7fc07fc0u) *reinterpret_cast<uint4*>(blk + ((static_cast<uint32_t>(i) ^ sw) * 16)) = o;
                 }
+                if (!(dbg & 8)) fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA engine
                 __syncwarp();
+                if (lane == 0 && !(dbg & 1)) {
+                    tma_store_2d(&tmapC, stg_addr + buf * 2048, col_base + c * 32, row0);
+                    tma_store_commit();
+                }
+                buf ^= 1;
             }
-            // all of this warp's TMEM reads of the tile have completed (last tmem_ld_wait above)
+            // every TMEM read of this tile by this warp has completed (tmem_ld_wait above)
+            __syncwarp();
             tc_fence_before();
             if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
+        if (lane == 0) tma_store_wait_all<0>();  // global writes complete before the kernel ends
     }
 
     tc_fence_before();
@@ -292,9 +337,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 }
 
 template <int BN, int EPI>
-int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const float* bias,
-                const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int num_sms,
-                cudaStream_t stream) {
+int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
+                const __nv_bfloat16* residual, int M, int N, int K, int num_sms, cudaStream_t stream) {
     using cfg = Cfg<BN>;
     static bool configured[64] = {};  // per instantiation and per device
     auto kern = gemm_tc_kernel<BN, EPI>;
@@ -308,25 +352,28 @@ int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const float*
     const int m_tiles = (M + BM - 1) / BM;
     const int num_tiles = m_tiles * (N / BN);
     const int grid = num_tiles < num_sms ? num_tiles : num_sms;
-    kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, bias, residual, C, M, N, K);
+    static const int dbg = [] { const char* e = getenv("LSC_GEMM_DBG"); return e ? atoi(e) : 0; }();
+    kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, dbg);
     LSC_CUDA(cudaGetLastError());
     return 1;
 }
 
 template <int BN>
-int launch_bn(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const float* bias,
-              const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,
-              int num_sms, cudaStream_t stream) {
+int launch_bn(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
+              const __nv_bfloat16* residual, int M, int N, int K, int epilogue, int num_sms,
+              cudaStream_t stream) {
     switch (epilogue) {
         case EPI_BIAS:
-            return launch_inst<BN, EPI_BIAS>(tmapA, tmapW, bias, residual, C, M, N, K, num_sms, stream);
+            return launch_inst<BN, EPI_BIAS>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
         case EPI_BIAS_GELU:
-            return launch_inst<BN, EPI_BIAS_GELU>(tmapA, tmapW, bias, residual, C, M, N, K, num_sms,
-                                                  stream);
+            return launch_inst<BN, EPI_BIAS_GELU>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
         case EPI_BIAS_RESIDUAL:
             if (residual == nullptr) return fail(LSC_E_INVALID, "gemm: residual epilogue without residual");
-            return launch_inst<BN, EPI_BIAS_RESIDUAL>(tmapA, tmapW, bias, residual, C, M, N, K, num_sms,
-                                                      stream);
+            return launch_inst<BN, EPI_BIAS_RESIDUAL>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
+        case EPI_DISCARD:
+            return launch_inst<BN, EPI_DISCARD>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
+        case EPI_LOADONLY:
+            return launch_inst<BN, EPI_LOADONLY>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
         default:
             return fail(LSC_E_INVALID, "gemm: unknown epilogue");
     }
@@ -335,25 +382,31 @@ int launch_bn(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const float* b
 }  // namespace
 
 int gemm_tc_block_n(int N) {
+    // LSC_GEMM_BN (debug): force a tile width when it divides N
+    static const int forced = [] {
+        const char* e = getenv("LSC_GEMM_BN");
+        return e ? atoi(e) : 0;
+    }();
+    if (forced > 0 && N % forced == 0 && (forced == 128 || forced == 192 || forced == 256)) return forced;
     if (N % 192 == 0) return 192;
     if (N % 256 == 0) return 256;
     if (N % 128 == 0) return 128;
     return 0;
 }
 
-int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const float* bias,
-                   const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,
+int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
+                   const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,
                    int num_sms, cudaStream_t stream) {
     if (M <= 0) return 0;
     if (K % BK != 0 || K <= 0) return fail(LSC_E_UNSUPPORTED, "gemm: K must be a positive multiple of 64");
     if (bias == nullptr) return fail(LSC_E_INVALID, "gemm: bias is required");
     switch (gemm_tc_block_n(N)) {
         case 192:
-            return launch_bn<192>(tmapA, tmapW, bias, residual, C, M, N, K, epilogue, num_sms, stream);
+            return launch_bn<192>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, num_sms, stream);
         case 256:
-            return launch_bn<256>(tmapA, tmapW, bias, residual, C, M, N, K, epilogue, num_sms, stream);
+            return launch_bn<256>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, num_sms, stream);
         case 128:
-            return launch_bn<128>(tmapA, tmapW, bias, residual, C, M, N, K, epilogue, num_sms, stream);
+            return launch_bn<128>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, num_sms, stream);
         default:
             return fail(LSC_E_UNSUPPORTED, "gemm: N must be a multiple of 128");
     }
