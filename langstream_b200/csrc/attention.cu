@@ -4,11 +4,19 @@
 // (AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:194-196):
 // packing makes the mask implicit — only a sequence's own tokens are ever keys.
 //
-// One CTA per (head, sequence); K and V of that head live in shared memory for the CTA's lifetime;
-// each warp owns 16 query rows at a time and streams key blocks of 64 with an online (flash-style)
-// softmax in fp32.  d_head is 32 or 64, so the contraction depth per tile is tiny and the kernel is
-// bound by exp2 / shared-memory traffic, not by the tensor pipe: it uses warp-level
-// mma.sync.m16n8k16 (bf16 in, fp32 accumulate) rather than tcgen05.
+// One CTA per (sequence, head); K (bf16) and V (converted to fp16) of that head live in shared memory
+// for the CTA's lifetime; each warp owns 16 query rows at a time and streams key blocks of 64 with an
+// online (flash-style) softmax.  d_head is 32 or 64, so the contraction depth per tile is tiny and the
+// kernel is bound by the exponentials and the instruction issue rate, not by the tensor pipe; it
+// therefore uses warp-level mma.sync.m16n8k16 (fp32 accumulate) rather than tcgen05, and spends its
+// effort on the softmax:
+//   * P = exp2(...) is evaluated with ex2.approx.f16x2 — two probabilities per MUFU operation —
+//     and the packed fp16 pair IS the A fragment of the P·V MMA (no separate convert/pack);
+//   * the row sums come out of the tensor core too: one extra MMA per 16 keys against an all-ones
+//     B fragment accumulates sum_j P[i][j] in fp32, so no per-element additions or shuffles;
+//   * the key mask is applied only in a sequence's last, partial key block.
+#include <cuda_fp16.h>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -39,9 +47,30 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a
         : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
+__device__ __forceinline__ void mma_f16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0,
+                                              uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
+        "{%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// exp2 of two fp32 arguments, evaluated as one packed fp16x2 MUFU operation.
+__device__ __forceinline__ uint32_t exp2_f16x2(float lo, float hi) {
+    uint32_t h, r;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(hi), "f"(lo));  // first source -> upper half
+    asm("ex2.approx.f16x2 %0, %1;" : "=r"(r) : "r"(h));
+    return r;
+}
+// bf16x2 -> fp16x2 (values of V are O(1): well inside fp16 range)
+__device__ __forceinline__ uint32_t bf16x2_to_f16x2(uint32_t w) {
+    uint32_t h;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(bf16_hi(w)), "f"(bf16_lo(w)));
+    return h;
+}
 
 template <int D>
-__global__ void __launch_bounds__(ATT_THREADS)
+__global__ void __launch_bounds__(ATT_THREADS, 3)
 attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ cu_seqlens, int H,
                  int heads, __nv_bfloat16* __restrict__ ctx, float scale_log2e) {
     constexpr int LD = D + 8;  // padded row (elements): conflict-free ldmatrix
@@ -53,11 +82,11 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
     if (s <= 0) return;
     const int s_pad = (s + KEY_BLOCK - 1) / KEY_BLOCK * KEY_BLOCK;
     __nv_bfloat16* sK = reinterpret_cast<__nv_bfloat16*>(att_smem);
-    __nv_bfloat16* sV = sK + static_cast<size_t>(s_pad) * LD;
+    __half* sV = reinterpret_cast<__half*>(sK + static_cast<size_t>(s_pad) * LD);
     const size_t row_stride = static_cast<size_t>(3) * H;
     const __nv_bfloat16* qbase = qkv + static_cast<size_t>(t0) * row_stride + head * D;
 
-    // ---- stage K and V (zero-padded to a multiple of the key block) ----
+    // ---- stage K (bf16) and V (fp16), zero-padded to a multiple of the key block ----
     constexpr int CPR = D / 8;  // 16-byte chunks per row
     for (int i = threadIdx.x; i < s_pad * CPR; i += ATT_THREADS) {
         const int r = i / CPR, c = i % CPR;
@@ -66,6 +95,10 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
             const __nv_bfloat16* rp = qbase + static_cast<size_t>(r) * row_stride + c * 8;
             kv = __ldg(reinterpret_cast<const uint4*>(rp + H));
             vv = __ldg(reinterpret_cast<const uint4*>(rp + 2 * H));
+            vv.x = bf16x2_to_f16x2(vv.x);
+            vv.y = bf16x2_to_f16x2(vv.y);
+            vv.z = bf16x2_to_f16x2(vv.z);
+            vv.w = bf16x2_to_f16x2(vv.w);
         }
         *reinterpret_cast<uint4*>(sK + static_cast<size_t>(r) * LD + c * 8) = kv;
         *reinterpret_cast<uint4*>(sV + static_cast<size_t>(r) * LD + c * 8) = vv;
@@ -76,6 +109,7 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
     const int g = lane >> 2, tq = lane & 3;
     const uint32_t sK_addr = smem_u32(sK), sV_addr = smem_u32(sV);
     const int lm = lane >> 3, lr = lane & 7;  // ldmatrix: matrix index / row within matrix
+    constexpr uint32_t ONES = 0x3C003C00u;    // fp16x2 (1, 1)
 
     for (int qb = warp; qb * 16 < s; qb += ATT_THREADS / 32) {
         // ---- Q fragments (A operand), straight from global ----
@@ -91,11 +125,11 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
             qa[ks][2] = r_lo < s ? __ldg(plo + 4) : 0u;
             qa[ks][3] = r_hi < s ? __ldg(phi + 4) : 0u;
         }
-        float o[D / 8][4];
+        // o[0..D/8) = output accumulators, o[D/8] = row sums (every column of that tile holds the sum)
+        float o[D / 8 + 1][4];
 #pragma unroll
-        for (int i = 0; i < D / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+        for (int i = 0; i <= D / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
         float m_run[2] = {-INFINITY, -INFINITY};
-        float l_run[2] = {0.f, 0.f};
 
         for (int kb0 = 0; kb0 < s; kb0 += KEY_BLOCK) {
             float sc[8][4];
@@ -114,73 +148,69 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
                     mma_bf16_16816(sc[nt + 1], qa[ks], b2, b3);
                 }
             }
-            // ---- mask the tail, online softmax ----
+            // ---- mask (last partial block only) and running max ----
+            if (kb0 + KEY_BLOCK > s) {
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (kb0 + nt * 8 + 2 * tq + (j & 1) >= s) sc[nt][j] = -INFINITY;
+            }
             float mx[2] = {-INFINITY, -INFINITY};
 #pragma unroll
             for (int nt = 0; nt < 8; ++nt) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int key = kb0 + nt * 8 + 2 * tq + (j & 1);
-                    if (key >= s) sc[nt][j] = -INFINITY;
-                    mx[j >> 1] = fmaxf(mx[j >> 1], sc[nt][j]);
-                }
+                mx[0] = fmaxf(mx[0], fmaxf(sc[nt][0], sc[nt][1]));
+                mx[1] = fmaxf(mx[1], fmaxf(sc[nt][2], sc[nt][3]));
             }
 #pragma unroll
             for (int h2 = 0; h2 < 2; ++h2) {
                 mx[h2] = fmaxf(mx[h2], __shfl_xor_sync(0xffffffffu, mx[h2], 1));
                 mx[h2] = fmaxf(mx[h2], __shfl_xor_sync(0xffffffffu, mx[h2], 2));
             }
-            float corr[2], mscaled[2];
+            float nms[2];  // -max * scale
+            if (kb0 == 0) {
+                m_run[0] = mx[0];
+                m_run[1] = mx[1];
+            } else {
+                float corr[2];
 #pragma unroll
-            for (int h2 = 0; h2 < 2; ++h2) {
-                const float m_new = fmaxf(m_run[h2], mx[h2]);  // finite: every block has a valid key
-                corr[h2] = exp2f((m_run[h2] - m_new) * scale_log2e);
-                m_run[h2] = m_new;
-                mscaled[h2] = m_new * scale_log2e;
-                l_run[h2] *= corr[h2];
-            }
+                for (int h2 = 0; h2 < 2; ++h2) {
+                    const float m_new = fmaxf(m_run[h2], mx[h2]);  // finite: every block has a valid key
+                    corr[h2] = exp2f((m_run[h2] - m_new) * scale_log2e);
+                    m_run[h2] = m_new;
+                }
 #pragma unroll
-            for (int i = 0; i < D / 8; ++i) {
-                o[i][0] *= corr[0];
-                o[i][1] *= corr[0];
-                o[i][2] *= corr[1];
-                o[i][3] *= corr[1];
-            }
-#pragma unroll
-            for (int nt = 0; nt < 8; ++nt) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float p = exp2f(sc[nt][j] * scale_log2e - mscaled[j >> 1]);
-                    sc[nt][j] = p;
-                    l_run[j >> 1] += p;
+                for (int i = 0; i <= D / 8; ++i) {
+                    o[i][0] *= corr[0];
+                    o[i][1] *= corr[0];
+                    o[i][2] *= corr[1];
+                    o[i][3] *= corr[1];
                 }
             }
-            // ---- O += P V ----
+            nms[0] = -m_run[0] * scale_log2e;
+            nms[1] = -m_run[1] * scale_log2e;
+            // ---- P = exp2(S*scale - max*scale) as packed fp16 A fragments; O += P V; sums += P 1 ----
 #pragma unroll
             for (int kk = 0; kk < KEY_BLOCK / 16; ++kk) {
                 uint32_t pa[4];
-                pa[0] = pack_bf16x2(sc[2 * kk][0], sc[2 * kk][1]);
-                pa[1] = pack_bf16x2(sc[2 * kk][2], sc[2 * kk][3]);
-                pa[2] = pack_bf16x2(sc[2 * kk + 1][0], sc[2 * kk + 1][1]);
-                pa[3] = pack_bf16x2(sc[2 * kk + 1][2], sc[2 * kk + 1][3]);
+                pa[0] = exp2_f16x2(fmaf(sc[2 * kk][0], scale_log2e, nms[0]), fmaf(sc[2 * kk][1], scale_log2e, nms[0]));
+                pa[1] = exp2_f16x2(fmaf(sc[2 * kk][2], scale_log2e, nms[1]), fmaf(sc[2 * kk][3], scale_log2e, nms[1]));
+                pa[2] = exp2_f16x2(fmaf(sc[2 * kk + 1][0], scale_log2e, nms[0]), fmaf(sc[2 * kk + 1][1], scale_log2e, nms[0]));
+                pa[3] = exp2_f16x2(fmaf(sc[2 * kk + 1][2], scale_log2e, nms[1]), fmaf(sc[2 * kk + 1][3], scale_log2e, nms[1]));
 #pragma unroll
                 for (int nt = 0; nt < D / 8; nt += 2) {
                     const int key = kb0 + kk * 16 + (lm & 1) * 8 + lr;
                     const int dof = (nt + (lm >> 1)) * 8;
                     uint32_t b0, b1, b2, b3;
                     ldmatrix_x4_trans(sV_addr + (key * LD + dof) * 2, b0, b1, b2, b3);
-                    mma_bf16_16816(o[nt], pa, b0, b1);
-                    mma_bf16_16816(o[nt + 1], pa, b2, b3);
+                    mma_f16_16816(o[nt], pa, b0, b1);
+                    mma_f16_16816(o[nt + 1], pa, b2, b3);
                 }
+                mma_f16_16816(o[D / 8], pa, ONES, ONES);
             }
         }
         // ---- normalise and store ----
-#pragma unroll
-        for (int h2 = 0; h2 < 2; ++h2) {
-            l_run[h2] += __shfl_xor_sync(0xffffffffu, l_run[h2], 1);
-            l_run[h2] += __shfl_xor_sync(0xffffffffu, l_run[h2], 2);
-        }
-        const float inv0 = 1.0f / l_run[0], inv1 = 1.0f / l_run[1];
+        const float inv0 = 1.0f / o[D / 8][0], inv1 = 1.0f / o[D / 8][2];
         __nv_bfloat16* obase = ctx + static_cast<size_t>(t0) * H + head * D;
 #pragma unroll
         for (int nt = 0; nt < D / 8; ++nt) {
@@ -225,3 +255,13 @@ int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_
 }
 
 }  // namespace lsc
+
+extern "C" int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_seqlens, int32_t n_seq,
+                                       int32_t hidden, int32_t heads, int32_t max_seqlen, void* d_ctx,
+                                       void* stream) {
+    if (d_qkv == nullptr || d_cu_seqlens == nullptr || d_ctx == nullptr || n_seq < 0 || hidden <= 0 || heads <= 0)
+        return lsc::fail(LSC_E_INVALID, "lsc_debug_attention_dev: bad argument");
+    int rc = lsc::attention_launch(static_cast<const __nv_bfloat16*>(d_qkv), d_cu_seqlens, n_seq, hidden, heads,
+                                   max_seqlen, static_cast<__nv_bfloat16*>(d_ctx), static_cast<cudaStream_t>(stream));
+    return rc < 0 ? rc : LSC_OK;
+}

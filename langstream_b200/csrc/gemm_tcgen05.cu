@@ -156,6 +156,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     if (warp == 0) {
         // ===== TMA producer =====
         if (elect_one()) {
+            const uint64_t pol_keep = policy_evict_last();
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -165,6 +166,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                     const uint32_t sA = smem_base + stage * cfg::STAGE_BYTES;
                     const uint32_t sB = sA + cfg::A_BYTES;
                     mbar_arrive_expect_tx(bar_full + 8 * stage, cfg::STAGE_BYTES);
+                    if (dbg & 16) {
+                        tma_load_2d_hint(sA, &tmapA, bar_full + 8 * stage, kb * BK, m_blk * BM, pol_keep);
+                        tma_load_2d_hint(sB, &tmapW, bar_full + 8 * stage, kb * BK, n_blk * BN, pol_keep);
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     tma_load_2d(sA, &tmapA, bar_full + 8 * stage, kb * BK, m_blk * BM);
                     tma_load_2d(sB, &tmapW, bar_full + 8 * stage, kb * BK, n_blk * BN);
                     if (++stage == STAGES) {
@@ -313,7 +320,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 if (!(dbg & 8)) fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA engine
                 __syncwarp();
                 if (lane == 0 && !(dbg & 1)) {
-                    tma_store_2d(&tmapC, stg_addr + buf * 2048, col_base + c * 32, row0);
+                    if (dbg & 32) tma_store_2d_hint(&tmapC, stg_addr + buf * 2048, col_base + c * 32, row0, policy_evict_first());
+                    else tma_store_2d(&tmapC, stg_addr + buf * 2048, col_base + c * 32, row0);
                     tma_store_commit();
                 }
                 buf ^= 1;

@@ -1,0 +1,54 @@
+"""Packed variable-length attention kernel alone against an fp32 torch reference of the same op."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _reference(qkv, cu, H, heads):
+    import torch
+
+    d = H // heads
+    out = torch.zeros(qkv.shape[0], H, dtype=torch.float32, device=qkv.device)
+    x = qkv.float()
+    for i in range(len(cu) - 1):
+        a, b = int(cu[i]), int(cu[i + 1])
+        if b == a:
+            continue
+        q = x[a:b, :H].view(b - a, heads, d).transpose(0, 1)
+        k = x[a:b, H:2 * H].view(b - a, heads, d).transpose(0, 1)
+        v = x[a:b, 2 * H:].view(b - a, heads, d).transpose(0, 1)
+        p = torch.softmax(q @ k.transpose(1, 2) / d ** 0.5, dim=-1)
+        out[a:b] = (p @ v).transpose(0, 1).reshape(b - a, H)
+    return out
+
+
+@pytest.mark.parametrize("H,heads,lens,scale", [
+    (384, 12, [128] * 6, 1.0),
+    (384, 12, [1, 7, 16, 63, 64, 65, 100, 127, 128, 0, 33], 1.0),
+    (384, 12, [128, 96, 50], 6.0),          # peaked softmax (large logits)
+    (768, 12, [512, 300, 64, 1, 257], 1.0),  # d_head 64, several key blocks with online rescaling
+    (768, 12, [512, 511], 4.0),
+    (128, 4, [40, 5], 1.0),
+])
+def test_attention_matches_fp32_reference(native_lib, cuda_device, H, heads, lens, scale):
+    import torch
+    from langstream_b200 import _native
+
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    T = int(cu[-1])
+    g = torch.Generator(device="cpu").manual_seed(len(lens) * 1000 + H)
+    qkv = (torch.randn(T, 3 * H, generator=g) * scale).to(torch.bfloat16).to(cuda_device)
+    ctx = torch.full((T, H), float("nan"), dtype=torch.bfloat16, device=cuda_device)
+    d_cu = torch.from_numpy(cu).to(cuda_device)
+    _native.debug_attention_dev(qkv, d_cu, len(lens), H, heads, max(lens), ctx,
+                                torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    ref = _reference(qkv, cu, H, heads)
+    got = ctx.float()
+    assert torch.isfinite(got).all()
+    err = (got - ref).abs()
+    # bf16 output rounding (2^-8 relative) + fp16 probabilities (2^-11) on values of magnitude <= |V|max
+    tol = 0.01 * scale + 0.01 * ref.abs()
+    assert bool((err <= tol).all()), f"max err {err.max().item():.4f} (ref magnitude {ref.abs().max().item():.2f})"
+    assert err.mean().item() < 2e-3 * scale
