@@ -105,7 +105,7 @@ int lsc_debug_gemm_dev(const void* d_A, const void* d_W, const float* d_bias, co
     const __nv_bfloat16* R = static_cast<const __nv_bfloat16*>(d_residual);
     __nv_bfloat16* C = static_cast<__nv_bfloat16*>(d_C);
     if (impl == 1) {
-        int rc = gemm_ref_launch(A, W, d_bias, R, C, M, N, K, epilogue, st);
+        int rc = gemm_ref_launch(A, W, d_bias, R, C, M, N, K, epilogue, N, st);
         return rc < 0 ? rc : LSC_OK;
     }
     const int bn = gemm_tc_block_n(N);
@@ -118,7 +118,7 @@ int lsc_debug_gemm_dev(const void* d_A, const void* d_W, const float* d_bias, co
     LSC_TRY(make_tmap_bf16_sw128(&ta, A, M, K, 128));
     LSC_TRY(make_tmap_bf16_sw128(&tw, W, N, K, bn));
     LSC_TRY(make_tmap_bf16_store32(&tc, C, M, N));
-    int rc = gemm_tc_launch(ta, tw, tc, d_bias, R, M, N, K, epilogue, sms, st);
+    int rc = gemm_tc_launch(ta, tw, tc, d_bias, R, M, N, K, epilogue, N, sms, st);
     return rc < 0 ? rc : LSC_OK;
 }
 

@@ -4,8 +4,9 @@
 // (AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:194-196):
 // packing makes the mask implicit — only a sequence's own tokens are ever keys.
 //
-// One CTA per (sequence, head); K (bf16) and V (converted to fp16) of that head live in shared memory
-// for the CTA's lifetime; each warp owns 16 query rows at a time and streams key blocks of 64 with an
+// Layout of qkv: Q and K thirds bf16, V third fp16 (the QKV GEMM's epilogue writes it that way).
+// One CTA per (sequence, head); K (bf16) and V (fp16) of that head are copied to shared memory with
+// cp.async and stay there for the CTA's lifetime; each warp owns 16 query rows at a time and streams key blocks of 64 with an
 // online (flash-style) softmax.  d_head is 32 or 64, so the contraction depth per tile is tiny and the
 // kernel is bound by the exponentials and the instruction issue rate, not by the tensor pipe; it
 // therefore uses warp-level mma.sync.m16n8k16 (fp32 accumulate) rather than tcgen05, and spends its
@@ -62,11 +63,13 @@ __device__ __forceinline__ uint32_t exp2_f16x2(float lo, float hi) {
     asm("ex2.approx.f16x2 %0, %1;" : "=r"(r) : "r"(h));
     return r;
 }
-// bf16x2 -> fp16x2 (values of V are O(1): well inside fp16 range)
-__device__ __forceinline__ uint32_t bf16x2_to_f16x2(uint32_t w) {
-    uint32_t h;
-    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(bf16_hi(w)), "f"(bf16_lo(w)));
-    return h;
+__device__ __forceinline__ void cp_async_16(uint32_t smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
 template <int D>
@@ -86,33 +89,33 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
     const size_t row_stride = static_cast<size_t>(3) * H;
     const __nv_bfloat16* qbase = qkv + static_cast<size_t>(t0) * row_stride + head * D;
 
-    // ---- stage K (bf16) and V (fp16), zero-padded to a multiple of the key block ----
+    // ---- stage K (bf16) and V (fp16, written as such by the QKV GEMM) with cp.async; rows past the
+    //      sequence are zero-filled.  Two commit groups: the first QK^T only needs K. ----
     constexpr int CPR = D / 8;  // 16-byte chunks per row
+    const uint32_t sK_addr = smem_u32(sK), sV_addr = smem_u32(sV);
     for (int i = threadIdx.x; i < s_pad * CPR; i += ATT_THREADS) {
         const int r = i / CPR, c = i % CPR;
-        uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
-        if (r < s) {
-            const __nv_bfloat16* rp = qbase + static_cast<size_t>(r) * row_stride + c * 8;
-            kv = __ldg(reinterpret_cast<const uint4*>(rp + H));
-            vv = __ldg(reinterpret_cast<const uint4*>(rp + 2 * H));
-            vv.x = bf16x2_to_f16x2(vv.x);
-            vv.y = bf16x2_to_f16x2(vv.y);
-            vv.z = bf16x2_to_f16x2(vv.z);
-            vv.w = bf16x2_to_f16x2(vv.w);
-        }
-        *reinterpret_cast<uint4*>(sK + static_cast<size_t>(r) * LD + c * 8) = kv;
-        *reinterpret_cast<uint4*>(sV + static_cast<size_t>(r) * LD + c * 8) = vv;
+        const uint32_t dst = sK_addr + (r * LD + c * 8) * 2;
+        if (r < s) cp_async_16(dst, qbase + static_cast<size_t>(r) * row_stride + c * 8 + H);
+        else *reinterpret_cast<uint4*>(sK + static_cast<size_t>(r) * LD + c * 8) = make_uint4(0, 0, 0, 0);
     }
-    __syncthreads();
+    cp_async_commit();
+    for (int i = threadIdx.x; i < s_pad * CPR; i += ATT_THREADS) {
+        const int r = i / CPR, c = i % CPR;
+        const uint32_t dst = sV_addr + (r * LD + c * 8) * 2;
+        if (r < s) cp_async_16(dst, qbase + static_cast<size_t>(r) * row_stride + c * 8 + 2 * H);
+        else *reinterpret_cast<uint4*>(sV + static_cast<size_t>(r) * LD + c * 8) = make_uint4(0, 0, 0, 0);
+    }
+    cp_async_commit();
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, tq = lane & 3;
-    const uint32_t sK_addr = smem_u32(sK), sV_addr = smem_u32(sV);
     const int lm = lane >> 3, lr = lane & 7;  // ldmatrix: matrix index / row within matrix
     constexpr uint32_t ONES = 0x3C003C00u;    // fp16x2 (1, 1)
+    bool k_ready = false, v_ready = false;    // warp-uniform
 
     for (int qb = warp; qb * 16 < s; qb += ATT_THREADS / 32) {
-        // ---- Q fragments (A operand), straight from global ----
+        // ---- Q fragments (A operand), straight from global (overlaps the K/V copies) ----
         uint32_t qa[D / 16][4];
         const int r_lo = qb * 16 + g, r_hi = r_lo + 8;
 #pragma unroll
@@ -124,6 +127,11 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
             qa[ks][1] = r_hi < s ? __ldg(phi) : 0u;
             qa[ks][2] = r_lo < s ? __ldg(plo + 4) : 0u;
             qa[ks][3] = r_hi < s ? __ldg(phi + 4) : 0u;
+        }
+        if (!k_ready) {  // every warp passes each of the two barriers exactly once (here or after the loop)
+            cp_async_wait<1>();
+            __syncthreads();
+            k_ready = true;
         }
         // o[0..D/8) = output accumulators, o[D/8] = row sums (every column of that tile holds the sum)
         float o[D / 8 + 1][4];
@@ -189,6 +197,11 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
             }
             nms[0] = -m_run[0] * scale_log2e;
             nms[1] = -m_run[1] * scale_log2e;
+            if (!v_ready) {
+                cp_async_wait<0>();
+                __syncthreads();
+                v_ready = true;
+            }
             // ---- P = exp2(S*scale - max*scale) as packed fp16 A fragments; O += P V; sums += P 1 ----
 #pragma unroll
             for (int kk = 0; kk < KEY_BLOCK / 16; ++kk) {
@@ -222,6 +235,14 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
                 *reinterpret_cast<uint32_t*>(obase + static_cast<size_t>(r_hi) * H + c) =
                     pack_bf16x2(o[nt][2] * inv1, o[nt][3] * inv1);
         }
+    }
+    if (!k_ready) {  // warps without a query block still take part in the two barriers
+        cp_async_wait<1>();
+        __syncthreads();
+    }
+    if (!v_ready) {
+        cp_async_wait<0>();
+        __syncthreads();
     }
 }
 

@@ -90,16 +90,18 @@ int make_tmap_bf16_store32(CUtensorMap* out, const void* base, uint64_t rows, ui
 // ---- kernel launchers (defined in the .cu files) ---------------------------------------------
 enum GemmEpilogue { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESIDUAL = 2, EPI_DISCARD = 3 /* debug */, EPI_LOADONLY = 4 /* debug */ };
 
+// Output columns >= f16_from_col are written as fp16 instead of bf16 (pass N for "none"): the QKV GEMM
+// emits its V third in fp16, the operand type of the attention kernel's P·V product.
 // tcgen05 GEMM: C[M,N] = epi(A[M,K]·W[N,K]^T + bias).  tmapA: box 128 rows; tmapW: box BN rows,
 // where BN = gemm_tc_block_n(N).  Returns number of kernel launches (1) or <0 on error.
 int gemm_tc_block_n(int N);
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
                    const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,
-                   int num_sms, cudaStream_t stream);
+                   int f16_from_col, int num_sms, cudaStream_t stream);
 // CUDA-core validation GEMM (debug).
 int gemm_ref_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const float* bias,
                     const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,
-                    cudaStream_t stream);
+                    int f16_from_col, cudaStream_t stream);
 
 // word + position + token-type embedding gather, then LayerNorm -> bf16 [T,H].
 int embed_ln_launch(const int32_t* token_ids, const int32_t* cu_seqlens, int n_seq, int T, int H,

@@ -164,9 +164,9 @@ int ensure_staging(lsc_encoder* e, int64_t T, int64_t n_seq) {
 
 int gemm(lsc_encoder* e, const CUtensorMap& tmA, const __nv_bfloat16* A, const CUtensorMap& tmW,
          const __nv_bfloat16* W, const float* bias, const __nv_bfloat16* residual, const CUtensorMap& tmC,
-         __nv_bfloat16* C, int M, int N, int K, int epi, cudaStream_t st) {
-    if (e->cfg.gemm_impl == 1) return gemm_ref_launch(A, W, bias, residual, C, M, N, K, epi, st);
-    return gemm_tc_launch(tmA, tmW, tmC, bias, residual, M, N, K, epi, e->num_sms, st);
+         __nv_bfloat16* C, int M, int N, int K, int epi, int f16_from_col, cudaStream_t st) {
+    if (e->cfg.gemm_impl == 1) return gemm_ref_launch(A, W, bias, residual, C, M, N, K, epi, f16_from_col, st);
+    return gemm_tc_launch(tmA, tmW, tmC, bias, residual, M, N, K, epi, f16_from_col, e->num_sms, st);
 }
 
 #define LSC_LAUNCH(cls, expr)         \
@@ -200,12 +200,12 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                                    e->d_pos, e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, st));
         for (int l = 0; l < c.layers; ++l) {
             const LayerW& w = e->layers[l];
-            LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.b_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H, EPI_BIAS, st));
+            LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.b_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H, EPI_BIAS, 2 * H, st));
             LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, H, c.heads, max_seqlen, e->ctx, st));
-            LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, tc_tmp, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, st));
+            LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, tc_tmp, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, H, st));
             LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
-            LSC_LAUNCH(1, gemm(e, tm_x1, e->x1, w.tm_1, w.w_1, w.b_1, nullptr, tc_ffn, e->ffn, T, F, H, EPI_BIAS_GELU, st));
-            LSC_LAUNCH(1, gemm(e, tm_ffn, e->ffn, w.tm_2, w.w_2, w.b_2, e->x1, tc_tmp, e->tmp, T, H, F, EPI_BIAS_RESIDUAL, st));
+            LSC_LAUNCH(1, gemm(e, tm_x1, e->x1, w.tm_1, w.w_1, w.b_1, nullptr, tc_ffn, e->ffn, T, F, H, EPI_BIAS_GELU, F, st));
+            LSC_LAUNCH(1, gemm(e, tm_ffn, e->ffn, w.tm_2, w.w_2, w.b_2, e->x1, tc_tmp, e->tmp, T, H, F, EPI_BIAS_RESIDUAL, H, st));
             LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln2_g, w.ln2_b, c.ln_eps, e->x, T, H, st));
         }
     }

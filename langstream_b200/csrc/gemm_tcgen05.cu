@@ -11,6 +11,8 @@
 //   warps 2-9   epilogue: tcgen05.ld (thread = row) -> bias (+GELU | +residual) in fp32 -> bf16 ->
 //               32x32 blocks in swizzled smem -> TMA stores
 // Three mbarrier pipelines: smem full/empty (TMA <-> MMA) and TMEM full/empty (MMA <-> epilogue).
+#include <cuda_fp16.h>
+
 #include <cstdlib>
 
 #include "common.h"
@@ -107,7 +109,7 @@ template <int BN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
                const __grid_constant__ CUtensorMap tmapC, const float* __restrict__ bias,
-               const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int dbg) {
+               const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int f16_from_col, int dbg) {
     using cfg = Cfg<BN>;
     constexpr int STAGES = cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -292,6 +294,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 if (lane == 0) tma_store_wait_read<1>();
                 __syncwarp();
                 uint8_t* blk = stg + buf * 2048 + lane * 64;
+                const bool as_f16 = col_base + c * 32 >= f16_from_col;  // V third of the QKV output
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {  // 4 x 16 bytes = 8 columns each
                     const float4 b0 = __ldg(bp + 2 * i), b1 = __ldg(bp + 2 * i + 1);
@@ -311,10 +314,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                         }
                     }
                     uint4 o;
-                    o.x = pack_bf16x2(x[0], x[1]);
-                    o.y = pack_bf16x2(x[2], x[3]);
-                    o.z = pack_bf16x2(x[4], x[5]);
-                    o.w = pack_bf16x2(x[6], x[7]);
+                    if (as_f16) {
+                        o.x = pack_f16x2(x[0], x[1]);
+                        o.y = pack_f16x2(x[2], x[3]);
+                        o.z = pack_f16x2(x[4], x[5]);
+                        o.w = pack_f16x2(x[6], x[7]);
+                    } else {
+                        o.x = pack_bf16x2(x[0], x[1]);
+                        o.y = pack_bf16x2(x[2], x[3]);
+                        o.z = pack_bf16x2(x[4], x[5]);
+                        o.w = pack_bf16x2(x[6], x[7]);
+                    }
                     if (!(dbg & 2) || o.x == 0x7fc07fc0u) *reinterpret_cast<uint4*>(blk + ((static_cast<uint32_t>(i) ^ sw) * 16)) = o;
                 }
                 if (!(dbg & 8)) fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA engine
@@ -346,7 +356,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 
 template <int BN, int EPI>
 int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
-                const __nv_bfloat16* residual, int M, int N, int K, int num_sms, cudaStream_t stream) {
+                const __nv_bfloat16* residual, int M, int N, int K, int f16_from_col, int num_sms, cudaStream_t stream) {
     using cfg = Cfg<BN>;
     static bool configured[64] = {};  // per instantiation and per device
     auto kern = gemm_tc_kernel<BN, EPI>;
@@ -361,27 +371,27 @@ int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtens
     const int num_tiles = m_tiles * (N / BN);
     const int grid = num_tiles < num_sms ? num_tiles : num_sms;
     static const int dbg = [] { const char* e = getenv("LSC_GEMM_DBG"); return e ? atoi(e) : 0; }();
-    kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, dbg);
+    kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, dbg);
     LSC_CUDA(cudaGetLastError());
     return 1;
 }
 
 template <int BN>
 int launch_bn(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
-              const __nv_bfloat16* residual, int M, int N, int K, int epilogue, int num_sms,
+              const __nv_bfloat16* residual, int M, int N, int K, int epilogue, int f16_from_col, int num_sms,
               cudaStream_t stream) {
     switch (epilogue) {
         case EPI_BIAS:
-            return launch_inst<BN, EPI_BIAS>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
+            return launch_inst<BN, EPI_BIAS>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
         case EPI_BIAS_GELU:
-            return launch_inst<BN, EPI_BIAS_GELU>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
+            return launch_inst<BN, EPI_BIAS_GELU>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
         case EPI_BIAS_RESIDUAL:
             if (residual == nullptr) return fail(LSC_E_INVALID, "gemm: residual epilogue without residual");
-            return launch_inst<BN, EPI_BIAS_RESIDUAL>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
+            return launch_inst<BN, EPI_BIAS_RESIDUAL>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
         case EPI_DISCARD:
-            return launch_inst<BN, EPI_DISCARD>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
+            return launch_inst<BN, EPI_DISCARD>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
         case EPI_LOADONLY:
-            return launch_inst<BN, EPI_LOADONLY>(tmapA, tmapW, tmapC, bias, residual, M, N, K, num_sms, stream);
+            return launch_inst<BN, EPI_LOADONLY>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
         default:
             return fail(LSC_E_INVALID, "gemm: unknown epilogue");
     }
@@ -404,17 +414,17 @@ int gemm_tc_block_n(int N) {
 
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
                    const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,
-                   int num_sms, cudaStream_t stream) {
+                   int f16_from_col, int num_sms, cudaStream_t stream) {
     if (M <= 0) return 0;
     if (K % BK != 0 || K <= 0) return fail(LSC_E_UNSUPPORTED, "gemm: K must be a positive multiple of 64");
     if (bias == nullptr) return fail(LSC_E_INVALID, "gemm: bias is required");
     switch (gemm_tc_block_n(N)) {
         case 192:
-            return launch_bn<192>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, num_sms, stream);
+            return launch_bn<192>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, num_sms, stream);
         case 256:
-            return launch_bn<256>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, num_sms, stream);
+            return launch_bn<256>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, num_sms, stream);
         case 128:
-            return launch_bn<128>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, num_sms, stream);
+            return launch_bn<128>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, num_sms, stream);
         default:
             return fail(LSC_E_UNSUPPORTED, "gemm: N must be a multiple of 128");
     }
@@ -429,7 +439,7 @@ template <int EPI>
 __global__ void __launch_bounds__(256)
 gemm_ref_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __restrict__ W,
                 const float* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
-                __nv_bfloat16* __restrict__ C, int M, int N, int K) {
+                __nv_bfloat16* __restrict__ C, int M, int N, int K, int f16_from_col) {
     __shared__ float sA[16][64 + 1];
     __shared__ float sW[16][64 + 1];
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -467,7 +477,10 @@ gemm_ref_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __rest
             float x = acc[i][j] + bias[gn];
             if (EPI == EPI_BIAS_GELU) x = gelu_erf(x);
             if (EPI == EPI_BIAS_RESIDUAL) x += __bfloat162float(residual[static_cast<size_t>(gm) * N + gn]);
-            C[static_cast<size_t>(gm) * N + gn] = __float2bfloat16_rn(x);
+            if (gn >= f16_from_col)
+                reinterpret_cast<__half*>(C)[static_cast<size_t>(gm) * N + gn] = __float2half_rn(x);
+            else
+                C[static_cast<size_t>(gm) * N + gn] = __float2bfloat16_rn(x);
         }
     }
 }
@@ -476,19 +489,19 @@ gemm_ref_kernel(const __nv_bfloat16* __restrict__ A, const __nv_bfloat16* __rest
 
 int gemm_ref_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const float* bias,
                     const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,
-                    cudaStream_t stream) {
+                    int f16_from_col, cudaStream_t stream) {
     if (M <= 0) return 0;
     dim3 grid((N + 63) / 64, (M + 63) / 64);
     switch (epilogue) {
         case EPI_BIAS:
-            gemm_ref_kernel<EPI_BIAS><<<grid, 256, 0, stream>>>(A, W, bias, residual, C, M, N, K);
+            gemm_ref_kernel<EPI_BIAS><<<grid, 256, 0, stream>>>(A, W, bias, residual, C, M, N, K, f16_from_col);
             break;
         case EPI_BIAS_GELU:
-            gemm_ref_kernel<EPI_BIAS_GELU><<<grid, 256, 0, stream>>>(A, W, bias, residual, C, M, N, K);
+            gemm_ref_kernel<EPI_BIAS_GELU><<<grid, 256, 0, stream>>>(A, W, bias, residual, C, M, N, K, f16_from_col);
             break;
         case EPI_BIAS_RESIDUAL:
             if (residual == nullptr) return fail(LSC_E_INVALID, "gemm: residual epilogue without residual");
-            gemm_ref_kernel<EPI_BIAS_RESIDUAL><<<grid, 256, 0, stream>>>(A, W, bias, residual, C, M, N, K);
+            gemm_ref_kernel<EPI_BIAS_RESIDUAL><<<grid, 256, 0, stream>>>(A, W, bias, residual, C, M, N, K, f16_from_col);
             break;
         default:
             return fail(LSC_E_INVALID, "gemm: unknown epilogue");
