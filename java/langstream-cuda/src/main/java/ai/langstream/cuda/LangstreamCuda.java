@@ -1,0 +1,54 @@
+package ai.langstream.cuda;
+
+import java.nio.ByteBuffer;
+import java.nio.FloatBuffer;
+import java.nio.IntBuffer;
+import java.nio.LongBuffer;
+
+/**
+ * One-to-one JNI surface over include/langstream_cuda.h. All buffers must be DIRECT buffers in native
+ * byte order; handles are opaque pointers carried as long. Every method throws
+ * IllegalArgumentException (LSC_E_INVALID, LSC_E_TOO_LONG) or RuntimeException (anything else) with the
+ * text of lsc_last_error().
+ */
+public final class LangstreamCuda {
+    static {
+        NativeLoader.loadOnce("langstream_cuda", "langstream_cuda_jni");
+    }
+
+    private LangstreamCuda() {}
+
+    public static native String version();
+
+    public static native int deviceCount();
+
+    // ---- encoder (replaces DJL Criteria.loadModel / Predictor.predict) ----
+    public static native long encoderCreate(
+            int layers, int hidden, int heads, int ffn, int vocab, int maxPosition, int typeVocab,
+            float lnEps, ByteBuffer weightsFp32, int device);
+
+    public static native void encoderEmbed(
+            long encoder, IntBuffer tokenIds, IntBuffer cuSeqlens, int nSeq, FloatBuffer out);
+
+    public static native int encoderDim(long encoder);
+
+    public static native void encoderDestroy(long encoder);
+
+    // ---- vector index (replaces the HerdDB table and its cosine ORDER BY scan) ----
+    public static native long indexCreate(int dim, long capacity, int device);
+
+    public static native void indexUpsert(long index, LongBuffer ids, FloatBuffer vectors, int n);
+
+    public static native void indexDelete(long index, LongBuffer ids, int n);
+
+    public static native long indexSize(long index);
+
+    public static native void indexSearch(
+            long index, FloatBuffer queries, int b, int k, LongBuffer outIds, FloatBuffer outScores);
+
+    public static native void indexSave(long index, String path);
+
+    public static native long indexLoad(String path, int device);
+
+    public static native void indexDestroy(long index);
+}

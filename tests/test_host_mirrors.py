@@ -1,0 +1,164 @@
+"""Host-side mirrors of the reference SPI (CPU: fakes built on the oracle stand in for the GPU handles).
+The flows follow the reference's own tests: ComputeAIEmbeddingsTest / HuggingFaceEmbeddingServiceTest
+(index alignment, dimension), JdbcWriterTest (upsert / update / delete round trip) and
+RerankAgentRunnerIT (sink -> cosine SQL -> MMR)."""
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from fakes import FakeEncoder, FakeIndex
+
+GOLDEN = Path(__file__).parent / "golden"
+
+
+@pytest.fixture()
+def fake_tables():
+    from langstream_b200 import vector
+
+    yield lambda d, dev: FakeIndex(d, dev)
+    for name in list(vector._TABLES):
+        vector.drop_table(name)
+
+
+def test_provider_lookup_and_config_errors():
+    from langstream_b200.embeddings import CudaServiceProviderProvider
+
+    p = CudaServiceProviderProvider()
+    assert p.supports({"cuda": {"device": 0}}) and not p.supports({"huggingface": {}})
+    sp = p.create_implementation({"cuda": {"device": 0}})
+    with pytest.raises(ValueError):
+        sp.get_completions_service({})          # like the no-op provider: no completions here
+    with pytest.raises(ValueError):
+        sp.get_embeddings_service({"model": "no-such-model"})
+    with pytest.raises(PermissionError):       # ALLOWED_HF_URLS semantics: only file:// is allowed
+        sp.get_embeddings_service({"model": "all-MiniLM-L6-v2", "model-url": "http://example.com/w.npy"})
+
+
+def test_embeddings_service_alignment_batching_and_errors():
+    from langstream_b200 import weights as W
+    from langstream_b200.embeddings import CudaEmbeddingsService, HashingTokenizer
+    from oracle.encoder_oracle import bert_numpy
+
+    spec = W.TINY
+    blob = W.random_init(spec, 3, True)
+    enc = FakeEncoder(spec, blob)
+    svc = CudaEmbeddingsService(spec, blob, encoder_factory=lambda: enc, max_batch=64, flush_interval_ms=30)
+    texts_a = ["something to embed", "another text"]            # HuggingFaceEmbeddingServiceTest: 2 texts
+    texts_b = ["a b c d e", "", "x"]
+    fa, fb = svc.compute_embeddings(texts_a), svc.compute_embeddings(texts_b)
+    ra, rb = fa.result(timeout=30), fb.result(timeout=30)
+    assert len(ra) == 2 and len(rb) == 3 and all(len(v) == spec.hidden for v in ra + rb)
+    assert isinstance(ra[0][0], float)                           # List<List<Double>>
+    assert enc.calls == [5]                                      # both callers merged into ONE pass
+    tok = HashingTokenizer(spec.vocab, spec.max_position)
+    ids = tok(texts_a + texts_b)
+    cu = np.concatenate([[0], np.cumsum([len(s) for s in ids])]).astype(np.int32)
+    want = bert_numpy(spec, blob, np.concatenate(ids).astype(np.int32), cu, dtype=np.float32)
+    assert np.allclose(np.array(ra + rb), want, atol=1e-6)       # index-aligned with the inputs
+    assert svc.compute_embeddings([]).result(timeout=5) == []
+    # a failing batch fails the future, it does not raise (AbstractHuggingFaceEmbeddingService.java:213-223)
+    svc.tokenizer = lambda texts: [[1] * (spec.max_position + 5) for _ in texts]
+    f = svc.compute_embeddings(["too long"])
+    with pytest.raises(RuntimeError, match="failed to compute embeddings"):
+        f.result(timeout=30)
+    assert "number of tokens is too high" in str(f.exception().__cause__)
+    svc.close()
+
+
+def test_expression_evaluation_subset():
+    from langstream_b200.vector import Record, evaluate
+
+    r = Record(key={"name": "doc1"}, value={"text": "t", "chunk": {"id": 7}, "embeddings": [1.5, 2, 3]},
+               headers={"h": "v"})
+    assert evaluate("value.text", r) == "t" and evaluate("value.chunk.id", r) == 7
+    assert evaluate("key.name", r) == "doc1" and evaluate("properties.h", r) == "v"
+    assert evaluate("fn:toListOfFloat(value.embeddings)", r) == [1.5, 2.0, 3.0]
+    assert evaluate("fn:toListOfFloat(value.missing)", r) is None
+    assert evaluate("value.missing.deeper", r) is None
+    assert evaluate("value.text", Record(value=json.dumps({"text": "from json"}))) == "from json"
+    with pytest.raises(ValueError):
+        evaluate("unknown.root", r)
+
+
+def test_writer_round_trip_like_jdbc_writer_test(fake_tables):
+    """JdbcWriterTest.java:49-176: insert a row, query it with the cosine SQL, update it, delete it."""
+    from langstream_b200.vector import (CudaVectorDataSourceProvider, CudaVectorDatabaseWriterProvider, Record)
+
+    ds_cfg = {"service": "cuda"}
+    wp = CudaVectorDatabaseWriterProvider(fake_tables)
+    assert wp.supports(ds_cfg) and not wp.supports({"service": "jdbc"})
+    w = wp.create_implementation(ds_cfg)
+    w.initialise({"table-name": "documents", "fields": [
+        {"name": "name", "expression": "key.name", "primary-key": True},
+        {"name": "vector", "expression": "fn:toListOfFloat(value.vector)"},
+        {"name": "text", "expression": "value.text"},
+        {"name": "chunk_id", "expression": "value.chunk_id"}]})
+    vec = [float(i) for i in range(32)]
+    rec = Record(key={"name": "do'c1"}, value={"vector": vec, "text": "Lorem ipsum...", "chunk_id": 1})
+    assert w.upsert(rec, {}).result(timeout=5) is None
+    ds = CudaVectorDataSourceProvider(fake_tables).create_data_source_implementation(ds_cfg)
+    ds.initialize(ds_cfg)
+    sql = "SELECT chunk_id,name,text FROM documents ORDER BY cosine_similarity(vector,cast(? as float array)) DESC LIMIT 10"
+    rows = ds.fetch_data(sql, [vec])
+    assert rows == [{"chunk_id": 1, "name": "do'c1", "text": "Lorem ipsum..."}]
+    w.upsert(Record(key={"name": "do'c1"}, value={"vector": vec, "text": "Lorem ipsum changed...", "chunk_id": 1}), {}).result(5)
+    assert ds.fetch_data(sql, [vec])[0]["text"] == "Lorem ipsum changed..."
+    w.upsert(Record(key={"name": "do'c1"}, value=None), {}).result(5)   # null value => delete
+    assert ds.fetch_data(sql, [vec]) == []
+    # errors complete the future exceptionally instead of raising (JdbcWriter.java:175-177)
+    bad = w.upsert(Record(key={"name": "x"}, value={"vector": [1.0, 2.0], "text": "t", "chunk_id": 2}), {})
+    assert isinstance(bad.exception(timeout=5), ValueError)
+    with pytest.raises(ValueError):
+        ds.fetch_data("DROP TABLE documents", [])
+    w.upsert(rec, {}).result(5)
+    with pytest.raises(ValueError):
+        ds.fetch_data("SELECT nope FROM documents ORDER BY cosine_similarity(vector,cast(? as float array)) DESC LIMIT 1", [vec])
+
+
+def test_rerank_it_pipeline_on_host_mirrors(fake_tables):
+    """RerankAgentRunnerIT.java:95-264 end to end: vector-db-sink x10 -> query-vector-db with the
+    reference's exact SQL -> MMR re-rank -> the exact expected documents, vectors returned unchanged."""
+    from langstream_b200.vector import CudaVectorDataSource, CudaVectorDatabaseWriter, Record
+    from oracle import rerank_oracle
+
+    fx = json.loads((GOLDEN / "rerank_it.json").read_text())
+    w = CudaVectorDatabaseWriter({"service": "cuda"}, fake_tables)
+    w.initialise({"table-name": "documents", "fields": [
+        {"name": "filename", "expression": "value.filename", "primary-key": True},
+        {"name": "chunk_id", "expression": "value.chunk_id", "primary-key": True},
+        {"name": "embeddings_vector", "expression": "fn:toListOfFloat(value.embeddings_vector)"},
+        {"name": "text", "expression": "value.text"}]})
+    for i, r in enumerate(fx["rows"]):
+        msg = {"filename": f"doc{i}.pdf", "chunk_id": 1, "embeddings_vector": r["embeddings_vector"],
+               "language": "en", "text": r["text"], "chunk_num_tokens": 10}
+        w.upsert(Record(value=json.dumps(msg)), {}).result(5)
+    ds = CudaVectorDataSource(fake_tables)
+    related = ds.fetch_data(fx["sql"], [fx["query_embeddings"]])
+    assert len(related) == 10 and related[0] == {"text": "text1", "embeddings_vector": [1.0, 2.0, 3.0, 4.0, 5.0]}
+    docs = [(d["text"], np.array(d["embeddings_vector"], np.float32)) for d in related]
+    m = fx["mmr"]
+    order = rerank_oracle.rerank_mmr(docs, int(m["max"]), fx["query_text"], m["lambda"], m["k1"], m["b"])
+    assert [related[i] for i in order] == fx["expected_related_documents"]
+    # the JSON query form returns the same rows plus the similarity column
+    q = json.dumps({"table": "documents", "vector": "?", "topK": 3, "select": ["text"]}).replace('"?"', "?")
+    top3 = ds.fetch_data(q, [fx["query_embeddings"]])
+    assert [r["text"] for r in top3] == [r["text"] for r in related[:3]] and "similarity" in top3[0]
+
+
+def test_split_by_tokens_covers_everything_once():
+    from langstream_b200.distributed import shard_rows, split_by_tokens
+
+    rng = np.random.default_rng(0)
+    for world in (1, 2, 3, 8):
+        lens = rng.integers(0, 129, size=200)
+        cu = np.concatenate([[0], np.cumsum(lens)])
+        parts = split_by_tokens(cu, world)
+        assert parts[0][0] == 0 and parts[-1][1] == 200
+        assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
+        tokens = [cu[e] - cu[s] for s, e in parts]
+        assert max(tokens) - min(tokens) <= 2 * 128          # balanced to within one sequence or two
+        rows = [shard_rows(1000003, world, r) for r in range(world)]
+        assert rows[0][0] == 0 and rows[-1][1] == 1000003 and all(a[1] == b[0] for a, b in zip(rows, rows[1:]))
+    assert split_by_tokens(np.array([0]), 4) == [(0, 0)] * 4   # empty batch

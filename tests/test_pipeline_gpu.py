@@ -1,0 +1,67 @@
+"""The host mirrors on the real CUDA handles: the reference's RerankAgentRunnerIT flow
+(vector-db-sink -> query-vector-db with the reference's SQL -> MMR) and the embeddings service."""
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+GOLDEN = Path(__file__).parent / "golden"
+
+
+def test_rerank_it_pipeline_on_gpu(native_lib, cuda_device):
+    from langstream_b200 import vector
+    from langstream_b200.vector import CudaVectorDataSource, CudaVectorDatabaseWriter, Record
+    from oracle import rerank_oracle
+
+    fx = json.loads((GOLDEN / "rerank_it.json").read_text())
+    vector.drop_table("documents")
+    w = CudaVectorDatabaseWriter({"service": "cuda", "device": 0})
+    w.initialise({"table-name": "documents", "fields": [
+        {"name": "filename", "expression": "value.filename", "primary-key": True},
+        {"name": "chunk_id", "expression": "value.chunk_id", "primary-key": True},
+        {"name": "embeddings_vector", "expression": "fn:toListOfFloat(value.embeddings_vector)"},
+        {"name": "text", "expression": "value.text"}]})
+    for i, r in enumerate(fx["rows"]):
+        msg = {"filename": f"doc{i}.pdf", "chunk_id": 1, "embeddings_vector": r["embeddings_vector"],
+               "language": "en", "text": r["text"], "chunk_num_tokens": 10}
+        assert w.upsert(Record(value=json.dumps(msg)), {}).result(30) is None
+    ds = CudaVectorDataSource()
+    ds.initialize({"service": "cuda"})
+    related = ds.fetch_data(fx["sql"], [fx["query_embeddings"]])
+    assert len(related) == 10
+    assert related[0] == {"text": "text1", "embeddings_vector": [1.0, 2.0, 3.0, 4.0, 5.0]}
+    docs = [(d["text"], np.array(d["embeddings_vector"], np.float32)) for d in related]
+    m = fx["mmr"]
+    order = rerank_oracle.rerank_mmr(docs, int(m["max"]), fx["query_text"], m["lambda"], m["k1"], m["b"])
+    assert [related[i] for i in order] == fx["expected_related_documents"]
+    # delete on null value, then the row is gone
+    w.upsert(Record(value=None, key=None), {})  # pk evaluates to (None, None): unknown -> ignored
+    assert len(ds.fetch_data(fx["sql"], [fx["query_embeddings"]])) == 10
+    vector.drop_table("documents")
+
+
+def test_embeddings_service_on_gpu(native_lib, cuda_device):
+    """HuggingFaceEmbeddingServiceTest.java:27-44: two texts -> two vectors of the model dimension;
+    here also checked against the oracle on the same tokens."""
+    from langstream_b200 import weights as W
+    from langstream_b200.embeddings import CudaServiceProviderProvider, HashingTokenizer
+    from oracle.encoder_oracle import bert_numpy
+
+    provider = CudaServiceProviderProvider().create_implementation({"cuda": {"device": 0}})
+    svc = provider.get_embeddings_service({"model": "all-MiniLM-L6-v2", "options": {"random-init-seed": 0},
+                                           "batch-size": 64, "flush-interval": 5})
+    texts = ["something to embed", "A second, somewhat longer text with a few more words in it."]
+    futures = [svc.compute_embeddings([t]) for t in texts] + [svc.compute_embeddings(texts)]
+    res = [f.result(timeout=60) for f in futures]
+    assert [len(r) for r in res] == [1, 1, 2] and all(len(v) == 384 for r in res for v in r)
+    assert np.allclose(res[0][0], res[2][0], atol=1e-6) and np.allclose(res[1][0], res[2][1], atol=1e-6)
+    spec = W.MINILM_L6
+    ids = HashingTokenizer(spec.vocab, spec.max_position)(texts)
+    cu = np.concatenate([[0], np.cumsum([len(s) for s in ids])]).astype(np.int32)
+    want = bert_numpy(spec, W.random_init(spec, 0), np.concatenate(ids).astype(np.int32), cu, dtype=np.float32)
+    got = np.array(res[2], np.float32)
+    cos = (got * want).sum(1) / (np.linalg.norm(got, axis=1) * np.linalg.norm(want, axis=1))
+    assert cos.min() >= 0.999 and np.abs(got - want).max() <= 2e-3
+    provider.close()
