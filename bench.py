@@ -35,6 +35,24 @@ TOPK_K = 10
 FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
 
 
+_REAL_STDOUT = None
+
+
+def capture_stdout():
+    """Rank 0 must print exactly ONE line on stdout, but libraries write there too (NCCL prints its
+    version banner from C).  Point fd 1 at stderr for the run and keep the real stdout for emit()."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def peaks():
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -161,7 +179,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "embeddings/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -371,7 +389,7 @@ def run_cuda(args):
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
             "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "topk": topk,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     enc.close()
     if world > 1:
         dist.destroy_process_group()
@@ -395,6 +413,7 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29531", __file__] + sys.argv[1:]
         return subprocess.call(cmd)
+    capture_stdout()
     if args.impl == "reference":
         return run_reference(args)
     return run_cuda(args)
