@@ -10,11 +10,14 @@
 //              (SWIZZLE_128B, L2 evict-first) through a 4-stage smem ring
 //   warp 1     tcgen05.mma, M = 128 query rows (zero padded), N = 256 corpus rows, fp32 scores in
 //              TMEM, two accumulator stages
-//   warps 2-5  selection: thread q owns query q (TMEM lane q) and walks the 256 scores of the tile
-//              keeping its k best in a private sorted list; a chunk of 32 scores is skipped with one
-//              max-reduction when nothing beats the current k-th score
+//   warps 2-9  selection: thread q owns query q (TMEM lane q); the two warps of a lane quadrant each walk
+//              one half (128 columns) of the tile's scores keeping their k best in a private sorted
+//              list; a chunk of 32 scores is skipped with one max-reduction when nothing beats the
+//              current k-th score; the two halves are merged through shared memory at the end
 // Each CTA then writes its [128][k] candidates to scratch and topk_merge_kernel merges the per-CTA
 // lists (a k-way merge over sorted heads) into the final [B][k] ids and scores.
+#include <cstdlib>
+
 #include "common.h"
 #include "ptx.cuh"
 #include "topk.h"
@@ -23,7 +26,7 @@ namespace lsc {
 
 namespace {
 
-constexpr int TK_THREADS = 192;
+// threads = 64 + EW * 32: warp 0 TMA, warp 1 MMA, EW selection warps (8 or 16)
 constexpr int TK_BN = 256;
 constexpr int TK_BK = 64;
 constexpr int TK_ACC_STRIDE = 256;
@@ -32,23 +35,25 @@ constexpr int TK_STAGE_BYTES = TK_BN * TK_BK * 2;  // 32 KB
 constexpr int TK_QBLK_BYTES = TK_QROWS * TK_BK * 2;  // 16 KB per 64-dim slice of the query block
 constexpr int TK_MAX_STAGES = 6;
 
-template <int KCAP>
-__device__ __noinline__ void list_insert(float* ls, int32_t* li, int& cnt, float& thr, int k, float s,
-                                         int32_t idx) {
-    int pos = cnt < k ? cnt : k - 1;
-    while (pos > 0 && ls[pos - 1] < s) {
-        ls[pos] = ls[pos - 1];
-        li[pos] = li[pos - 1];
+// Per-query sorted (best first) list of the k best rows so far, in (L1-resident) local memory; empty
+// slots hold (-inf, -1).  tie=false: the new row goes after every listed row with an equal score
+// (the scan feeds rows in increasing order) — "ties by lower row" without index compares;
+// tie=true compares row numbers explicitly (used where rows do not arrive in order).
+__device__ __noinline__ void list_insert_mem(float* s, int32_t* i, int k, float v, int32_t idx, bool tie) {
+    auto before = [&](int j) { return s[j] > v || (s[j] == v && (!tie || (i[j] >= 0 && i[j] < idx))); };
+    if (before(k - 1)) return;
+    int pos = k - 1;
+    while (pos > 0 && !before(pos - 1)) {
+        s[pos] = s[pos - 1];
+        i[pos] = i[pos - 1];
         --pos;
     }
-    ls[pos] = s;
-    li[pos] = idx;
-    if (cnt < k) ++cnt;
-    thr = cnt == k ? ls[k - 1] : -INFINITY;
+    s[pos] = v;
+    i[pos] = idx;
 }
 
-template <int KCAP>
-__global__ void __launch_bounds__(TK_THREADS, 1)
+template <int KCAP, int EW>
+__global__ void __launch_bounds__(64 + EW * 32, 1)
 topk_scan_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constant__ CUtensorMap tmapC,
                  int q_row0, int nq, int n_rows, int dim, int k, int stages,
                  float* __restrict__ cand_scores, int32_t* __restrict__ cand_idx) {
@@ -78,7 +83,7 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constan
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
-            mbar_init(bar_tempty + 8 * a, 4);
+            mbar_init(bar_tempty + 8 * a, EW);
         }
         mbar_init(bar_q, 1);
         fence_mbar_init();
@@ -148,41 +153,60 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constan
             }
         }
     } else {
+        // Selection: EW/4 warps per TMEM lane quadrant, each walking its share of the columns of every
+        // 256-row score tile for the same 32 queries; thread = query.
+        constexpr int PARTS = EW / 4;
+        constexpr int PCOLS = TK_BN / PARTS;
         const int quad = warp & 3;
+        const int half = (warp - 2) >> 2;  // which column part
         const int q = quad * 32 + lane;        // query (TMEM lane) owned by this thread
         const bool active = q < nq;
         const bool warp_active = quad * 32 < nq;
         float ls[KCAP];
         int32_t li[KCAP];
-        int cnt = 0;
-        float thr = -INFINITY;
+        for (int j = 0; j < k; ++j) {
+            ls[j] = -INFINITY;
+            li[j] = -1;
+        }
+        float thr = -INFINITY;  // current k-th best score of this query
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             mbar_wait(bar_tfull + 8 * acc, acc_phase);
             tc_fence_after();
             if (warp_active) {
-                const int row_base = tile * TK_BN;
-#pragma unroll 1
-                for (int c = 0; c < TK_BN / 32; ++c) {
-                    uint32_t v[32];
-                    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
-                                           acc * TK_ACC_STRIDE + c * 32;
-                    tmem_ld_32x32(taddr, v);
+                const int col0 = half * PCOLS;
+                const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
+                                       acc * TK_ACC_STRIDE + col0;
+                uint32_t va[32], vb[32];
+                tmem_ld_32x32(tbase, va);
+#pragma unroll
+                for (int c = 0; c < PCOLS / 32; ++c) {
+                    uint32_t(&v)[32] = (c & 1) ? vb : va;
+                    uint32_t(&vnext)[32] = (c & 1) ? va : vb;
                     tmem_ld_wait();
-                    const int r0 = row_base + c * 32;
+                    if (c + 1 < PCOLS / 32) tmem_ld_32x32(tbase + (c + 1) * 32, vnext);
+                    const int r0 = tile * TK_BN + col0 + c * 32;
                     const int nvalid = n_rows - r0;  // rows past n_rows are not candidates
                     if (active && nvalid > 0) {
-                        float mx = -INFINITY;
+                        // max tree of the chunk: one comparison against the k-th best rejects it
+                        float m[16];
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            mx = fmaxf(mx, j < nvalid ? __uint_as_float(v[j]) : -INFINITY);
-                        if (mx > thr) {
+                        for (int j = 0; j < 16; ++j)
+                            m[j] = fmaxf(j < nvalid ? __uint_as_float(v[j]) : -INFINITY,
+                                         j + 16 < nvalid ? __uint_as_float(v[j + 16]) : -INFINITY);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], m[j + 8]);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) m[j] = fmaxf(m[j], m[j + 4]);
+                        if (fmaxf(fmaxf(m[0], m[2]), fmaxf(m[1], m[3])) > thr) {
 #pragma unroll
                             for (int j = 0; j < 32; ++j) {
-                                const float s = __uint_as_float(v[j]);
-                                if (j < nvalid && s > thr)
-                                    list_insert<KCAP>(ls, li, cnt, thr, k, s, r0 + j);
+                                const float sc = __uint_as_float(v[j]);
+                                if (j < nvalid && sc > thr) {
+                                    list_insert_mem(ls, li, k, sc, r0 + j, false);
+                                    thr = ls[k - 1];
+                                }
                             }
                         }
                     }
@@ -194,11 +218,34 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constan
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
-        if (active) {
+        // ---- combine the two column halves of each query inside the CTA, then write [128][k] ----
+        // The smem ring is idle now (every TMA load has been consumed by an MMA that completed before
+        // the last tfull arrival), so it serves as the exchange buffer: [128][k] (score, row) pairs.
+        float* xs = reinterpret_cast<float*>(smem);  // queries and ring are both dead by now
+        int32_t* xi = reinterpret_cast<int32_t*>(xs + (PARTS - 1) * TK_QROWS * k);
+        asm volatile("bar.sync 1, %0;" ::"n"(EW * 32));  // all selection warps are past their last tile
+        if (half > 0 && active) {
+            for (int j = 0; j < k; ++j) {
+                xs[((half - 1) * TK_QROWS + q) * k + j] = ls[j];
+                xi[((half - 1) * TK_QROWS + q) * k + j] = li[j];
+            }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(EW * 32));
+        if (half == 0 && active) {
+            for (int j = 0; j < (PARTS - 1) * k; ++j) {
+                const int src = (j / k) * TK_QROWS * k + q * k + (j % k);
+                const float sc = xs[src];
+                const int32_t idx = xi[src];
+                // the other half holds rows interleaved with ours: order equal scores by row number
+                if (idx >= 0 && sc >= thr) {
+                    list_insert_mem(ls, li, k, sc, idx, true);
+                    thr = ls[k - 1];
+                }
+            }
             const size_t base = (static_cast<size_t>(blockIdx.x) * TK_QROWS + q) * k;
-            for (int i = 0; i < k; ++i) {
-                cand_scores[base + i] = i < cnt ? ls[i] : -INFINITY;
-                cand_idx[base + i] = i < cnt ? li[i] : -1;
+            for (int j = 0; j < k; ++j) {
+                cand_scores[base + j] = ls[j];
+                cand_idx[base + j] = li[j];
             }
         }
     }
@@ -383,13 +430,13 @@ __global__ void fill_empty_kernel(int64_t* ids, float* scores, size_t n) {
     }
 }
 
-template <int KCAP>
+template <int KCAP, int EW>
 int scan_inst(const CUtensorMap& tmapQ, const CUtensorMap& tmapC, int q_row0, int nq, int n_rows,
               int dim, int k, int stages, size_t smem, int grid, float* cand_scores, int32_t* cand_idx,
               cudaStream_t stream) {
-    auto kern = topk_scan_kernel<KCAP>;
+    auto kern = topk_scan_kernel<KCAP, EW>;
     LSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    kern<<<grid, TK_THREADS, smem, stream>>>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, cand_scores,
+    kern<<<grid, 64 + EW * 32, smem, stream>>>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, cand_scores,
                                              cand_idx);
     LSC_CUDA(cudaGetLastError());
     return 1;
@@ -413,9 +460,15 @@ int topk_scan_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC, int q_r
     if (stages > TK_MAX_STAGES) stages = TK_MAX_STAGES;
     if (stages < 2) return fail(LSC_E_UNSUPPORTED, "top-k: dim too large for the shared-memory ring");
     const size_t smem = static_cast<size_t>(q_bytes) + static_cast<size_t>(stages) * TK_STAGE_BYTES + 256 + 1024;
-    if (k <= 16) return scan_inst<16>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
-    if (k <= 32) return scan_inst<32>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
-    return scan_inst<128>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+    static const int ew = [] { const char* e = getenv("LSC_TOPK_WARPS"); return e ? atoi(e) : 8; }();
+    if (ew == 16) {
+        if (k <= 16) return scan_inst<16, 16>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+        if (k <= 32) return scan_inst<32, 16>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+        return scan_inst<128, 16>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+    }
+    if (k <= 16) return scan_inst<16, 8>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+    if (k <= 32) return scan_inst<32, 8>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
+    return scan_inst<128, 8>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, smem, grid, cand_scores, cand_idx, stream);
 }
 
 int topk_merge_scan_launch(const float* cand_scores, const int32_t* cand_idx, int parts, int B, int k,
