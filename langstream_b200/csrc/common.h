@@ -88,7 +88,32 @@ int make_tmap_bf16_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint
 int make_tmap_bf16_store32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols);
 
 // ---- kernel launchers (defined in the .cu files) ---------------------------------------------
-enum GemmEpilogue { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESIDUAL = 2, EPI_DISCARD = 3 /* debug */, EPI_LOADONLY = 4 /* debug */ };
+enum GemmEpilogue {
+    EPI_BIAS = 0,           // C = A.W^T + bias
+    EPI_BIAS_GELU = 1,      // C = gelu(A.W^T + bias)
+    EPI_BIAS_RESIDUAL = 2,  // C = A.W^T + bias + residual
+    EPI_DISCARD = 3,        // debug: main loop only
+    EPI_LOADONLY = 4,       // debug: main loop + TMEM reads
+    EPI_LNIN_BIAS = 5,      // C = LayerNorm(A).W^T + bias, with the LayerNorm folded into the epilogue
+    EPI_LNIN_GELU = 6,      // C = gelu(LayerNorm(A).W^T + bias), same folding
+    EPI_RES_LN = 7          // C = A.W^T + bias + LayerNorm(residual); also emits row statistics of C
+};
+
+// Operands of the LayerNorm-folding epilogues.  A LayerNorm between two GEMMs is never materialised:
+// the producer GEMM (EPI_RES_LN) writes the pre-LayerNorm rows and, per row, partial (sum, sum of
+// squares) pairs — one per (column tile, warp half) = 2*N/BN per row; the consumer GEMM
+// (EPI_LNIN_*) multiplies the RAW rows by W' = W diag(gamma) and finishes the algebra per element:
+//   LN(a).W^T + b = rstd * (a.W'^T) - rstd * mean * c + d,  c_n = sum_k W'_nk,  d_n = b_n + sum_k beta_k W_nk.
+struct LnArgs {
+    const float* c = nullptr;          // [N]  column sums of the folded weights        (EPI_LNIN_*)
+    const float* stats_in = nullptr;   // [M][p_in][2] partials of the tensor being normalised
+    int p_in = 0;
+    float* stats_out = nullptr;        // [M][2*N/BN][2] partials of the rows written  (EPI_RES_LN)
+    const float* gamma = nullptr;      // [N]  LayerNorm weight / bias applied to the residual (EPI_RES_LN)
+    const float* beta = nullptr;
+    float inv_h = 0.f;                 // 1 / row length of the normalised tensor
+    float eps = 0.f;
+};
 
 // Output columns >= f16_from_col are written as fp16 instead of bf16 (pass N for "none"): the QKV GEMM
 // emits its V third in fp16, the operand type of the attention kernel's P·V product.
@@ -97,7 +122,7 @@ enum GemmEpilogue { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESIDUAL = 2, EPI_
 int gemm_tc_block_n(int N);
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
                    const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,
-                   int f16_from_col, int num_sms, cudaStream_t stream);
+                   int f16_from_col, const LnArgs& ln, int num_sms, cudaStream_t stream);
 // CUDA-core validation GEMM (debug).
 int gemm_ref_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const float* bias,
                     const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,
@@ -107,15 +132,19 @@ int gemm_ref_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const float*
 int embed_ln_launch(const int32_t* token_ids, const int32_t* cu_seqlens, int n_seq, int T, int H,
                     int max_position, int vocab, const float* word, const float* pos,
                     const float* type0, const float* gamma, const float* beta, float eps,
-                    __nv_bfloat16* out, int32_t* seq_of_token, cudaStream_t stream);
+                    __nv_bfloat16* out, int32_t* seq_of_token, float* stats_out, int stats_p,
+                    cudaStream_t stream);
 // LayerNorm over rows of a bf16 [T,H] tensor (input already holds residual + sublayer output).
 int layernorm_launch(const __nv_bfloat16* in, const float* gamma, const float* beta, float eps,
                      __nv_bfloat16* out, int T, int H, cudaStream_t stream);
 // Packed variable-length multi-head self-attention over qkv [T,3H] -> ctx [T,H].
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int H, int heads,
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream);
-// Masked mean-pool over each sequence's tokens + L2 normalisation -> fp32 [n_seq,H].
+// Masked mean-pool over each sequence's tokens + L2 normalisation -> fp32 [n_seq,H].  With `stats`
+// (per-row partial sums, see LnArgs) x holds pre-LayerNorm rows and the final LayerNorm (gamma, beta)
+// is applied on the fly.
 int pool_l2_launch(const __nv_bfloat16* x, const int32_t* cu_seqlens, int n_seq, int H, float* out,
+                   const float* stats, int stats_p, const float* gamma, const float* beta, float eps,
                    cudaStream_t stream);
 
 }  // namespace lsc

@@ -24,7 +24,8 @@ embed_ln_kernel(const int32_t* __restrict__ token_ids, const int32_t* __restrict
                 int n_seq, int T, int max_position, int vocab, const float* __restrict__ word,
                 const float* __restrict__ pos, const float* __restrict__ type0,
                 const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
-                __nv_bfloat16* __restrict__ out, int32_t* __restrict__ seq_of_token) {
+                __nv_bfloat16* __restrict__ out, int32_t* __restrict__ seq_of_token,
+                float* __restrict__ stats_out, int stats_p) {
     constexpr int H = 128 * VPL;
     const int lane = threadIdx.x & 31;
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -37,6 +38,11 @@ embed_ln_kernel(const int32_t* __restrict__ token_ids, const int32_t* __restrict
     }
     const int p = t - __ldg(cu_seqlens + lo);
     if (lane == 0 && seq_of_token != nullptr) seq_of_token[t] = lo;
+    // The rows written here are already normalised; downstream GEMMs fold a LayerNorm over their input
+    // from per-row partial (sum, sum of squares): emit partials that mean "mean 0, variance 1".
+    if (stats_out != nullptr && lane < stats_p)
+        reinterpret_cast<float2*>(stats_out)[static_cast<size_t>(t) * stats_p + lane] =
+            make_float2(0.f, static_cast<float>(H) / static_cast<float>(stats_p));
     int id = __ldg(token_ids + t);
     id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
     const int pp = p < max_position ? p : max_position - 1;
@@ -120,7 +126,8 @@ layernorm_kernel(const __nv_bfloat16* __restrict__ in, const float* __restrict__
 
 // One CTA per sequence; thread j owns columns 2j, 2j+1 (blockDim = H/2); rows are read coalesced.
 __global__ void pool_l2_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ cu_seqlens,
-                               int H, float* __restrict__ out) {
+                               int H, float* __restrict__ out, const float* __restrict__ stats, int stats_p,
+                               const float* __restrict__ gamma, const float* __restrict__ beta, float eps) {
     __shared__ float red[32];
     const int s = blockIdx.x;
     const int t0 = __ldg(cu_seqlens + s), t1 = __ldg(cu_seqlens + s + 1);
@@ -129,6 +136,30 @@ __global__ void pool_l2_kernel(const __nv_bfloat16* __restrict__ x, const int32_
     const uint32_t* xp = reinterpret_cast<const uint32_t*>(x) + j;
     const int H2 = H >> 1;
     int t = t0;
+    if (stats != nullptr) {
+        // x holds pre-LayerNorm rows; apply the final LayerNorm on the fly:
+        // mean_t LN(x_t) = gamma * mean_t((x_t - mu_t) * rstd_t) + beta  (for a non-empty sequence)
+        const float inv_h = 1.0f / static_cast<float>(H);
+        for (; t < t1; ++t) {
+            const float2* sp = reinterpret_cast<const float2*>(stats) + static_cast<size_t>(t) * stats_p;
+            float sum = 0.f, sq = 0.f;
+            for (int p = 0; p < stats_p; ++p) {
+                const float2 v = __ldg(sp + p);
+                sum += v.x;
+                sq += v.y;
+            }
+            const float mean = sum * inv_h;
+            const float rstd = rsqrtf(fmaxf(sq * inv_h - mean * mean, 0.f) + eps);
+            const uint32_t w0 = __ldg(xp + static_cast<size_t>(t) * H2);
+            a0 += (bf16_lo(w0) - mean) * rstd;
+            a1 += (bf16_hi(w0) - mean) * rstd;
+        }
+        const float cnt = static_cast<float>(t1 - t0);
+        if (cnt > 0.f) {
+            a0 = a0 * __ldg(gamma + 2 * j) + cnt * __ldg(beta + 2 * j);
+            a1 = a1 * __ldg(gamma + 2 * j + 1) + cnt * __ldg(beta + 2 * j + 1);
+        }
+    }
     for (; t + 4 <= t1; t += 4) {
         const uint32_t w0 = __ldg(xp + static_cast<size_t>(t) * H2);
         const uint32_t w1 = __ldg(xp + static_cast<size_t>(t + 1) * H2);
@@ -164,17 +195,19 @@ __global__ void pool_l2_kernel(const __nv_bfloat16* __restrict__ x, const int32_
 int embed_ln_launch(const int32_t* token_ids, const int32_t* cu_seqlens, int n_seq, int T, int H,
                     int max_position, int vocab, const float* word, const float* pos,
                     const float* type0, const float* gamma, const float* beta, float eps,
-                    __nv_bfloat16* out, int32_t* seq_of_token, cudaStream_t stream) {
+                    __nv_bfloat16* out, int32_t* seq_of_token, float* stats_out, int stats_p,
+                    cudaStream_t stream) {
     if (T <= 0) return 0;
+    if (stats_p > 32) return fail(LSC_E_UNSUPPORTED, "embed: more than 32 statistics partials per row");
     const int wpb = 8;
     const int grid = (T + wpb - 1) / wpb;
     switch (H) {
-        case 128: embed_ln_kernel<1><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token); break;
-        case 256: embed_ln_kernel<2><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token); break;
-        case 384: embed_ln_kernel<3><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token); break;
-        case 512: embed_ln_kernel<4><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token); break;
-        case 768: embed_ln_kernel<6><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token); break;
-        case 1024: embed_ln_kernel<8><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token); break;
+        case 128: embed_ln_kernel<1><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
+        case 256: embed_ln_kernel<2><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
+        case 384: embed_ln_kernel<3><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
+        case 512: embed_ln_kernel<4><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
+        case 768: embed_ln_kernel<6><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
+        case 1024: embed_ln_kernel<8><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
         default: return fail(LSC_E_UNSUPPORTED, "hidden size must be one of 128,256,384,512,768,1024");
     }
     LSC_CUDA(cudaGetLastError());
@@ -200,10 +233,11 @@ int layernorm_launch(const __nv_bfloat16* in, const float* gamma, const float* b
 }
 
 int pool_l2_launch(const __nv_bfloat16* x, const int32_t* cu_seqlens, int n_seq, int H, float* out,
+                   const float* stats, int stats_p, const float* gamma, const float* beta, float eps,
                    cudaStream_t stream) {
     if (n_seq <= 0) return 0;
     if (H % 64 != 0 || H / 2 > 1024) return fail(LSC_E_UNSUPPORTED, "pool: bad hidden size");
-    pool_l2_kernel<<<n_seq, H / 2, 0, stream>>>(x, cu_seqlens, H, out);
+    pool_l2_kernel<<<n_seq, H / 2, 0, stream>>>(x, cu_seqlens, H, out, stats, stats_p, gamma, beta, eps);
     LSC_CUDA(cudaGetLastError());
     return 1;
 }

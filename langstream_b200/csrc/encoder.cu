@@ -29,6 +29,15 @@ struct LayerW {
     float* b_2 = nullptr;
     float* ln2_g = nullptr;
     float* ln2_b = nullptr;
+    // LayerNorm folding (tcgen05 path): w_qkv / w_1 hold W diag(gamma_in); c = column sums of those
+    // folded bf16 weights; d = bias + W beta_in; in_g / in_b = the LayerNorm applied to this layer's input
+    // (ones / zeros for layer 0, whose input the embedding kernel already normalised).
+    float* c_qkv = nullptr;
+    float* d_qkv = nullptr;
+    float* c_1 = nullptr;
+    float* d_1 = nullptr;
+    float* in_g = nullptr;
+    float* in_b = nullptr;
     CUtensorMap tm_qkv, tm_o, tm_1, tm_2;
 };
 
@@ -58,6 +67,9 @@ struct lsc_encoder {
     int32_t* d_ids = nullptr;
     int32_t* d_cu = nullptr;
     float* d_out = nullptr;
+    float* stats_x = nullptr;   // [cap_tokens][stats_p][2] partial row statistics of x / tmp (LN folding)
+    float* stats_1 = nullptr;
+    int stats_p = 0;
     std::atomic<int64_t> launches{0};
     Profiler prof;  // classes: 0 embed+LN, 1 GEMM, 2 attention, 3 LayerNorm, 4 pool
 };
@@ -95,6 +107,30 @@ int upload_bf16(lsc_encoder* e, __nv_bfloat16** dst, const float* const* parts, 
     return LSC_OK;
 }
 
+// W' = W diag(gamma) as bf16 [N,K]; c_n = sum_k bf16(W'_nk); d_n = bias_n + sum_k beta_k W_nk.
+int upload_folded(lsc_encoder* e, const float* W, const float* bias, const float* gamma, const float* beta,
+                  size_t N, size_t K, __nv_bfloat16** d_w, float** d_c, float** d_d) {
+    std::vector<__nv_bfloat16> h(N * K);
+    std::vector<float> c(N), d(N);
+    for (size_t n = 0; n < N; ++n) {
+        double cs = 0.0, ds = bias[n];
+        for (size_t k = 0; k < K; ++k) {
+            const float w = W[n * K + k];
+            const __nv_bfloat16 q = __float2bfloat16_rn(w * gamma[k]);
+            h[n * K + k] = q;
+            cs += static_cast<double>(__bfloat162float(q));
+            ds += static_cast<double>(beta[k]) * static_cast<double>(w);
+        }
+        c[n] = static_cast<float>(cs);
+        d[n] = static_cast<float>(ds);
+    }
+    LSC_TRY(dev_alloc(e, d_w, N * K));
+    LSC_CUDA(cudaMemcpy(*d_w, h.data(), N * K * sizeof(__nv_bfloat16), cudaMemcpyHostToDevice));
+    LSC_TRY(upload_f32(e, d_c, c.data(), N));
+    LSC_TRY(upload_f32(e, d_d, d.data(), N));
+    return LSC_OK;
+}
+
 int check_config(const lsc_encoder_config* c) {
     if (c == nullptr) return fail(LSC_E_INVALID, "encoder config is null");
     if (c->layers <= 0 || c->hidden <= 0 || c->heads <= 0 || c->ffn <= 0 || c->vocab <= 0 ||
@@ -128,12 +164,20 @@ int ensure_workspace(lsc_encoder* e, int64_t T) {
         if (*b) cudaFree(*b);
         *b = nullptr;
     }
+    if (e->stats_x) cudaFree(e->stats_x);
+    if (e->stats_1) cudaFree(e->stats_1);
+    e->stats_x = e->stats_1 = nullptr;
     e->cap_tokens = 0;
     const size_t sizes[6] = {H, H, H, 3 * H, H, F};
     for (int i = 0; i < 6; ++i) {
         void* p = nullptr;
         LSC_CUDA(cudaMalloc(&p, static_cast<size_t>(cap) * sizes[i] * sizeof(__nv_bfloat16)));
         *bufs[i] = static_cast<__nv_bfloat16*>(p);
+    }
+    if (e->stats_p > 0) {
+        const size_t n = static_cast<size_t>(cap) * e->stats_p * 2 * sizeof(float);
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->stats_x), n));
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->stats_1), n));
     }
     e->cap_tokens = cap;
     return LSC_OK;
@@ -164,9 +208,9 @@ int ensure_staging(lsc_encoder* e, int64_t T, int64_t n_seq) {
 
 int gemm(lsc_encoder* e, const CUtensorMap& tmA, const __nv_bfloat16* A, const CUtensorMap& tmW,
          const __nv_bfloat16* W, const float* bias, const __nv_bfloat16* residual, const CUtensorMap& tmC,
-         __nv_bfloat16* C, int M, int N, int K, int epi, int f16_from_col, cudaStream_t st) {
+         __nv_bfloat16* C, int M, int N, int K, int epi, int f16_from_col, const LnArgs& ln, cudaStream_t st) {
     if (e->cfg.gemm_impl == 1) return gemm_ref_launch(A, W, bias, residual, C, M, N, K, epi, f16_from_col, st);
-    return gemm_tc_launch(tmA, tmW, tmC, bias, residual, M, N, K, epi, f16_from_col, e->num_sms, st);
+    return gemm_tc_launch(tmA, tmW, tmC, bias, residual, M, N, K, epi, f16_from_col, ln, e->num_sms, st);
 }
 
 #define LSC_LAUNCH(cls, expr)         \
@@ -186,30 +230,67 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
     int64_t nlaunch = 0;
     if (T > 0) {
         LSC_TRY(ensure_workspace(e, T));
-        CUtensorMap tm_x, tm_x1, tm_ctx, tm_ffn, tc_qkv, tc_tmp, tc_ffn;
         if (c.gemm_impl == 0) {
+            // ---- product path: tcgen05 GEMMs, every LayerNorm folded into the neighbouring epilogues ----
+            // x and tmp hold PRE-LayerNorm rows plus per-row partial statistics; a normalised activation is
+            // never written to memory.
+            CUtensorMap tm_x, tm_tmp, tm_ctx, tm_ffn, tc_qkv, tc_tmp, tc_x, tc_ffn;
             LSC_TRY(make_tmap_bf16_store32(&tc_qkv, e->qkv, T, 3 * H));
             LSC_TRY(make_tmap_bf16_store32(&tc_tmp, e->tmp, T, H));
+            LSC_TRY(make_tmap_bf16_store32(&tc_x, e->x, T, H));
             LSC_TRY(make_tmap_bf16_store32(&tc_ffn, e->ffn, T, F));
             LSC_TRY(make_tmap_bf16_sw128(&tm_x, e->x, T, H, 128));
-            LSC_TRY(make_tmap_bf16_sw128(&tm_x1, e->x1, T, H, 128));
+            LSC_TRY(make_tmap_bf16_sw128(&tm_tmp, e->tmp, T, H, 128));
             LSC_TRY(make_tmap_bf16_sw128(&tm_ctx, e->ctx, T, H, 128));
             LSC_TRY(make_tmap_bf16_sw128(&tm_ffn, e->ffn, T, F, 128));
-        }
-        LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word,
-                                   e->d_pos, e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, st));
-        for (int l = 0; l < c.layers; ++l) {
-            const LayerW& w = e->layers[l];
-            LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.b_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H, EPI_BIAS, 2 * H, st));
-            LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, H, c.heads, max_seqlen, e->ctx, st));
-            LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, tc_tmp, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, H, st));
-            LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
-            LSC_LAUNCH(1, gemm(e, tm_x1, e->x1, w.tm_1, w.w_1, w.b_1, nullptr, tc_ffn, e->ffn, T, F, H, EPI_BIAS_GELU, F, st));
-            LSC_LAUNCH(1, gemm(e, tm_ffn, e->ffn, w.tm_2, w.w_2, w.b_2, e->x1, tc_tmp, e->tmp, T, H, F, EPI_BIAS_RESIDUAL, H, st));
-            LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln2_g, w.ln2_b, c.ln_eps, e->x, T, H, st));
+            const int P = e->stats_p;
+            const float inv_h = 1.0f / static_cast<float>(H);
+            LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word, e->d_pos,
+                                          e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, e->stats_x, P, st));
+            for (int l = 0; l < c.layers; ++l) {
+                const LayerW& w = e->layers[l];
+                LnArgs ln_in;  // consumer of x: LN_in folded
+                ln_in.c = w.c_qkv; ln_in.stats_in = e->stats_x; ln_in.p_in = P; ln_in.inv_h = inv_h; ln_in.eps = c.ln_eps;
+                LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.d_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H,
+                                   EPI_LNIN_BIAS, 2 * H, ln_in, st));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, H, c.heads, max_seqlen, e->ctx, st));
+                LnArgs ln_o;  // tmp = ctx.Wo^T + b + LN_in(x); statistics of tmp -> stats_1
+                ln_o.stats_in = e->stats_x; ln_o.p_in = P; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
+                ln_o.inv_h = inv_h; ln_o.eps = c.ln_eps;
+                LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, tc_tmp, e->tmp, T, H, H, EPI_RES_LN, H, ln_o, st));
+                LnArgs ln_1;  // consumer of tmp: LN1 folded, then GELU
+                ln_1.c = w.c_1; ln_1.stats_in = e->stats_1; ln_1.p_in = P; ln_1.inv_h = inv_h; ln_1.eps = c.ln_eps;
+                LSC_LAUNCH(1, gemm(e, tm_tmp, e->tmp, w.tm_1, w.w_1, w.d_1, nullptr, tc_ffn, e->ffn, T, F, H,
+                                   EPI_LNIN_GELU, F, ln_1, st));
+                LnArgs ln_2;  // x = ffn.W2^T + b + LN1(tmp); statistics of x -> stats_x
+                ln_2.stats_in = e->stats_1; ln_2.p_in = P; ln_2.stats_out = e->stats_x; ln_2.gamma = w.ln1_g; ln_2.beta = w.ln1_b;
+                ln_2.inv_h = inv_h; ln_2.eps = c.ln_eps;
+                LSC_LAUNCH(1, gemm(e, tm_ffn, e->ffn, w.tm_2, w.w_2, w.b_2, e->tmp, tc_x, e->x, T, H, F, EPI_RES_LN, H, ln_2, st));
+            }
+        } else {
+            // ---- validation path: CUDA-core GEMMs and explicit LayerNorm kernels (unfused) ----
+            CUtensorMap none;
+            const LnArgs no_ln;
+            LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word, e->d_pos,
+                                          e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, nullptr, 0, st));
+            for (int l = 0; l < c.layers; ++l) {
+                const LayerW& w = e->layers[l];
+                LSC_LAUNCH(1, gemm(e, none, e->x, none, w.w_qkv, w.b_qkv, nullptr, none, e->qkv, T, 3 * H, H, EPI_BIAS, 2 * H, no_ln, st));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, H, c.heads, max_seqlen, e->ctx, st));
+                LSC_LAUNCH(1, gemm(e, none, e->ctx, none, w.w_o, w.b_o, e->x, none, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, H, no_ln, st));
+                LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
+                LSC_LAUNCH(1, gemm(e, none, e->x1, none, w.w_1, w.b_1, nullptr, none, e->ffn, T, F, H, EPI_BIAS_GELU, F, no_ln, st));
+                LSC_LAUNCH(1, gemm(e, none, e->ffn, none, w.w_2, w.b_2, e->x1, none, e->tmp, T, H, F, EPI_BIAS_RESIDUAL, H, no_ln, st));
+                LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln2_g, w.ln2_b, c.ln_eps, e->x, T, H, st));
+            }
         }
     }
-    LSC_LAUNCH(4, pool_l2_launch(e->x, d_cu, n_seq, H, d_out, st));
+    if (c.gemm_impl == 0 && T > 0) {
+        const LayerW& last = e->layers[c.layers - 1];
+        LSC_LAUNCH(4, pool_l2_launch(e->x, d_cu, n_seq, H, d_out, e->stats_x, e->stats_p, last.ln2_g, last.ln2_b, c.ln_eps, st));
+    } else {
+        LSC_LAUNCH(4, pool_l2_launch(e->x, d_cu, n_seq, H, d_out, nullptr, 0, nullptr, nullptr, c.ln_eps, st));
+    }
     e->launches += nlaunch;
     return LSC_OK;
 }
@@ -229,7 +310,7 @@ void lsc_encoder_destroy(lsc_encoder* e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     for (void* p : e->owned) cudaFree(p);
-    void* ws[] = {e->x, e->x1, e->tmp, e->qkv, e->ctx, e->ffn, e->d_ids, e->d_cu, e->d_out};
+    void* ws[] = {e->x, e->x1, e->tmp, e->qkv, e->ctx, e->ffn, e->d_ids, e->d_cu, e->d_out, e->stats_x, e->stats_1};
     for (void* p : ws)
         if (p) cudaFree(p);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -273,41 +354,59 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
         LSC_TRY(upload_f32(e, &e->d_emb_b, p, H));
         p += H;
         e->layers.resize(cfg->layers);
+        const float* prev_ln2_g = nullptr;
+        const float* prev_ln2_b = nullptr;
+        if (cfg->gemm_impl == 0) e->stats_p = 2 * static_cast<int>(H) / gemm_tc_block_n(static_cast<int>(H));
         for (int l = 0; l < cfg->layers; ++l) {
             LayerW& w = e->layers[l];
             const float* qw = p;            const float* qb = qw + H * H;
             const float* kw = qb + H;       const float* kb = kw + H * H;
             const float* vw = kb + H;       const float* vb = vw + H * H;
             p = vb + H;
-            const float* wparts[3] = {qw, kw, vw};
-            const size_t wcounts[3] = {H * H, H * H, H * H};
-            LSC_TRY(upload_bf16(e, &w.w_qkv, wparts, wcounts, 3));
-            std::vector<float> bq(3 * H);
+            const size_t hh = H * H, fh = F * H;
+            // the LayerNorm applied to this layer's input: previous layer's output LayerNorm
+            // (layer 0: identity, the embedding kernel normalises)
+            std::vector<float> in_g(H, 1.0f), in_b(H, 0.0f);
+            if (l > 0) {
+                memcpy(in_g.data(), prev_ln2_g, H * sizeof(float));
+                memcpy(in_b.data(), prev_ln2_b, H * sizeof(float));
+            }
+            std::vector<float> wq(3 * hh), bq(3 * H);
+            memcpy(wq.data(), qw, hh * sizeof(float));
+            memcpy(wq.data() + hh, kw, hh * sizeof(float));
+            memcpy(wq.data() + 2 * hh, vw, hh * sizeof(float));
             memcpy(bq.data(), qb, H * sizeof(float));
             memcpy(bq.data() + H, kb, H * sizeof(float));
             memcpy(bq.data() + 2 * H, vb, H * sizeof(float));
+            const float* ow = p;             const float* ob = ow + hh;
+            const float* l1g = ob + H;       const float* l1b = l1g + H;
+            const float* w1 = l1b + H;       const float* b1 = w1 + fh;
+            const float* w2 = b1 + F;        const float* b2 = w2 + fh;
+            const float* l2g = b2 + H;       const float* l2b = l2g + H;
+            p = l2b + H;
+            if (cfg->gemm_impl == 0) {
+                LSC_TRY(upload_folded(e, wq.data(), bq.data(), in_g.data(), in_b.data(), 3 * H, H, &w.w_qkv, &w.c_qkv, &w.d_qkv));
+                LSC_TRY(upload_folded(e, w1, b1, l1g, l1b, F, H, &w.w_1, &w.c_1, &w.d_1));
+                LSC_TRY(upload_f32(e, &w.in_g, in_g.data(), H));
+                LSC_TRY(upload_f32(e, &w.in_b, in_b.data(), H));
+            } else {
+                const float* wp[1] = {wq.data()};
+                const size_t wc[1] = {3 * hh};
+                LSC_TRY(upload_bf16(e, &w.w_qkv, wp, wc, 1));
+                LSC_TRY(upload_bf16(e, &w.w_1, &w1, &fh, 1));
+            }
             LSC_TRY(upload_f32(e, &w.b_qkv, bq.data(), 3 * H));
-            const size_t hh = H * H, fh = F * H;
-            LSC_TRY(upload_bf16(e, &w.w_o, &p, &hh, 1));
-            p += hh;
-            LSC_TRY(upload_f32(e, &w.b_o, p, H));
-            p += H;
-            LSC_TRY(upload_f32(e, &w.ln1_g, p, H));
-            p += H;
-            LSC_TRY(upload_f32(e, &w.ln1_b, p, H));
-            p += H;
-            LSC_TRY(upload_bf16(e, &w.w_1, &p, &fh, 1));
-            p += fh;
-            LSC_TRY(upload_f32(e, &w.b_1, p, F));
-            p += F;
-            LSC_TRY(upload_bf16(e, &w.w_2, &p, &fh, 1));
-            p += fh;
-            LSC_TRY(upload_f32(e, &w.b_2, p, H));
-            p += H;
-            LSC_TRY(upload_f32(e, &w.ln2_g, p, H));
-            p += H;
-            LSC_TRY(upload_f32(e, &w.ln2_b, p, H));
-            p += H;
+            LSC_TRY(upload_bf16(e, &w.w_o, &ow, &hh, 1));
+            LSC_TRY(upload_f32(e, &w.b_o, ob, H));
+            LSC_TRY(upload_f32(e, &w.ln1_g, l1g, H));
+            LSC_TRY(upload_f32(e, &w.ln1_b, l1b, H));
+            LSC_TRY(upload_f32(e, &w.b_1, b1, F));
+            LSC_TRY(upload_bf16(e, &w.w_2, &w2, &fh, 1));
+            LSC_TRY(upload_f32(e, &w.b_2, b2, H));
+            LSC_TRY(upload_f32(e, &w.ln2_g, l2g, H));
+            LSC_TRY(upload_f32(e, &w.ln2_b, l2b, H));
+            prev_ln2_g = l2g;
+            prev_ln2_b = l2b;
             if (cfg->gemm_impl == 0) {
                 const int bn3 = gemm_tc_block_n(3 * static_cast<int>(H));
                 const int bnh = gemm_tc_block_n(static_cast<int>(H));

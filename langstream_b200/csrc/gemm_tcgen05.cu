@@ -60,45 +60,38 @@ __device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
     return d;
 }
 
-// 256-bit global accesses (sm_100: LDG/STG.E.ENL2.256): one whole 32-byte sector per thread.
+// 256-bit global load (sm_100: LDG.E.ENL2.256): one whole 32-byte sector per thread.
 __device__ __forceinline__ void ldg256(const void* p, uint32_t* r) {
     asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                  : "l"(p));
 }
-__device__ __forceinline__ void stg256(void* p, const uint32_t* r) {
-    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]),
-                 "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
-                 : "memory");
-}
-
 // Exact-erf GELU, x * Phi(x), evaluated without erff():
-//   gelu(x) = max(x,0) - |x| * tail(|x|),  tail(a) = Phi(-a) = 0.5 - a * P(a^2)  on a <= 4,
-// P = 9-term minimax fit (Lawson, weighted for the absolute error of gelu), tail clamped to >= 0 and
-// shifted so that tail(4) = 0.  Max abs error 1.3e-4 over all x (fp32 evaluation), i.e. an order of
-// magnitude below the bf16 rounding of the result; two elements per FFMA2.
+//   Phi(x) = 0.5 * (1 + tanh(p(x))),  p(x) = atanh(erf(x / sqrt 2)),
+// with p fitted by an odd degree-5 polynomial x * (a + b x^2 + c x^4) (minimax for the absolute error
+// of gelu; 2.5e-5 with an exact tanh).  tanh is one MUFU.TANH (relative error 2^-11), so the result is
+// within ~5e-4 absolute / 2.5e-4 relative of the erf form everywhere — an eighth of the bf16 rounding
+// applied to it next.  x^2 is clamped at 64, beyond which tanh has saturated (and before the fitted
+// polynomial turns over).  Two elements per FFMA2/FMUL2: ~5 issue slots per element instead of ~25
+// for erff().  (The familiar 0.044715 "tanh GELU" is a different, 2-term fit of the same p with
+// 4.7e-4 systematic error; this is not that approximation.)
+__device__ __forceinline__ float tanh_approx(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ void gelu2(float& x0, float& x1) {
-    const float a0 = fabsf(x0), a1 = fabsf(x1);
-    const float c0 = fminf(a0, 4.0f), c1 = fminf(a1, 4.0f);
-    const uint64_t ac = pk2(c0, c1);
-    const uint64_t u = mul2(ac, ac);
-    uint64_t p = pk2(6.740397823e-11f, 6.740397823e-11f);
-    p = fma2(p, u, pk2(-6.066908309e-09f, -6.066908309e-09f));
-    p = fma2(p, u, pk2(2.440845606e-07f, 2.440845606e-07f));
-    p = fma2(p, u, pk2(-5.860600595e-06f, -5.860600595e-06f));
-    p = fma2(p, u, pk2(9.494025289e-05f, 9.494025289e-05f));
-    p = fma2(p, u, pk2(-1.112856087e-03f, -1.112856087e-03f));
-    p = fma2(p, u, pk2(9.815800935e-03f, 9.815800935e-03f));
-    p = fma2(p, u, pk2(-6.632363051e-02f, -6.632363051e-02f));
-    p = fma2(p, u, pk2(3.988810182e-01f, 3.988810182e-01f));
-    // t = half - ac * p
-    const uint64_t t = fma2(pk2(-c0, -c1), p, pk2(4.999701977e-01f, 4.999701977e-01f));
+    const uint64_t xx = pk2(x0, x1);
+    float u0, u1;
+    upk2(mul2(xx, xx), u0, u1);
+    const uint64_t u = pk2(fminf(u0, 64.0f), fminf(u1, 64.0f));
+    uint64_t p = fma2(pk2(-0.000351517994f, -0.000351517994f), u, pk2(0.0370056538f, 0.0370056538f));
+    p = fma2(p, u, pk2(0.797507875f, 0.797507875f));
     float t0, t1;
-    upk2(t, t0, t1);
-    t0 = fmaxf(t0, 0.f);
-    t1 = fmaxf(t1, 0.f);
-    x0 = fmaf(-a0, t0, fmaxf(x0, 0.f));
-    x1 = fmaf(-a1, t1, fmaxf(x1, 0.f));
+    upk2(mul2(p, xx), t0, t1);
+    const uint64_t th = pk2(tanh_approx(t0), tanh_approx(t1));
+    const uint64_t hx = mul2(xx, pk2(0.5f, 0.5f));
+    upk2(fma2(hx, th, hx), x0, x1);
 }
 
 __device__ __forceinline__ float gelu_erf(float x) {
@@ -109,7 +102,7 @@ template <int BN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
                const __grid_constant__ CUtensorMap tmapC, const float* __restrict__ bias,
-               const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int f16_from_col, int dbg) {
+               const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int f16_from_col, const LnArgs ln) {
     using cfg = Cfg<BN>;
     constexpr int STAGES = cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -158,7 +151,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     if (warp == 0) {
         // ===== TMA producer =====
         if (elect_one()) {
-            const uint64_t pol_keep = policy_evict_last();
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -168,12 +160,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                     const uint32_t sA = smem_base + stage * cfg::STAGE_BYTES;
                     const uint32_t sB = sA + cfg::A_BYTES;
                     mbar_arrive_expect_tx(bar_full + 8 * stage, cfg::STAGE_BYTES);
-                    if (dbg & 16) {
-                        tma_load_2d_hint(sA, &tmapA, bar_full + 8 * stage, kb * BK, m_blk * BM, pol_keep);
-                        tma_load_2d_hint(sB, &tmapW, bar_full + 8 * stage, kb * BK, n_blk * BN, pol_keep);
-                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
-                        continue;
-                    }
                     tma_load_2d(sA, &tmapA, bar_full + 8 * stage, kb * BK, m_blk * BM);
                     tma_load_2d(sB, &tmapW, bar_full + 8 * stage, kb * BK, n_blk * BN);
                     if (++stage == STAGES) {
@@ -245,8 +231,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             const int col_base = n_blk * BN + half * (BN / 2);
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC_STRIDE +
                                    half * (BN / 2);
-            const __nv_bfloat16* rrow =
-                EPI == EPI_BIAS_RESIDUAL ? residual + static_cast<size_t>(row_ok ? grow : 0) * N + col_base : nullptr;
+            constexpr bool kRes = EPI == EPI_BIAS_RESIDUAL || EPI == EPI_RES_LN;
+            constexpr bool kLnIn = EPI == EPI_LNIN_BIAS || EPI == EPI_LNIN_GELU;
+            constexpr bool kGelu = EPI == EPI_BIAS_GELU || EPI == EPI_LNIN_GELU;
+            const __nv_bfloat16* rrow = kRes ? residual + static_cast<size_t>(row_ok ? grow : 0) * N + col_base : nullptr;
+            // LayerNorm folding: row statistics of the tensor being normalised (the A operand for
+            // kLnIn, the residual for EPI_RES_LN) from its per-row partial (sum, sum of squares).
+            float rstd = 1.f, nm = 0.f;  // nm = -mean * rstd
+            if (kLnIn || EPI == EPI_RES_LN) {
+                float sum = 0.f, sq = 0.f;
+                if (row_ok) {
+                    const float2* sp = reinterpret_cast<const float2*>(ln.stats_in) + static_cast<size_t>(grow) * ln.p_in;
+                    for (int p = 0; p < ln.p_in; ++p) {
+                        const float2 t = __ldg(sp + p);
+                        sum += t.x;
+                        sq += t.y;
+                    }
+                }
+                const float mean = sum * ln.inv_h;
+                const float var = fmaxf(sq * ln.inv_h - mean * mean, 0.f);
+                rstd = row_ok ? rsqrtf(var + ln.eps) : 1.f;
+                nm = -mean * rstd;
+            }
+            float osum = 0.f, osq = 0.f;  // EPI_RES_LN: statistics of the rows this thread writes
             mbar_wait(bar_tfull + 8 * acc, acc_phase);
             tc_fence_after();
             uint32_t va[32], vb[32];
@@ -283,26 +290,39 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 uint32_t(&v)[32] = (c & 1) ? vb : va;
                 uint32_t(&vnext)[32] = (c & 1) ? va : vb;
                 uint32_t res[16];
-                if (EPI == EPI_BIAS_RESIDUAL) {
+                if (kRes) {
                     ldg256(rrow + c * 32, res);
                     ldg256(rrow + c * 32 + 16, res + 8);
                 }
                 tmem_ld_wait();
                 if (c + 1 < NCH) tmem_ld_32x32(tbase + (c + 1) * 32, vnext);
-                const float4* bp = reinterpret_cast<const float4*>(bias + ((dbg & 4) ? 0 : col_base + c * 32));
+                const int col = col_base + c * 32;
+                const float4* bp = reinterpret_cast<const float4*>(bias + col);
+                const float4* cp = reinterpret_cast<const float4*>((kLnIn ? ln.c : bias) + col);
+                const float4* gp = reinterpret_cast<const float4*>((EPI == EPI_RES_LN ? ln.gamma : bias) + col);
+                const float4* ep = reinterpret_cast<const float4*>((EPI == EPI_RES_LN ? ln.beta : bias) + col);
                 // the block we are about to fill was the source of the TMA store issued two chunks ago
                 if (lane == 0) tma_store_wait_read<1>();
                 __syncwarp();
                 uint8_t* blk = stg + buf * 2048 + lane * 64;
-                const bool as_f16 = col_base + c * 32 >= f16_from_col;  // V third of the QKV output
+                const bool as_f16 = col >= f16_from_col;  // V third of the QKV output
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {  // 4 x 16 bytes = 8 columns each
                     const float4 b0 = __ldg(bp + 2 * i), b1 = __ldg(bp + 2 * i + 1);
-                    float x[8] = {__uint_as_float(v[8 * i]) + b0.x,     __uint_as_float(v[8 * i + 1]) + b0.y,
-                                  __uint_as_float(v[8 * i + 2]) + b0.z, __uint_as_float(v[8 * i + 3]) + b0.w,
-                                  __uint_as_float(v[8 * i + 4]) + b1.x, __uint_as_float(v[8 * i + 5]) + b1.y,
-                                  __uint_as_float(v[8 * i + 6]) + b1.z, __uint_as_float(v[8 * i + 7]) + b1.w};
-                    if (EPI == EPI_BIAS_GELU) {
+                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                    float x[8];
+                    if (kLnIn) {
+                        // LN(a) . W^T + b  ==  rstd * (a . W'^T) - rstd * mean * c + d,  W' = W diag(gamma)
+                        const float4 c0 = __ldg(cp + 2 * i), c1 = __ldg(cp + 2 * i + 1);
+                        const float cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            x[j] = fmaf(rstd, __uint_as_float(v[8 * i + j]), fmaf(nm, cc[j], bb[j]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) x[j] = __uint_as_float(v[8 * i + j]) + bb[j];
+                    }
+                    if (kGelu) {
 #pragma unroll
                         for (int j = 0; j < 8; j += 2) gelu2(x[j], x[j + 1]);
                     }
@@ -311,6 +331,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                         for (int j = 0; j < 4; ++j) {
                             x[2 * j] += bf16_lo(res[4 * i + j]);
                             x[2 * j + 1] += bf16_hi(res[4 * i + j]);
+                        }
+                    }
+                    if (EPI == EPI_RES_LN) {
+                        // residual = LayerNorm(raw) computed on the fly: raw * (rstd*gamma) + (beta - mean*rstd*gamma)
+                        const float4 g0 = __ldg(gp + 2 * i), g1 = __ldg(gp + 2 * i + 1);
+                        const float4 e0 = __ldg(ep + 2 * i), e1 = __ldg(ep + 2 * i + 1);
+                        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+                        const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float raw = (j & 1) ? bf16_hi(res[4 * i + (j >> 1)]) : bf16_lo(res[4 * i + (j >> 1)]);
+                            x[j] += fmaf(raw, rstd * gg[j], fmaf(nm, gg[j], ee[j]));
+                            osum += x[j];
+                            osq = fmaf(x[j], x[j], osq);
                         }
                     }
                     uint4 o;
@@ -325,16 +359,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                         o.z = pack_bf16x2(x[4], x[5]);
                         o.w = pack_bf16x2(x[6], x[7]);
                     }
-                    if (!(dbg & 2) || o.x == 0x7fc07fc0u) *reinterpret_cast<uint4*>(blk + ((static_cast<uint32_t>(i) ^ sw) * 16)) = o;
+                    *reinterpret_cast<uint4*>(blk + ((static_cast<uint32_t>(i) ^ sw) * 16)) = o;
                 }
-                if (!(dbg & 8)) fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA engine
+                fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA engine
                 __syncwarp();
-                if (lane == 0 && !(dbg & 1)) {
-                    if (dbg & 32) tma_store_2d_hint(&tmapC, stg_addr + buf * 2048, col_base + c * 32, row0, policy_evict_first());
-                    else tma_store_2d(&tmapC, stg_addr + buf * 2048, col_base + c * 32, row0);
+                if (lane == 0) {
+                    tma_store_2d(&tmapC, stg_addr + buf * 2048, col, row0);
                     tma_store_commit();
                 }
                 buf ^= 1;
+            }
+            if (EPI == EPI_RES_LN && row_ok) {
+                // partial (sum, sum of squares) of this row over this warp's columns; the consumer adds
+                // the 2*N/BN partials of a row
+                float2* so = reinterpret_cast<float2*>(ln.stats_out) +
+                             static_cast<size_t>(grow) * (2 * n_tiles) + (n_blk * 2 + half);
+                *so = make_float2(osum, osq);
             }
             // every TMEM read of this tile by this warp has completed (tmem_ld_wait above)
             __syncwarp();
@@ -356,7 +396,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 
 template <int BN, int EPI>
 int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
-                const __nv_bfloat16* residual, int M, int N, int K, int f16_from_col, int num_sms, cudaStream_t stream) {
+                const __nv_bfloat16* residual, int M, int N, int K, int f16_from_col, const LnArgs& ln, int num_sms,
+                cudaStream_t stream) {
     using cfg = Cfg<BN>;
     static bool configured[64] = {};  // per instantiation and per device
     auto kern = gemm_tc_kernel<BN, EPI>;
@@ -370,28 +411,37 @@ int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtens
     const int m_tiles = (M + BM - 1) / BM;
     const int num_tiles = m_tiles * (N / BN);
     const int grid = num_tiles < num_sms ? num_tiles : num_sms;
-    static const int dbg = [] { const char* e = getenv("LSC_GEMM_DBG"); return e ? atoi(e) : 0; }();
-    kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, dbg);
+    kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln);
     LSC_CUDA(cudaGetLastError());
     return 1;
 }
 
 template <int BN>
 int launch_bn(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
-              const __nv_bfloat16* residual, int M, int N, int K, int epilogue, int f16_from_col, int num_sms,
-              cudaStream_t stream) {
+              const __nv_bfloat16* residual, int M, int N, int K, int epilogue, int f16_from_col, const LnArgs& ln,
+              int num_sms, cudaStream_t stream) {
     switch (epilogue) {
         case EPI_BIAS:
-            return launch_inst<BN, EPI_BIAS>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
+            return launch_inst<BN, EPI_BIAS>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
         case EPI_BIAS_GELU:
-            return launch_inst<BN, EPI_BIAS_GELU>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
+            return launch_inst<BN, EPI_BIAS_GELU>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
         case EPI_BIAS_RESIDUAL:
             if (residual == nullptr) return fail(LSC_E_INVALID, "gemm: residual epilogue without residual");
-            return launch_inst<BN, EPI_BIAS_RESIDUAL>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
+            return launch_inst<BN, EPI_BIAS_RESIDUAL>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
+        case EPI_LNIN_BIAS:
+            if (ln.c == nullptr || ln.stats_in == nullptr) return fail(LSC_E_INVALID, "gemm: LN-folded epilogue without statistics");
+            return launch_inst<BN, EPI_LNIN_BIAS>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
+        case EPI_LNIN_GELU:
+            if (ln.c == nullptr || ln.stats_in == nullptr) return fail(LSC_E_INVALID, "gemm: LN-folded epilogue without statistics");
+            return launch_inst<BN, EPI_LNIN_GELU>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
+        case EPI_RES_LN:
+            if (residual == nullptr || ln.stats_in == nullptr || ln.stats_out == nullptr || ln.gamma == nullptr || ln.beta == nullptr)
+                return fail(LSC_E_INVALID, "gemm: residual-LN epilogue needs residual, statistics, gamma and beta");
+            return launch_inst<BN, EPI_RES_LN>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
         case EPI_DISCARD:
-            return launch_inst<BN, EPI_DISCARD>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
+            return launch_inst<BN, EPI_DISCARD>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
         case EPI_LOADONLY:
-            return launch_inst<BN, EPI_LOADONLY>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, num_sms, stream);
+            return launch_inst<BN, EPI_LOADONLY>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
         default:
             return fail(LSC_E_INVALID, "gemm: unknown epilogue");
     }
@@ -414,17 +464,17 @@ int gemm_tc_block_n(int N) {
 
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
                    const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,
-                   int f16_from_col, int num_sms, cudaStream_t stream) {
+                   int f16_from_col, const LnArgs& ln, int num_sms, cudaStream_t stream) {
     if (M <= 0) return 0;
     if (K % BK != 0 || K <= 0) return fail(LSC_E_UNSUPPORTED, "gemm: K must be a positive multiple of 64");
     if (bias == nullptr) return fail(LSC_E_INVALID, "gemm: bias is required");
     switch (gemm_tc_block_n(N)) {
         case 192:
-            return launch_bn<192>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, num_sms, stream);
+            return launch_bn<192>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, ln, num_sms, stream);
         case 256:
-            return launch_bn<256>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, num_sms, stream);
+            return launch_bn<256>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, ln, num_sms, stream);
         case 128:
-            return launch_bn<128>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, num_sms, stream);
+            return launch_bn<128>(tmapA, tmapW, tmapC, bias, residual, M, N, K, epilogue, f16_from_col, ln, num_sms, stream);
         default:
             return fail(LSC_E_UNSUPPORTED, "gemm: N must be a multiple of 128");
     }
