@@ -269,7 +269,8 @@ int lsc_debug_gemm_dev(const void* d_A, const void* d_W, const float* d_bias, co
  * — the layout the QKV GEMM writes), d_ctx receives [T, hidden] bf16.  Lets the tests check it against an fp32 reference.
  */
 int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_seqlens, int32_t n_seq,
-                            int32_t hidden, int32_t heads, int32_t max_seqlen, void* d_ctx, void* stream);
+                            int32_t total_tokens, int32_t hidden, int32_t heads, int32_t max_seqlen,
+                            void* d_ctx, void* stream);
 
 #ifdef __cplusplus
 }

@@ -77,7 +77,7 @@ SIGNATURES = {
     "lsc_index_save": (C.c_int, [_vp, C.c_char_p]),
     "lsc_index_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(_vp)]),
     "lsc_index_destroy": (None, [_vp]),
-    "lsc_debug_attention_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _vp, _vp]),
+    "lsc_debug_attention_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "lsc_debug_gemm_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
 }
 
@@ -287,9 +287,9 @@ def topk_search_static_dev(d_rows_bf16, d_row_ids, n_rows, dim, d_queries, B, k,
                                            _ptr(d_out_scores), stream))
 
 
-def debug_attention_dev(d_qkv, d_cu_seqlens, n_seq, hidden, heads, max_seqlen, d_ctx, stream=0):
-    check(lib().lsc_debug_attention_dev(_ptr(d_qkv), _ptr(d_cu_seqlens), n_seq, hidden, heads, max_seqlen,
-                                        _ptr(d_ctx), stream))
+def debug_attention_dev(d_qkv, d_cu_seqlens, n_seq, total_tokens, hidden, heads, max_seqlen, d_ctx, stream=0):
+    check(lib().lsc_debug_attention_dev(_ptr(d_qkv), _ptr(d_cu_seqlens), n_seq, total_tokens, hidden, heads,
+                                        max_seqlen, _ptr(d_ctx), stream))
 
 
 def debug_gemm_dev(d_A, d_W, d_bias, d_residual, d_C, M, N, K, epilogue, impl, stream=0):

@@ -70,6 +70,14 @@ int make_tmap_bf16_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint
     return make_tmap_bf16(out, base, rows, cols, box_rows, 64, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
+int make_tmap_bf16_box(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                       uint32_t box_cols, int swizzle_bytes) {
+    const CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                  : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                  : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+    return make_tmap_bf16(out, base, rows, cols, box_rows, box_cols, sw);
+}
+
 int make_tmap_bf16_store32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols) {
     return make_tmap_bf16(out, base, rows, cols, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B);
 }

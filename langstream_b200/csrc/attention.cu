@@ -18,6 +18,8 @@
 //   * the key mask is applied only in a sequence's last, partial key block.
 #include <cuda_fp16.h>
 
+#include <cstdlib>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -73,7 +75,7 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 template <int D>
-__global__ void __launch_bounds__(ATT_THREADS, 3)
+__global__ void __launch_bounds__(ATT_THREADS, D == 32 ? 3 : 1)
 attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ cu_seqlens, int H,
                  int heads, __nv_bfloat16* __restrict__ ctx, float scale_log2e) {
     constexpr int LD = D + 8;  // padded row (elements): conflict-free ldmatrix
@@ -246,10 +248,192 @@ attention_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restric
     }
 }
 
+// ---- persistent, double-buffered variant (short sequences) ---------------------------------------
+// One CTA loops over (sequence, head) items; while it computes item i out of one shared-memory buffer,
+// cp.async fills the other buffer with Q, K and V of item i + gridDim.x, so the global-memory latency
+// of every item but the first is hidden.  Q comes from shared memory through ldmatrix as well.
+template <int D>
+__global__ void __launch_bounds__(ATT_THREADS, D == 32 ? 3 : 2)
+attention_pipelined_kernel(const __nv_bfloat16* __restrict__ qkv, const int32_t* __restrict__ cu_seqlens, int H,
+                           int heads, int n_items, int s_pad_max, __nv_bfloat16* __restrict__ ctx,
+                           float scale_log2e) {
+    constexpr int LD = D + 8;
+    constexpr int CPR = D / 8;
+    extern __shared__ __align__(16) uint8_t att_smem[];
+    const uint32_t smem_addr = smem_u32(att_smem);
+    const uint32_t mat_bytes = static_cast<uint32_t>(s_pad_max) * LD * 2;  // one of Q / K / V
+    const size_t row_stride = static_cast<size_t>(3) * H;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, tq = lane & 3;
+    const int lm = lane >> 3, lr = lane & 7;
+    constexpr uint32_t ONES = 0x3C003C00u;
+
+    auto issue = [&](int item, int buf) {
+        const int seq = item / heads, head = item % heads;
+        const int t0 = __ldg(cu_seqlens + seq);
+        const int s = __ldg(cu_seqlens + seq + 1) - t0;
+        const int s_pad = (s + KEY_BLOCK - 1) / KEY_BLOCK * KEY_BLOCK;
+        const __nv_bfloat16* base = qkv + static_cast<size_t>(t0) * row_stride + head * D;
+        const uint32_t dst0 = smem_addr + buf * 3 * mat_bytes;
+        for (int i = threadIdx.x; i < 3 * s_pad * CPR; i += ATT_THREADS) {
+            const int which = i / (s_pad * CPR);  // 0 Q, 1 K, 2 V
+            const int rem = i - which * s_pad * CPR;
+            const int r = rem / CPR, c = rem % CPR;
+            const uint32_t dst = dst0 + which * mat_bytes + (r * LD + c * 8) * 2;
+            if (r < s) cp_async_16(dst, base + static_cast<size_t>(r) * row_stride + which * H + c * 8);
+            else asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(dst), "r"(0) : "memory");
+        }
+    };
+
+    int item = blockIdx.x;
+    if (item < n_items) issue(item, 0);
+    cp_async_commit();
+    for (int buf = 0; item < n_items; item += gridDim.x, buf ^= 1) {
+        const int next = item + gridDim.x;
+        if (next < n_items) issue(next, buf ^ 1);
+        cp_async_commit();   // possibly empty: keeps the group count uniform
+        cp_async_wait<1>();  // the current item's copies have landed
+        __syncthreads();
+        const int seq = item / heads, head = item % heads;
+        const int t0 = __ldg(cu_seqlens + seq);
+        const int s = __ldg(cu_seqlens + seq + 1) - t0;
+        const uint32_t sQ_addr = smem_addr + buf * 3 * mat_bytes;
+        const uint32_t sK_addr = sQ_addr + mat_bytes, sV_addr = sK_addr + mat_bytes;
+        for (int qb = warp; qb * 16 < s; qb += ATT_THREADS / 32) {
+            uint32_t qa[D / 16][4];
+            const int r_lo = qb * 16 + g, r_hi = r_lo + 8;
+#pragma unroll
+            for (int ks = 0; ks < D / 16; ++ks) {
+                const int row = qb * 16 + (lm & 1) * 8 + lr;
+                const int col = ks * 16 + (lm >> 1) * 8;
+                ldmatrix_x4(sQ_addr + (row * LD + col) * 2, qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
+            }
+            // o[0..D/8) = output accumulators, o[D/8] = row sums (every column of that tile holds the sum)
+            float o[D / 8 + 1][4];
+    #pragma unroll
+            for (int i = 0; i <= D / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+            float m_run[2] = {-INFINITY, -INFINITY};
+
+            for (int kb0 = 0; kb0 < s; kb0 += KEY_BLOCK) {
+                float sc[8][4];
+    #pragma unroll
+                for (int i = 0; i < 8; ++i) sc[i][0] = sc[i][1] = sc[i][2] = sc[i][3] = 0.f;
+                // ---- S = Q K^T ----
+    #pragma unroll
+                for (int ks = 0; ks < D / 16; ++ks) {
+    #pragma unroll
+                    for (int nt = 0; nt < 8; nt += 2) {
+                        const int key = kb0 + (nt + (lm >> 1)) * 8 + lr;
+                        const int dof = ks * 16 + (lm & 1) * 8;
+                        uint32_t b0, b1, b2, b3;
+                        ldmatrix_x4(sK_addr + (key * LD + dof) * 2, b0, b1, b2, b3);
+                        mma_bf16_16816(sc[nt], qa[ks], b0, b1);
+                        mma_bf16_16816(sc[nt + 1], qa[ks], b2, b3);
+                    }
+                }
+                // ---- mask (last partial block only) and running max ----
+                if (kb0 + KEY_BLOCK > s) {
+    #pragma unroll
+                    for (int nt = 0; nt < 8; ++nt)
+    #pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (kb0 + nt * 8 + 2 * tq + (j & 1) >= s) sc[nt][j] = -INFINITY;
+                }
+                float mx[2] = {-INFINITY, -INFINITY};
+    #pragma unroll
+                for (int nt = 0; nt < 8; ++nt) {
+                    mx[0] = fmaxf(mx[0], fmaxf(sc[nt][0], sc[nt][1]));
+                    mx[1] = fmaxf(mx[1], fmaxf(sc[nt][2], sc[nt][3]));
+                }
+    #pragma unroll
+                for (int h2 = 0; h2 < 2; ++h2) {
+                    mx[h2] = fmaxf(mx[h2], __shfl_xor_sync(0xffffffffu, mx[h2], 1));
+                    mx[h2] = fmaxf(mx[h2], __shfl_xor_sync(0xffffffffu, mx[h2], 2));
+                }
+                float nms[2];  // -max * scale
+                if (kb0 == 0) {
+                    m_run[0] = mx[0];
+                    m_run[1] = mx[1];
+                } else {
+                    float corr[2];
+    #pragma unroll
+                    for (int h2 = 0; h2 < 2; ++h2) {
+                        const float m_new = fmaxf(m_run[h2], mx[h2]);  // finite: every block has a valid key
+                        corr[h2] = exp2f((m_run[h2] - m_new) * scale_log2e);
+                        m_run[h2] = m_new;
+                    }
+    #pragma unroll
+                    for (int i = 0; i <= D / 8; ++i) {
+                        o[i][0] *= corr[0];
+                        o[i][1] *= corr[0];
+                        o[i][2] *= corr[1];
+                        o[i][3] *= corr[1];
+                    }
+                }
+                nms[0] = -m_run[0] * scale_log2e;
+                nms[1] = -m_run[1] * scale_log2e;
+                // ---- P = exp2(S*scale - max*scale) as packed fp16 A fragments; O += P V; sums += P 1 ----
+    #pragma unroll
+                for (int kk = 0; kk < KEY_BLOCK / 16; ++kk) {
+                    uint32_t pa[4];
+                    pa[0] = exp2_f16x2(fmaf(sc[2 * kk][0], scale_log2e, nms[0]), fmaf(sc[2 * kk][1], scale_log2e, nms[0]));
+                    pa[1] = exp2_f16x2(fmaf(sc[2 * kk][2], scale_log2e, nms[1]), fmaf(sc[2 * kk][3], scale_log2e, nms[1]));
+                    pa[2] = exp2_f16x2(fmaf(sc[2 * kk + 1][0], scale_log2e, nms[0]), fmaf(sc[2 * kk + 1][1], scale_log2e, nms[0]));
+                    pa[3] = exp2_f16x2(fmaf(sc[2 * kk + 1][2], scale_log2e, nms[1]), fmaf(sc[2 * kk + 1][3], scale_log2e, nms[1]));
+    #pragma unroll
+                    for (int nt = 0; nt < D / 8; nt += 2) {
+                        const int key = kb0 + kk * 16 + (lm & 1) * 8 + lr;
+                        const int dof = (nt + (lm >> 1)) * 8;
+                        uint32_t b0, b1, b2, b3;
+                        ldmatrix_x4_trans(sV_addr + (key * LD + dof) * 2, b0, b1, b2, b3);
+                        mma_f16_16816(o[nt], pa, b0, b1);
+                        mma_f16_16816(o[nt + 1], pa, b2, b3);
+                    }
+                    mma_f16_16816(o[D / 8], pa, ONES, ONES);
+                }
+            }
+            // ---- normalise and store ----
+            const float inv0 = 1.0f / o[D / 8][0], inv1 = 1.0f / o[D / 8][2];
+            __nv_bfloat16* obase = ctx + static_cast<size_t>(t0) * H + head * D;
+    #pragma unroll
+            for (int nt = 0; nt < D / 8; ++nt) {
+                const int c = nt * 8 + 2 * tq;
+                if (r_lo < s)
+                    *reinterpret_cast<uint32_t*>(obase + static_cast<size_t>(r_lo) * H + c) =
+                        pack_bf16x2(o[nt][0] * inv0, o[nt][1] * inv0);
+                if (r_hi < s)
+                    *reinterpret_cast<uint32_t*>(obase + static_cast<size_t>(r_hi) * H + c) =
+                        pack_bf16x2(o[nt][2] * inv1, o[nt][3] * inv1);
+            }
+        }
+        __syncthreads();  // the buffer is refilled by the next iteration's prefetch
+    }
+    cp_async_wait<0>();
+}
+
 template <int D>
 int launch_d(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int H, int heads,
              int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream) {
     const int s_pad = (max_seqlen + KEY_BLOCK - 1) / KEY_BLOCK * KEY_BLOCK;
+    const float scale = 1.4426950408889634f / sqrtf(static_cast<float>(D));
+    // short sequences: persistent CTAs with double-buffered Q/K/V (two or three CTAs per SM)
+    const size_t smem_pipe = static_cast<size_t>(2) * 3 * s_pad * (D + 8) * sizeof(__nv_bfloat16);
+    if (smem_pipe <= 112 * 1024) {
+        static int sms_cache[64] = {};
+        int dev = 0;
+        LSC_CUDA(cudaGetDevice(&dev));
+        if (dev >= 0 && dev < 64 && sms_cache[dev] == 0)
+            LSC_CUDA(cudaDeviceGetAttribute(&sms_cache[dev], cudaDevAttrMultiProcessorCount, dev));
+        const int sms = (dev >= 0 && dev < 64) ? sms_cache[dev] : 148;
+        auto pk = attention_pipelined_kernel<D>;
+        LSC_CUDA(cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_pipe)));
+        const int per_sm = smem_pipe <= 74 * 1024 ? 3 : 2;
+        const long long n_items = static_cast<long long>(heads) * n_seq;
+        const int grid_p = static_cast<int>(n_items < static_cast<long long>(sms) * per_sm ? n_items : static_cast<long long>(sms) * per_sm);
+        pk<<<grid_p, ATT_THREADS, smem_pipe, stream>>>(qkv, cu_seqlens, H, heads, static_cast<int>(n_items), s_pad, ctx, scale);
+        LSC_CUDA(cudaGetLastError());
+        return 1;
+    }
     const size_t smem = static_cast<size_t>(2) * s_pad * (D + 8) * sizeof(__nv_bfloat16);
     if (smem > 227 * 1024) return fail(LSC_E_UNSUPPORTED, "attention: sequence too long for shared memory");
     auto kern = attention_kernel<D>;
@@ -265,11 +449,21 @@ int launch_d(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int
 
 }  // namespace
 
-int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int H, int heads,
+int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream) {
     if (n_seq <= 0 || max_seqlen <= 0) return 0;
     const int d = H / heads;
     if (d * heads != H) return fail(LSC_E_INVALID, "attention: hidden not divisible by heads");
+    static const bool legacy_only = getenv("LSC_ATTN_LEGACY") != nullptr;  // debug: force the mma.sync kernel
+    if (d == 32 && max_seqlen <= 128 && !legacy_only) {
+        static int sms_cache[64] = {};
+        int dev = 0;
+        LSC_CUDA(cudaGetDevice(&dev));
+        if (dev >= 0 && dev < 64 && sms_cache[dev] == 0)
+            LSC_CUDA(cudaDeviceGetAttribute(&sms_cache[dev], cudaDevAttrMultiProcessorCount, dev));
+        return attention_tc_launch(qkv, cu_seqlens, n_seq, T, H, heads, max_seqlen, ctx,
+                                   (dev >= 0 && dev < 64) ? sms_cache[dev] : 148, stream);
+    }
     if (d == 32) return launch_d<32>(qkv, cu_seqlens, n_seq, H, heads, max_seqlen, ctx, stream);
     if (d == 64) return launch_d<64>(qkv, cu_seqlens, n_seq, H, heads, max_seqlen, ctx, stream);
     return fail(LSC_E_UNSUPPORTED, "attention: head dimension must be 32 or 64");
@@ -278,11 +472,11 @@ int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_
 }  // namespace lsc
 
 extern "C" int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_seqlens, int32_t n_seq,
-                                       int32_t hidden, int32_t heads, int32_t max_seqlen, void* d_ctx,
-                                       void* stream) {
+                                       int32_t total_tokens, int32_t hidden, int32_t heads, int32_t max_seqlen,
+                                       void* d_ctx, void* stream) {
     if (d_qkv == nullptr || d_cu_seqlens == nullptr || d_ctx == nullptr || n_seq < 0 || hidden <= 0 || heads <= 0)
         return lsc::fail(LSC_E_INVALID, "lsc_debug_attention_dev: bad argument");
-    int rc = lsc::attention_launch(static_cast<const __nv_bfloat16*>(d_qkv), d_cu_seqlens, n_seq, hidden, heads,
-                                   max_seqlen, static_cast<__nv_bfloat16*>(d_ctx), static_cast<cudaStream_t>(stream));
+    int rc = lsc::attention_launch(static_cast<const __nv_bfloat16*>(d_qkv), d_cu_seqlens, n_seq, total_tokens, hidden,
+                                   heads, max_seqlen, static_cast<__nv_bfloat16*>(d_ctx), static_cast<cudaStream_t>(stream));
     return rc < 0 ? rc : LSC_OK;
 }

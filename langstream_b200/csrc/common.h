@@ -86,6 +86,9 @@ int make_tmap_bf16_sw128(CUtensorMap* out, const void* base, uint64_t rows, uint
 // Store map of a bf16 row-major [rows, cols] output: box = [32 rows, 32 cols], SWIZZLE_64B (the GEMM
 // epilogue stages 32x32 blocks in shared memory and writes them with TMA; rows past `rows` are clipped).
 int make_tmap_bf16_store32(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols);
+// Any 16-bit row-major tensor: box [box_rows, box_cols], swizzle 0 / 32 / 64 / 128 bytes.
+int make_tmap_bf16_box(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows,
+                       uint32_t box_cols, int swizzle_bytes);
 
 // ---- kernel launchers (defined in the .cu files) ---------------------------------------------
 enum GemmEpilogue {
@@ -138,8 +141,12 @@ int embed_ln_launch(const int32_t* token_ids, const int32_t* cu_seqlens, int n_s
 int layernorm_launch(const __nv_bfloat16* in, const float* gamma, const float* beta, float eps,
                      __nv_bfloat16* out, int T, int H, cudaStream_t stream);
 // Packed variable-length multi-head self-attention over qkv [T,3H] -> ctx [T,H].
-int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int H, int heads,
+// qkv: Q and K thirds bf16, V third fp16.  Dispatches to the tcgen05 kernel (attention_tc.cu) for
+// d_head 32 and sequences of at most 128 tokens, else to the mma.sync kernel (attention.cu).
+int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream);
+int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
+                        int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
 // Masked mean-pool over each sequence's tokens + L2 normalisation -> fp32 [n_seq,H].  With `stats`
 // (per-row partial sums, see LnArgs) x holds pre-LayerNorm rows and the final LayerNorm (gamma, beta)
 // is applied on the fly.

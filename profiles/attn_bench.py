@@ -14,10 +14,10 @@ for name, n, L, H, heads, ragged in [("minilm 1024x128", 1024, 128, 384, 12, Fal
     qkv[:, 2 * H:] = qkv[:, 2 * H:].to(torch.float16).view(torch.bfloat16)
     ctx = torch.empty(T, H, device=dev, dtype=torch.bfloat16)
     d_cu = torch.from_numpy(cu).to(dev)
-    for _ in range(3): _native.debug_attention_dev(qkv, d_cu, n, H, heads, int(lens.max()), ctx, st)
+    for _ in range(3): _native.debug_attention_dev(qkv, d_cu, n, T, H, heads, int(lens.max()), ctx, st)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(20): _native.debug_attention_dev(qkv, d_cu, n, H, heads, int(lens.max()), ctx, st)
+    for _ in range(20): _native.debug_attention_dev(qkv, d_cu, n, T, H, heads, int(lens.max()), ctx, st)
     e1.record(); torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / 20 * 1000
     flops = 4.0 * H * float((lens.astype(np.float64) ** 2).sum())

@@ -44,7 +44,7 @@ def test_attention_matches_fp32_reference(native_lib, cuda_device, H, heads, len
     packed[:, 2 * H:] = qkv[:, 2 * H:].to(torch.float16).view(torch.bfloat16)
     ctx = torch.full((T, H), float("nan"), dtype=torch.bfloat16, device=cuda_device)
     d_cu = torch.from_numpy(cu).to(cuda_device)
-    _native.debug_attention_dev(packed, d_cu, len(lens), H, heads, max(lens), ctx,
+    _native.debug_attention_dev(packed, d_cu, len(lens), T, H, heads, max(lens), ctx,
                                 torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     ref = _reference(qkv, cu, H, heads)
