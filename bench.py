@@ -233,9 +233,9 @@ def run_cuda(args):
     for _ in range(max(args.warmup, 3)):
         step_dev()
     barrier()
+    # ---- headline: K steps, nothing but the kernels in the timed region ----
     sampler = ClockSampler(local_rank)
     sampler.start()
-    enc.set_profiling(True)
     launches0 = enc.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -247,9 +247,21 @@ def run_cuda(args):
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
     clocks = sampler.stop()
     launches = enc.launch_count - launches0
+    value = world * N_SEQ * args.steps / (ms_total / 1000.0)
+
+    # ---- same K steps again with every launch bracketed by CUDA events on the launching stream:
+    #      per-kernel durations for the roofline (the events add a few microseconds per launch, which is
+    #      why this pass is not the headline) ----
+    enc.set_profiling(True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        step_dev()
+    ev1.record()
+    barrier()
+    ms_profiled = max_over_ranks(ev0.elapsed_time(ev1))
     prof = enc.read_profile()
     enc.set_profiling(False)
-    value = world * N_SEQ * args.steps / (ms_total / 1000.0)
 
     # roofline of the dominant kernel (the tcgen05 GEMM): algorithmic dense FLOPs / event-timed GEMM time
     total_flop, dense_flop = flops_per_sequence(spec, SEQ_LEN)
@@ -257,14 +269,23 @@ def run_cuda(args):
     gemm_flops_per_launch = dense_flop * N_SEQ * args.steps / max(gemm_launches, 1)
     gemm_tflops = dense_flop * N_SEQ * args.steps / (gemm_ms / 1000.0) / 1e12 if gemm_ms > 0 else 0.0
     peak_tf = pk["bf16_tflops_sustained"]
+    traffic = None
+    tpath = ROOT / "profiles" / "r01_traffic.json"
+    if tpath.exists():
+        try:
+            traffic = json.loads(tpath.read_text())["gemm_tc_kernel"]["dram_bytes_per_launch_avg"]
+        except Exception:
+            traffic = None
     roofline = {
-        "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05/TMEM/TMA, all 4 encoder GEMM shapes)",
+        "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05/TMEM/TMA, all 4 encoder GEMM shapes, LayerNorm folded in)",
         "achieved": gemm_tflops, "peak": peak_tf, "unit": "TFLOP/s",
-        "frac": gemm_tflops / peak_tf if peak_tf else None, "traffic": None,
+        "frac": gemm_tflops / peak_tf if peak_tf else None, "traffic": traffic,
+        "traffic_source": "ncu --set full capture, profiles/r01_ncu_full_encoder.csv (dram read+write, average of the 4 shapes)",
         "peak_source": pk_src + ", sustained bf16 (kernel timed inside a long step)",
         "flops_per_launch": gemm_flops_per_launch,
         "avg_launch_ms": gemm_ms / max(gemm_launches, 1),
         "kernel_share_of_step": {k: v[0] / max(sum(x[0] for x in prof.values()), 1e-9) for k, v in prof.items()},
+        "ms_per_step_with_event_profiling": ms_profiled / args.steps,
         "whole_step_tflops": total_flop * N_SEQ * args.steps / (ms_total / 1000.0) / 1e12,
     }
 
@@ -321,6 +342,11 @@ def run_cuda(args):
         topk = {"corpus": f"{rows_total} x {TOPK_DIM} bf16, seed 42, row-sharded over {world} GPU(s)", "k": TOPK_K,
                 "batches": {}}
         steps_topk = max(3, min(args.steps, 20))
+        topk_traffic = None
+        try:
+            topk_traffic = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())["topk_scan_kernel"]["dram_bytes_per_launch"]
+        except Exception:
+            pass
         for B in (1, 64, 1024):
             g = torch.Generator(device=dev).manual_seed(43)
             q = torch.randn(B, TOPK_DIM, generator=g, device=dev)
@@ -359,13 +385,12 @@ def run_cuda(args):
             if B <= 128:
                 entry["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
                                      "frac": gbs / pk["hbm_gbs"], "bytes_per_launch": bytes_per_launch,
-                                     "traffic": None}
+                                     "traffic": topk_traffic if (world == 1 and rows_total == TOPK_ROWS) else None}
             else:
                 tf = 2.0 * B * n_local * TOPK_DIM * steps_topk / (scan_ms / 1000.0) / 1e12 if scan_ms > 0 else 0.0
                 entry["roofline"] = {"bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s",
                                      "frac": tf / peak_tf}
             topk["batches"][str(B)] = entry
-        topk["gpu_launches_per_query_batch_B1"] = None
         ix.close()
 
     # ---- CPU baseline (rank 0, N=1 only): reference-shaped oracle on a bounded sample ------------

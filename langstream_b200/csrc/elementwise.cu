@@ -138,22 +138,46 @@ __global__ void pool_l2_kernel(const __nv_bfloat16* __restrict__ x, const int32_
     int t = t0;
     if (stats != nullptr) {
         // x holds pre-LayerNorm rows; apply the final LayerNorm on the fly:
-        // mean_t LN(x_t) = gamma * mean_t((x_t - mu_t) * rstd_t) + beta  (for a non-empty sequence)
+        // mean_t LN(x_t) = gamma * mean_t((x_t - mu_t) * rstd_t) + beta  (for a non-empty sequence).
+        // Token statistics are finalised once per token into shared memory, in blocks of 128 tokens.
+        __shared__ float2 tok[128];  // (mean * rstd, rstd)
         const float inv_h = 1.0f / static_cast<float>(H);
-        for (; t < t1; ++t) {
-            const float2* sp = reinterpret_cast<const float2*>(stats) + static_cast<size_t>(t) * stats_p;
-            float sum = 0.f, sq = 0.f;
-            for (int p = 0; p < stats_p; ++p) {
-                const float2 v = __ldg(sp + p);
-                sum += v.x;
-                sq += v.y;
+        for (int tb = t0; tb < t1; tb += 128) {
+            const int nb = min(128, t1 - tb);
+            __syncthreads();
+            for (int i = threadIdx.x; i < nb; i += blockDim.x) {
+                const float2* sp = reinterpret_cast<const float2*>(stats) + static_cast<size_t>(tb + i) * stats_p;
+                float sum = 0.f, sq = 0.f;
+                for (int p = 0; p < stats_p; ++p) {
+                    const float2 v = __ldg(sp + p);
+                    sum += v.x;
+                    sq += v.y;
+                }
+                const float mean = sum * inv_h;
+                const float rstd = rsqrtf(fmaxf(sq * inv_h - mean * mean, 0.f) + eps);
+                tok[i] = make_float2(mean * rstd, rstd);
             }
-            const float mean = sum * inv_h;
-            const float rstd = rsqrtf(fmaxf(sq * inv_h - mean * mean, 0.f) + eps);
-            const uint32_t w0 = __ldg(xp + static_cast<size_t>(t) * H2);
-            a0 += (bf16_lo(w0) - mean) * rstd;
-            a1 += (bf16_hi(w0) - mean) * rstd;
+            __syncthreads();
+            int i = 0;
+            for (; i + 4 <= nb; i += 4) {
+                const uint32_t w0 = __ldg(xp + static_cast<size_t>(tb + i) * H2);
+                const uint32_t w1 = __ldg(xp + static_cast<size_t>(tb + i + 1) * H2);
+                const uint32_t w2 = __ldg(xp + static_cast<size_t>(tb + i + 2) * H2);
+                const uint32_t w3 = __ldg(xp + static_cast<size_t>(tb + i + 3) * H2);
+                const float2 s0 = tok[i], s1 = tok[i + 1], s2 = tok[i + 2], s3 = tok[i + 3];
+                a0 += (fmaf(bf16_lo(w0), s0.y, -s0.x) + fmaf(bf16_lo(w1), s1.y, -s1.x)) +
+                      (fmaf(bf16_lo(w2), s2.y, -s2.x) + fmaf(bf16_lo(w3), s3.y, -s3.x));
+                a1 += (fmaf(bf16_hi(w0), s0.y, -s0.x) + fmaf(bf16_hi(w1), s1.y, -s1.x)) +
+                      (fmaf(bf16_hi(w2), s2.y, -s2.x) + fmaf(bf16_hi(w3), s3.y, -s3.x));
+            }
+            for (; i < nb; ++i) {
+                const uint32_t w0 = __ldg(xp + static_cast<size_t>(tb + i) * H2);
+                const float2 s0 = tok[i];
+                a0 += fmaf(bf16_lo(w0), s0.y, -s0.x);
+                a1 += fmaf(bf16_hi(w0), s0.y, -s0.x);
+            }
         }
+        t = t1;
         const float cnt = static_cast<float>(t1 - t0);
         if (cnt > 0.f) {
             a0 = a0 * __ldg(gamma + 2 * j) + cnt * __ldg(beta + 2 * j);
