@@ -29,7 +29,8 @@ struct lsc_index {
     int64_t* d_ids = nullptr;
     std::vector<int64_t> ids;                      // host mirror of d_ids[0..n)
     std::unordered_map<int64_t, int64_t> slot_of;  // id -> slot
-    CUtensorMap tmapC;
+    CUtensorMap tmapC;     // 256-row boxes (query-major scan)
+    CUtensorMap tmapC128;  // 128-row boxes (row-major scan)
     // query / scratch buffers (grow on demand)
     int64_t cap_q = 0;      // padded query rows the buffers hold
     int64_t cap_cand = 0;   // candidate entries the scratch holds
@@ -76,6 +77,7 @@ int grow_rows(lsc_index* ix, int64_t need) {
     ix->d_rows = rows;
     ix->d_ids = ids;
     ix->capacity = cap;
+    LSC_TRY(make_tmap_bf16_sw128(&ix->tmapC128, ix->d_rows, static_cast<uint64_t>(cap), ix->dim, 128));
     return make_tmap_bf16_sw128(&ix->tmapC, ix->d_rows, static_cast<uint64_t>(cap), ix->dim, 256);
 }
 
@@ -135,12 +137,17 @@ int search_dev(lsc_index* ix, const float* d_queries, int B, int k, int64_t* d_o
     const int bpad = (B + TK_QROWS - 1) / TK_QROWS * TK_QROWS;
     LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st));
     const int n_rows = static_cast<int>(ix->n);
-    const int grid = topk_scan_grid(n_rows, ix->num_sms);
+    const bool rows_kernel = topk_scan_rows_supported(ix->dim, k);
+    const int grid = rows_kernel ? topk_scan_rows_grid(n_rows, ix->num_sms) : topk_scan_grid(n_rows, ix->num_sms);
     for (int qb = 0; qb * TK_QROWS < B; ++qb) {
         const int nq = std::min(TK_QROWS, B - qb * TK_QROWS);
         const size_t off = static_cast<size_t>(qb) * grid * TK_QROWS * k;
-        LSC_LAUNCH(1, topk_scan_launch(ix->tmapQ, ix->tmapC, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
-                                    ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+        if (rows_kernel)
+            LSC_LAUNCH(1, topk_scan_rows_launch(ix->tmapQ, ix->tmapC128, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
+                                                ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+        else
+            LSC_LAUNCH(1, topk_scan_launch(ix->tmapQ, ix->tmapC, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
+                                           ix->d_cand_scores + off, ix->d_cand_idx + off, st));
     }
     LSC_LAUNCH(2, topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, d_out_ids,
                                       d_out_scores, st));

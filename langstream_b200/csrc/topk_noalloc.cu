@@ -117,10 +117,14 @@ extern "C" int lsc_topk_search_static_dev(const void* d_rows_bf16, const int64_t
     LSC_TRY(make_tmap_bf16_sw128(&tmapC, d_rows_bf16, static_cast<uint64_t>(n_rows), static_cast<uint64_t>(dim), 256));
 
     const int n = static_cast<int>(n_rows);
-    const int grid = topk_scan_grid(n, s->num_sms);
+    const bool rows_kernel = topk_scan_rows_supported(dim, k);
+    if (rows_kernel)  // the row-major scan reads the corpus through 128-row boxes
+        LSC_TRY(make_tmap_bf16_sw128(&tmapC, d_rows_bf16, static_cast<uint64_t>(n_rows), static_cast<uint64_t>(dim), 128));
+    const int grid = rows_kernel ? topk_scan_rows_grid(n, s->num_sms) : topk_scan_grid(n, s->num_sms);
     int rc = normalize_rows_launch(d_queries, B, TK_QROWS, dim, nullptr, d_q, st);  // rewrites all 128 rows
     if (rc < 0) return rc;
-    rc = topk_scan_launch(tmapQ, tmapC, 0, B, n, dim, k, grid, d_cand_scores, d_cand_idx, st);
+    rc = rows_kernel ? topk_scan_rows_launch(tmapQ, tmapC, 0, B, n, dim, k, grid, d_cand_scores, d_cand_idx, st)
+                     : topk_scan_launch(tmapQ, tmapC, 0, B, n, dim, k, grid, d_cand_scores, d_cand_idx, st);
     if (rc < 0) return rc;
     rc = topk_merge_scan_launch(d_cand_scores, d_cand_idx, grid, B, k, d_row_ids, d_out_ids, d_out_scores, st);
     if (rc < 0) return rc;

@@ -1,0 +1,367 @@
+// Brute-force cosine top-k, row-major selection (k <= 16): the second scan kernel behind
+// lsc_index_search*, same contract as topk_scan_kernel in topk.cu (HerdDB's
+// `ORDER BY cosine_similarity(...) DESC LIMIT k`, JdbcDataSourceProvider.java:103-124).
+//
+// topk.cu puts the QUERIES on the TMEM lanes (thread = query): with 32 queries per warp, every lane has
+// its own threshold and a hit in any lane sends the whole warp down the insertion path, which costs
+// 1.6-1.8x the HBM time at B = 64.  Here the operands are swapped: the corpus tile is the A operand
+// (M = 128 rows), the query block the B operand (N = queries), so the score tile has ROWS on lanes and
+// queries on columns.  For one query the 32 lanes of a warp hold 32 different rows against ONE
+// threshold, so the common case is branch-free: each lane builds the bit mask of queries its row beats
+// (32 compares against broadcast thresholds) and one warp-wide OR says whether anything happened.
+// Sixteen selection warps: warp (quadrant, chunk) looks at 32 rows x 32 queries of every tile, so a full
+// query block keeps four warps on each scheduler (one warp per scheduler runs at the latency of every
+// single instruction and cannot keep up with HBM).
+// A hit is APPENDED by its own lane to the query's candidate buffer in shared memory (one shared-memory
+// atomic for the slot; the score of the hit column is re-read from TMEM, which is how a run-time column
+// index is done without local memory); nothing warp-wide happens per hit.  After each tile the selection
+// warps meet at a named barrier, and every query whose buffer holds >= TR_TRIG candidates is compacted into
+// its sorted top-k list by the warp that owns it: all-pairs ranking, every lane counts how many of the
+// buffered candidates and list entries precede its own candidate / list entry and stores it at that
+// position - no serial insertion.  The compaction also raises the query's threshold.  With k = 10 a query
+// is compacted about 7 times per CTA over a 10M-row scan (each compaction lets the seen-row count grow
+// 2.6x before the buffer refills), against ~100 list insertions when every hit is inserted at once.
+// A buffer that overflows inside one tile (the first tiles, thresholds still at -inf) leaves the
+// (row, query) pair pending: the tile is re-tested for pending pairs after the compaction, against the
+// raised thresholds, until none is left.
+// At the end the lists are written out as the same [128][k] per-CTA candidates topk_merge_kernel consumes.
+#include <cstdlib>
+
+#include "common.h"
+#include "ptx.cuh"
+#include "topk.h"
+
+namespace lsc {
+
+namespace {
+
+constexpr int TR_SEL_WARPS = 16;  // selection warp s: TMEM lane quadrant (s + 2) % 4, query chunk s / 4
+constexpr int TR_THREADS = 64 + 32 * TR_SEL_WARPS;  // warp 0 TMA, warp 1 MMA, warps 2-17 selection
+constexpr int TR_BM = 128;       // corpus rows per tile
+constexpr int TR_BK = 64;
+constexpr int TR_STAGE_BYTES = TR_BM * TR_BK * 2;      // 16 KB: one 64-dim slice of a corpus tile
+constexpr int TR_QBLK_BYTES = TK_QROWS * TR_BK * 2;    // 16 KB: one 64-dim slice of the query block
+constexpr int TR_MAX_STAGES = 8;
+constexpr int TR_ACC_STRIDE = 128;                     // TMEM columns per accumulator stage (N <= 128)
+constexpr int TR_BUF = 32;                             // candidate buffer entries per query (= one per lane)
+constexpr int TR_TRIG = 16;                            // compact a query once its buffer holds this many
+constexpr int TR_FIXED_EXTRA = TK_QROWS * (TR_BUF * 8 + 8) + 256 + 1024;  // buffers, thresholds, counters, barriers, alignment
+
+// One warp merges the n (<= 32) buffered candidates of a query into its sorted top-k list (k <= 16) by
+// all-pairs ranking.  Order: higher score first, equal scores by lower row number (the reference's stable
+// descending sort); rows are unique, so the positions are a permutation.  Lane t holds candidate t and, for
+// t < k, list entry t; the others' values are broadcast reads from shared memory, all independent.
+// ls / li / bs / bi / thr are 32-bit shared-window addresses; the caller owns the query.
+__device__ __forceinline__ void compact_query(uint32_t ls, uint32_t li, uint32_t bs, uint32_t bi, uint32_t thr,
+                                              int k, int n) {
+    const int lane = threadIdx.x & 31;
+    const bool hc = lane < n, hl = lane < k;
+    const float cs = hc ? lds_f32(bs + 4 * lane) : -INFINITY;
+    const int32_t cr = hc ? lds_s32(bi + 4 * lane) : 0x7fffffff;
+    const float es = hl ? lds_f32(ls + 4 * lane) : -INFINITY;
+    const int32_t er = hl ? lds_s32(li + 4 * lane) : -1;
+    int cpos = 0;     // candidates and valid list entries in front of my candidate
+    int epos = lane;  // list entries in front of my list entry (their order is kept) + candidates in front
+    for (int t = 0; t < n; ++t) {
+        const float s = lds_f32(bs + 4 * t);
+        const int32_t r = lds_s32(bi + 4 * t);
+        cpos += (s > cs || (s == cs && r < cr)) ? 1 : 0;
+        epos += (s > es || (s == es && r < er)) ? 1 : 0;  // an empty slot (-inf, -1) is behind everything
+    }
+    for (int t = 0; t < k; ++t) {
+        const float s = lds_f32(ls + 4 * t);
+        const int32_t r = lds_s32(li + 4 * t);
+        cpos += (r >= 0 && (s > cs || (s == cs && r < cr))) ? 1 : 0;
+    }
+    __syncwarp();  // every lane has read the old list
+    if (hc && cpos < k) {
+        sts_f32(ls + 4 * cpos, cs);
+        sts_s32(li + 4 * cpos, cr);
+        if (cpos == k - 1) sts_f32(thr, cs);
+    }
+    if (hl && epos < k) {
+        sts_f32(ls + 4 * epos, es);
+        sts_s32(li + 4 * epos, er);
+        if (epos == k - 1) sts_f32(thr, er >= 0 ? es : -INFINITY);
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(TR_THREADS, 1)
+topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constant__ CUtensorMap tmapC,
+                      int q_row0, int nq, int n_rows, int dim, int k, int stages, uint32_t idesc,
+                      float* __restrict__ cand_scores, int32_t* __restrict__ cand_idx) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    const int num_kb = dim / TR_BK;
+    const uint32_t sQ = smem_u32(smem);
+    const uint32_t sC = sQ + num_kb * TR_QBLK_BYTES;
+    uint8_t* after_ring = smem + num_kb * TR_QBLK_BYTES + stages * TR_STAGE_BYTES;
+    // per-query state shared by the CTA: sorted list [128][k] (scores, rows), candidate buffer [128][TR_BUF],
+    // current k-th score, number of buffered candidates
+    // (all held as 32-bit shared-window addresses, see ptx.cuh)
+    const uint32_t lists_s = smem_u32(after_ring);
+    const uint32_t lists_i = lists_s + 4 * TK_QROWS * k;
+    const uint32_t buf_s = lists_i + 4 * TK_QROWS * k;
+    const uint32_t buf_i = buf_s + 4 * TK_QROWS * TR_BUF;
+    const uint32_t thrs = buf_i + 4 * TK_QROWS * TR_BUF;
+    const uint32_t cnt = thrs + 4 * TK_QROWS;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * TK_QROWS * k + 8 * TK_QROWS * TR_BUF + 8 * TK_QROWS);
+    const uint32_t bar_full = smem_u32(bars);
+    const uint32_t bar_empty = bar_full + 8 * TR_MAX_STAGES;
+    const uint32_t bar_tfull = bar_empty + 8 * TR_MAX_STAGES;
+    const uint32_t bar_tempty = bar_tfull + 16;
+    const uint32_t bar_q = bar_tempty + 16;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(bars + 2 * TR_MAX_STAGES + 5);
+    const uint32_t again_epoch = smem_u32(bars + 2 * TR_MAX_STAGES + 6);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmapQ);
+        tma_prefetch_desc(&tmapC);
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(bar_full + 8 * s, 1);
+            mbar_init(bar_empty + 8 * s, 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(bar_tfull + 8 * a, 1);
+            mbar_init(bar_tempty + 8 * a, 4 * ((nq + 31) / 32));  // one arrival per scanning warp
+        }
+        mbar_init(bar_q, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), 256);
+        tmem_relinquish();
+    }
+    for (int i = threadIdx.x; i < TK_QROWS * k; i += TR_THREADS) {
+        sts_f32(lists_s + 4 * i, -INFINITY);
+        sts_s32(lists_i + 4 * i, -1);
+    }
+    for (int i = threadIdx.x; i < TK_QROWS; i += TR_THREADS) {
+        sts_f32(thrs + 4 * i, -INFINITY);
+        sts_s32(cnt + 4 * i, 0);
+    }
+    if (threadIdx.x == 0) sts_s32(again_epoch, -1);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int num_tiles = (n_rows + TR_BM - 1) / TR_BM;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            mbar_arrive_expect_tx(bar_q, num_kb * TR_QBLK_BYTES);
+            for (int kb = 0; kb < num_kb; ++kb)
+                tma_load_2d(sQ + kb * TR_QBLK_BYTES, &tmapQ, bar_q, kb * TR_BK, q_row0);
+            const uint64_t pol = policy_evict_first();
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    mbar_arrive_expect_tx(bar_full + 8 * stage, TR_STAGE_BYTES);
+                    tma_load_2d_hint(sC + stage * TR_STAGE_BYTES, &tmapC, bar_full + 8 * stage, kb * TR_BK,
+                                     tile * TR_BM, pol);
+                    if (++stage == stages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            mbar_wait(bar_q, 0);
+            tc_fence_after();
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(bar_tempty + 8 * acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * TR_ACC_STRIDE;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(bar_full + 8 * stage, phase);
+                    tc_fence_after();
+                    const uint64_t da = umma_desc_sw128(sC + stage * TR_STAGE_BYTES);  // corpus rows: M
+                    const uint64_t db = umma_desc_sw128(sQ + kb * TR_QBLK_BYTES);      // queries: N
+#pragma unroll
+                    for (int kk = 0; kk < TR_BK / 16; ++kk)
+                        umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
+                    umma_commit(bar_empty + 8 * stage);
+                    if (++stage == stages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(bar_tfull + 8 * acc);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+    } else {
+        // ===== selection: warp (quadrant, chunk); lane = corpus row, columns = the chunk's 32 queries =====
+        const int quad = warp & 3;
+        const int sw = warp - 2;   // selection warp 0..15; it owns the queries q with q % 16 == sw for compaction
+        const int c = sw >> 2;     // query chunk this warp scans
+        const int nchunks = (nq + 31) / 32;
+        const bool scans = c < nchunks;
+        const int qlim = nq - c * 32;  // queries of this chunk that exist
+        const uint32_t qmask = qlim >= 32 ? 0xffffffffu : (qlim > 0 ? ((1u << qlim) - 1u) : 0u);
+        const int myq = lane * TR_SEL_WARPS + sw;  // lanes 0..7: the queries this warp compacts
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        int epoch = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int32_t row = tile * TR_BM + quad * 32 + lane;
+            const uint32_t tcol = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * TR_ACC_STRIDE + c * 32;
+            uint32_t pend = 0u;  // (row, query) pairs whose append found the buffer full
+            bool released = !scans;
+            if (scans) {
+                mbar_wait(bar_tfull + 8 * acc, acc_phase);
+                tc_fence_after();
+            }
+            for (int round = 0;; ++round, ++epoch) {
+                // ---- append phase ----
+                if (scans && (round == 0 || __any_sync(0xffffffffu, pend != 0u))) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(tcol, v);
+                    tmem_ld_wait();
+                    const uint32_t tp = thrs + 4 * c * 32;  // broadcast reads
+                    uint32_t m = 0;
+#pragma unroll
+                    for (int j4 = 0; j4 < 8; ++j4) {
+                        const float4 t = lds_f32x4(tp + 16 * j4);
+                        m |= (__uint_as_float(v[j4 * 4 + 0]) > t.x ? 1u : 0u) << (j4 * 4 + 0);
+                        m |= (__uint_as_float(v[j4 * 4 + 1]) > t.y ? 1u : 0u) << (j4 * 4 + 1);
+                        m |= (__uint_as_float(v[j4 * 4 + 2]) > t.z ? 1u : 0u) << (j4 * 4 + 2);
+                        m |= (__uint_as_float(v[j4 * 4 + 3]) > t.w ? 1u : 0u) << (j4 * 4 + 3);
+                    }
+                    m &= row < n_rows ? qmask : 0u;
+                    if (round > 0) m &= pend;
+                    pend = 0u;
+                    uint32_t any = __reduce_or_sync(0xffffffffu, m);
+                    while (any) {  // warp-uniform; rare once the lists have warmed up
+                        const int j = __ffs(any) - 1;
+                        any &= any - 1;
+                        const uint32_t sc = tmem_ld_32x1(tcol + j);  // this lane's score against query c*32+j
+                        tmem_ld_wait();
+                        if ((m >> j) & 1u) {
+                            const int q = c * 32 + j;
+                            const int pos = atoms_add_s32(cnt + 4 * q, 1);
+                            if (pos < TR_BUF) {
+                                sts_f32(buf_s + 4 * (q * TR_BUF + pos), __uint_as_float(sc));
+                                sts_s32(buf_i + 4 * (q * TR_BUF + pos), row);
+                            } else {
+                                pend |= 1u << j;
+                            }
+                        }
+                    }
+                }
+                if (pend != 0u) sts_s32(again_epoch, epoch);
+                if (!released && !__any_sync(0xffffffffu, pend != 0u)) {
+                    // this warp is done with its part of the tile's accumulator
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+                    released = true;
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
+                // ---- compaction phase: buffers are stable until the second barrier ----
+                const bool again = lds_s32(again_epoch) == epoch;
+                const int n_my = (lane < TK_QROWS / TR_SEL_WARPS && myq < nq) ? lds_s32(cnt + 4 * myq) : 0;
+                uint32_t need = __ballot_sync(0xffffffffu, n_my >= TR_TRIG);
+                while (need) {
+                    const int l = __ffs(need) - 1;
+                    need &= need - 1;
+                    const int q = l * TR_SEL_WARPS + sw;
+                    int n = __shfl_sync(0xffffffffu, n_my, l);
+                    n = n < TR_BUF ? n : TR_BUF;
+                    compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * TR_BUF, buf_i + 4 * q * TR_BUF,
+                                  thrs + 4 * q, k, n);
+                    if (lane == 0) sts_s32(cnt + 4 * q, 0);
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
+                if (!again) break;  // CTA-uniform
+            }
+            ++epoch;
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+        // ---- flush what is left in the buffers, then the CTA's lists are final ----
+        {
+            const int n_my = (lane < TK_QROWS / TR_SEL_WARPS && myq < nq) ? lds_s32(cnt + 4 * myq) : 0;
+            uint32_t need = __ballot_sync(0xffffffffu, n_my > 0);
+            while (need) {
+                const int l = __ffs(need) - 1;
+                need &= need - 1;
+                const int q = l * TR_SEL_WARPS + sw;
+                int n = __shfl_sync(0xffffffffu, n_my, l);
+                n = n < TR_BUF ? n : TR_BUF;
+                compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * TR_BUF, buf_i + 4 * q * TR_BUF,
+                              thrs + 4 * q, k, n);
+            }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
+        for (int i = sw * 32 + lane; i < nq * k; i += 32 * TR_SEL_WARPS) {
+            const int q = i / k, pp = i % k;
+            const size_t base = (static_cast<size_t>(blockIdx.x) * TK_QROWS + q) * k;
+            const int32_t r = lds_s32(lists_i + 4 * i);
+            cand_scores[base + pp] = r >= 0 ? lds_f32(lists_s + 4 * i) : -INFINITY;
+            cand_idx[base + pp] = r;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
+}  // namespace
+
+int topk_scan_rows_grid(int n_rows, int num_sms) {
+    const int tiles = (n_rows + TR_BM - 1) / TR_BM;
+    return tiles < num_sms ? tiles : num_sms;
+}
+
+bool topk_scan_rows_supported(int dim, int k) {
+    static const bool legacy = getenv("LSC_TOPK_LEGACY") != nullptr;  // debug: force the query-major kernel
+    if (legacy || k > 16 || dim % TR_BK != 0 || dim <= 0 || dim > 512) return false;
+    const int fixed = (dim / TR_BK) * TR_QBLK_BYTES + TK_QROWS * k * 8 + TR_FIXED_EXTRA;
+    return (227 * 1024 - fixed) / TR_STAGE_BYTES >= 3;
+}
+
+// tmapC here must have a box of 128 rows x 64 columns (the query-major kernel uses 256-row boxes).
+int topk_scan_rows_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows,
+                          int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream) {
+    if (!topk_scan_rows_supported(dim, k)) return fail(LSC_E_UNSUPPORTED, "top-k (row-major): unsupported dim / k");
+    const int fixed = (dim / TR_BK) * TR_QBLK_BYTES + TK_QROWS * k * 8 + TR_FIXED_EXTRA;
+    int stages = (227 * 1024 - fixed) / TR_STAGE_BYTES;
+    if (stages > TR_MAX_STAGES) stages = TR_MAX_STAGES;
+    const size_t smem = static_cast<size_t>(fixed) + static_cast<size_t>(stages) * TR_STAGE_BYTES;
+    int n_mma = (nq + 15) / 16 * 16;
+    if (n_mma < 16) n_mma = 16;
+    const uint32_t idesc = umma_idesc_bf16(TR_BM, static_cast<uint32_t>(n_mma));
+    static bool configured[64] = {};
+    int dev = 0;
+    LSC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+        LSC_CUDA(cudaFuncSetAttribute(topk_scan_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
+    topk_scan_rows_kernel<<<grid, TR_THREADS, smem, stream>>>(tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, stages, idesc,
+                                                            cand_scores, cand_idx);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+}  // namespace lsc
