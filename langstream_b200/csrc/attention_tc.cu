@@ -61,8 +61,9 @@ __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const int32_t* __restrict__ cu_seqlens, int H,
                     int heads, int n_items, __nv_bfloat16* __restrict__ ctx, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                               ~static_cast<uintptr_t>(1023));
+    // aligned by pointer arithmetic on the shared array (an integer round trip would turn every access
+    // through it into a generic-address one)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
     const uint32_t sP = smem_base + AT_NST * AT_STAGE_BYTES;  // two 32 KB P tiles, 1024-byte aligned
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AT_NST * AT_STAGE_BYTES + AT_G * AT_P_BYTES);

@@ -106,8 +106,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     using cfg = Cfg<BN>;
     constexpr int STAGES = cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                               ~static_cast<uintptr_t>(1023));
+    // aligned by pointer arithmetic on the shared array (an integer round trip would turn every access
+    // through it into a generic-address one)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
     uint8_t* staging = smem + STAGES * cfg::STAGE_BYTES;  // 1024-byte aligned
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + cfg::BAR_OFFSET);

@@ -58,8 +58,9 @@ topk_scan_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constan
                  int q_row0, int nq, int n_rows, int dim, int k, int stages,
                  float* __restrict__ cand_scores, int32_t* __restrict__ cand_idx) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                               ~static_cast<uintptr_t>(1023));
+    // aligned by pointer arithmetic on the shared array (an integer round trip would turn every access
+    // through it into a generic-address one)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const int num_kb = dim / TK_BK;
     const uint32_t sQ = smem_u32(smem);
     const uint32_t sC = sQ + num_kb * TK_QBLK_BYTES;
