@@ -126,6 +126,14 @@ int gemm_tc_block_n(int N);
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
                    const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,
                    int f16_from_col, const LnArgs& ln, int num_sms, cudaStream_t stream);
+// Fused feed-forward block (ffn_fused.cu): x_out = GELU(LN(tmp).W1^T + b1).W2^T + b2 + LN(tmp), the [T, F]
+// intermediate never leaves the SM.  tmapA: tmp, box 128 rows; tmapW1 / tmapW2: W1' [F, H] and W2 [H, F],
+// box 128 rows; tmapC: store map of x_out.  c1 / d1: the LN fold of W1 (see LnArgs).  Returns launches (1).
+bool ffn_fused_supported(int H, int F);
+int ffn_fused_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW1, const CUtensorMap& tmapW2,
+                     const CUtensorMap& tmapC, int M, int H, int F, const float* c1, const float* d1, const float* b2,
+                     const float* gamma, const float* beta, const float* stats_in, int p_in, float* stats_out,
+                     int p_out, const __nv_bfloat16* residual, float eps, int num_sms, cudaStream_t stream);
 // CUDA-core validation GEMM (debug).
 int gemm_ref_launch(const __nv_bfloat16* A, const __nv_bfloat16* W, const float* bias,
                     const __nv_bfloat16* residual, __nv_bfloat16* C, int M, int N, int K, int epilogue,

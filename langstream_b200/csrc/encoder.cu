@@ -39,6 +39,7 @@ struct LayerW {
     float* in_g = nullptr;
     float* in_b = nullptr;
     CUtensorMap tm_qkv, tm_o, tm_1, tm_2;
+    CUtensorMap tm_1f, tm_2f;  // 128-row boxes of W1' / W2 for the fused feed-forward kernel
 };
 
 }  // namespace
@@ -258,6 +259,12 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                 ln_o.stats_in = e->stats_x; ln_o.p_in = P; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
                 ln_o.inv_h = inv_h; ln_o.eps = c.ln_eps;
                 LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, tc_tmp, e->tmp, T, H, H, EPI_RES_LN, H, ln_o, st));
+                if (ffn_fused_supported(H, F)) {
+                    // x = GELU(LN1(tmp).W1^T + b1).W2^T + b2 + LN1(tmp) in one kernel; statistics of x -> stats_x
+                    LSC_LAUNCH(1, ffn_fused_launch(tm_tmp, w.tm_1f, w.tm_2f, tc_x, T, H, F, w.c_1, w.d_1, w.b_2, w.ln1_g,
+                                                   w.ln1_b, e->stats_1, P, e->stats_x, P, e->tmp, c.ln_eps, e->num_sms, st));
+                    continue;
+                }
                 LnArgs ln_1;  // consumer of tmp: LN1 folded, then GELU
                 ln_1.c = w.c_1; ln_1.stats_in = e->stats_1; ln_1.p_in = P; ln_1.inv_h = inv_h; ln_1.eps = c.ln_eps;
                 LSC_LAUNCH(1, gemm(e, tm_tmp, e->tmp, w.tm_1, w.w_1, w.d_1, nullptr, tc_ffn, e->ffn, T, F, H,
@@ -417,6 +424,10 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
                 LSC_TRY(make_tmap_bf16_sw128(&w.tm_o, w.w_o, H, H, bnh));
                 LSC_TRY(make_tmap_bf16_sw128(&w.tm_1, w.w_1, F, H, bnf));
                 LSC_TRY(make_tmap_bf16_sw128(&w.tm_2, w.w_2, H, F, bnh));
+                if (ffn_fused_supported(static_cast<int>(H), static_cast<int>(F))) {
+                    LSC_TRY(make_tmap_bf16_sw128(&w.tm_1f, w.w_1, F, H, 128));
+                    LSC_TRY(make_tmap_bf16_sw128(&w.tm_2f, w.w_2, H, F, 128));
+                }
             }
         }
         return LSC_OK;
