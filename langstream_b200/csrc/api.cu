@@ -124,7 +124,7 @@ int lsc_debug_gemm_dev(const void* d_A, const void* d_W, const float* d_bias, co
     LSC_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     CUtensorMap ta, tw, tc;
     LSC_TRY(make_tmap_bf16_sw128(&ta, A, M, K, 128));
-    LSC_TRY(make_tmap_bf16_sw128(&tw, W, N, K, bn));
+    LSC_TRY(make_tmap_bf16_sw128(&tw, W, N, K, gemm_tc_w_box_rows(N)));
     LSC_TRY(make_tmap_bf16_store32(&tc, C, M, N));
     int rc = gemm_tc_launch(ta, tw, tc, d_bias, R, M, N, K, epilogue, N, LnArgs(), sms, st);
     return rc < 0 ? rc : LSC_OK;

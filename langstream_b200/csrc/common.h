@@ -123,6 +123,7 @@ struct LnArgs {
 // tcgen05 GEMM: C[M,N] = epi(A[M,K]·W[N,K]^T + bias).  tmapA: box 128 rows; tmapW: box BN rows,
 // where BN = gemm_tc_block_n(N).  Returns number of kernel launches (1) or <0 on error.
 int gemm_tc_block_n(int N);
+int gemm_tc_w_box_rows(int N);  // rows of the weight map's TMA box (BN, or BN / 2 with CTA pairs)
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
                    const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,
                    int f16_from_col, const LnArgs& ln, int num_sms, cudaStream_t stream);
@@ -130,6 +131,7 @@ int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUt
 // intermediate never leaves the SM.  tmapA: tmp, box 128 rows; tmapW1 / tmapW2: W1' [F, H] and W2 [H, F],
 // box 128 rows; tmapC: store map of x_out.  c1 / d1: the LN fold of W1 (see LnArgs).  Returns launches (1).
 bool ffn_fused_supported(int H, int F);
+int ffn_fused_w_box_rows();  // rows of the W1' / W2 maps' TMA boxes (128, or 64 with CTA pairs)
 int ffn_fused_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW1, const CUtensorMap& tmapW2,
                      const CUtensorMap& tmapC, int M, int H, int F, const float* c1, const float* d1, const float* b2,
                      const float* gamma, const float* beta, const float* stats_in, int p_in, float* stats_out,

@@ -70,7 +70,8 @@ struct lsc_encoder {
     float* d_out = nullptr;
     float* stats_x = nullptr;   // [cap_tokens][stats_p][2] partial row statistics of x / tmp (LN folding)
     float* stats_1 = nullptr;
-    int stats_p = 0;
+    int stats_p = 0;    // partials per row of stats_1 (written by the attention-output GEMM: 2 * H / BN)
+    int stats_px = 0;   // partials per row of stats_x (4 when the fused feed-forward kernel writes it)
     std::atomic<int64_t> launches{0};
     Profiler prof;  // classes: 0 embed+LN, 1 GEMM, 2 attention, 3 LayerNorm, 4 pool
 };
@@ -176,7 +177,7 @@ int ensure_workspace(lsc_encoder* e, int64_t T) {
         *bufs[i] = static_cast<__nv_bfloat16*>(p);
     }
     if (e->stats_p > 0) {
-        const size_t n = static_cast<size_t>(cap) * e->stats_p * 2 * sizeof(float);
+        const size_t n = static_cast<size_t>(cap) * std::max(e->stats_p, e->stats_px) * 2 * sizeof(float);
         LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->stats_x), n));
         LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->stats_1), n));
     }
@@ -244,25 +245,25 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
             LSC_TRY(make_tmap_bf16_sw128(&tm_tmp, e->tmp, T, H, 128));
             LSC_TRY(make_tmap_bf16_sw128(&tm_ctx, e->ctx, T, H, 128));
             LSC_TRY(make_tmap_bf16_sw128(&tm_ffn, e->ffn, T, F, 128));
-            const int P = e->stats_p;
+            const int P = e->stats_p, PX = e->stats_px;
             const float inv_h = 1.0f / static_cast<float>(H);
             LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word, e->d_pos,
-                                          e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, e->stats_x, P, st));
+                                          e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, e->stats_x, PX, st));
             for (int l = 0; l < c.layers; ++l) {
                 const LayerW& w = e->layers[l];
                 LnArgs ln_in;  // consumer of x: LN_in folded
-                ln_in.c = w.c_qkv; ln_in.stats_in = e->stats_x; ln_in.p_in = P; ln_in.inv_h = inv_h; ln_in.eps = c.ln_eps;
+                ln_in.c = w.c_qkv; ln_in.stats_in = e->stats_x; ln_in.p_in = PX; ln_in.inv_h = inv_h; ln_in.eps = c.ln_eps;
                 LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.d_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H,
                                    EPI_LNIN_BIAS, 2 * H, ln_in, st));
                 LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st));
                 LnArgs ln_o;  // tmp = ctx.Wo^T + b + LN_in(x); statistics of tmp -> stats_1
-                ln_o.stats_in = e->stats_x; ln_o.p_in = P; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
+                ln_o.stats_in = e->stats_x; ln_o.p_in = PX; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
                 ln_o.inv_h = inv_h; ln_o.eps = c.ln_eps;
                 LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, tc_tmp, e->tmp, T, H, H, EPI_RES_LN, H, ln_o, st));
                 if (ffn_fused_supported(H, F)) {
                     // x = GELU(LN1(tmp).W1^T + b1).W2^T + b2 + LN1(tmp) in one kernel; statistics of x -> stats_x
                     LSC_LAUNCH(1, ffn_fused_launch(tm_tmp, w.tm_1f, w.tm_2f, tc_x, T, H, F, w.c_1, w.d_1, w.b_2, w.ln1_g,
-                                                   w.ln1_b, e->stats_1, P, e->stats_x, P, e->tmp, c.ln_eps, e->num_sms, st));
+                                                   w.ln1_b, e->stats_1, P, e->stats_x, PX, e->tmp, c.ln_eps, e->num_sms, st));
                     continue;
                 }
                 LnArgs ln_1;  // consumer of tmp: LN1 folded, then GELU
@@ -294,7 +295,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
     }
     if (c.gemm_impl == 0 && T > 0) {
         const LayerW& last = e->layers[c.layers - 1];
-        LSC_LAUNCH(4, pool_l2_launch(e->x, d_cu, n_seq, H, d_out, e->stats_x, e->stats_p, last.ln2_g, last.ln2_b, c.ln_eps, st));
+        LSC_LAUNCH(4, pool_l2_launch(e->x, d_cu, n_seq, H, d_out, e->stats_x, e->stats_px, last.ln2_g, last.ln2_b, c.ln_eps, st));
     } else {
         LSC_LAUNCH(4, pool_l2_launch(e->x, d_cu, n_seq, H, d_out, nullptr, 0, nullptr, nullptr, c.ln_eps, st));
     }
@@ -363,7 +364,10 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
         e->layers.resize(cfg->layers);
         const float* prev_ln2_g = nullptr;
         const float* prev_ln2_b = nullptr;
-        if (cfg->gemm_impl == 0) e->stats_p = 2 * static_cast<int>(H) / gemm_tc_block_n(static_cast<int>(H));
+        if (cfg->gemm_impl == 0) {
+            e->stats_p = 2 * static_cast<int>(H) / gemm_tc_block_n(static_cast<int>(H));
+            e->stats_px = ffn_fused_supported(static_cast<int>(H), static_cast<int>(F)) ? 4 : e->stats_p;
+        }
         for (int l = 0; l < cfg->layers; ++l) {
             LayerW& w = e->layers[l];
             const float* qw = p;            const float* qb = qw + H * H;
@@ -415,9 +419,9 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
             prev_ln2_g = l2g;
             prev_ln2_b = l2b;
             if (cfg->gemm_impl == 0) {
-                const int bn3 = gemm_tc_block_n(3 * static_cast<int>(H));
-                const int bnh = gemm_tc_block_n(static_cast<int>(H));
-                const int bnf = gemm_tc_block_n(static_cast<int>(F));
+                const int bn3 = gemm_tc_w_box_rows(3 * static_cast<int>(H));
+                const int bnh = gemm_tc_w_box_rows(static_cast<int>(H));
+                const int bnf = gemm_tc_w_box_rows(static_cast<int>(F));
                 if (bn3 == 0 || bnh == 0 || bnf == 0)
                     return fail(LSC_E_UNSUPPORTED, "encoder: hidden and ffn must be multiples of 128");
                 LSC_TRY(make_tmap_bf16_sw128(&w.tm_qkv, w.w_qkv, 3 * H, H, bn3));
@@ -425,8 +429,8 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
                 LSC_TRY(make_tmap_bf16_sw128(&w.tm_1, w.w_1, F, H, bnf));
                 LSC_TRY(make_tmap_bf16_sw128(&w.tm_2, w.w_2, H, F, bnh));
                 if (ffn_fused_supported(static_cast<int>(H), static_cast<int>(F))) {
-                    LSC_TRY(make_tmap_bf16_sw128(&w.tm_1f, w.w_1, F, H, 128));
-                    LSC_TRY(make_tmap_bf16_sw128(&w.tm_2f, w.w_2, H, F, 128));
+                    LSC_TRY(make_tmap_bf16_sw128(&w.tm_1f, w.w_1, F, H, ffn_fused_w_box_rows()));
+                    LSC_TRY(make_tmap_bf16_sw128(&w.tm_2f, w.w_2, H, F, ffn_fused_w_box_rows()));
                 }
             }
         }

@@ -19,6 +19,16 @@ __device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
     return d;
 }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t pk2u(uint32_t a, uint32_t b) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(a), "r"(b));
+    return r;
+}
 __device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
     uint64_t d;
     asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
@@ -57,6 +67,21 @@ __device__ __forceinline__ void gelu2(float& x0, float& x1) {
     const uint64_t th = pk2(tanh_approx(t0), tanh_approx(t1));
     const uint64_t hx = mul2(xx, pk2(0.5f, 0.5f));
     upk2(fma2(hx, th, hx), x0, x1);
+}
+
+// same, packed in / packed out
+__device__ __forceinline__ uint64_t gelu2_pk(uint64_t xx) {
+    float x0, x1;
+    upk2(xx, x0, x1);
+    gelu2(x0, x1);
+    return pk2(x0, x1);
+}
+__device__ __forceinline__ uint32_t pack_bf16x2_pk(uint64_t v) {
+    float a, b;
+    upk2(v, a, b);
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
 }
 
 __device__ __forceinline__ float gelu_erf(float x) {

@@ -16,9 +16,9 @@
 //   warp 0      TMA producer: the A tile once per tile; W1' / W2 boxes of 128 rows x 64 K through a ring
 //   warp 1      TMEM allocation + the single-thread MMA issuer; issue order G1(0), G1(1), G2(0), G1(2), G2(1) ...
 //               so the tensor pipe works on G2(j-1) / G1(j+1) while the epilogue warps convert chunk j
-//   warps 2-9   epilogue: TMEM -> registers -> GELU -> smem (per chunk) and the final residual/LN epilogue
+//   warps 2-17  epilogue: TMEM -> registers -> GELU -> smem (per chunk) and the final residual/LN epilogue
 // TMEM: OUT in columns [0, H), Hacc in [384, 512).  Shared memory: A 16 KB x H/64, h two buffers of 32 KB,
-// weight ring 4 x 16 KB.  Supported: H <= 384, H % 64 == 0, F % 128 == 0 (MiniLM: H = 384, F = 1536);
+// weight ring 48 KB, per-column parameters 16.5 KB.  Supported: H <= 384, H % 64 == 0, F % 128 == 0 (MiniLM: H = 384, F = 1536);
 // other shapes keep the two-GEMM path.
 #include <cstdlib>
 
@@ -33,17 +33,20 @@ namespace {
 constexpr int FF_BM = 128;
 constexpr int FF_BK = 64;
 constexpr int FF_CH = 128;   // FFN columns per chunk
-constexpr int FF_EPI_WARPS = 8;
+constexpr int FF_EPI_WARPS = 16;
 constexpr int FF_THREADS = 64 + FF_EPI_WARPS * 32;
-constexpr int FF_STAGES = 4;
-constexpr int FF_BOX_BYTES = 128 * FF_BK * 2;      // 16 KB: every TMA box is 128 rows x 64 bf16
+constexpr int FF_RING_BYTES = 48 * 1024;           // weight ring: 3 x 16 KB boxes, or 6 x 8 KB with CTA pairs
+constexpr int FF_MAX_H = 384;
+constexpr int FF_MAX_F = 1536;
+constexpr int FF_PARAM_BYTES = (2 * FF_MAX_F + 3 * FF_MAX_H) * 4;  // c1, d1, b2, gamma, beta staged in shared memory
+constexpr int FF_MAX_STAGES = 8;
+constexpr int FF_BOX_BYTES = 128 * FF_BK * 2;      // 16 KB: a TMA box of 128 rows x 64 bf16 (A slices, h slices)
 constexpr int FF_HBUF_BYTES = FF_BM * FF_CH * 2;   // 32 KB: one h chunk = two K slices of 16 KB
 constexpr int FF_HACC_COL = 384;                   // TMEM column of the chunk accumulator
-constexpr int FF_MAX_H = 384;
 
 // barrier slots (8 bytes each) after the ring's full/empty pairs
 enum {
-    FB_A_FULL = 2 * FF_STAGES,
+    FB_A_FULL = 2 * FF_MAX_STAGES,
     FB_A_EMPTY,
     FB_HACC_FULL,
     FB_HACC_EMPTY,
@@ -53,6 +56,8 @@ enum {
     FB_SH_EMPTY1,
     FB_OUT_FULL,
     FB_OUT_EMPTY,
+    FB_SH_LOCAL0,  // CTA pairs, peer CTA only: its epilogue warps' arrivals, relayed to the leader's FB_SH_FULL*
+    FB_SH_LOCAL1,
     FB_COUNT
 };
 
@@ -73,6 +78,12 @@ __device__ __forceinline__ void sts_u32x4(uint32_t addr, uint32_t a, uint32_t b,
     asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+// PAIR = 2: a cluster of two CTAs works on 256 rows with cta_group::2 MMAs (M = 256): each CTA keeps its own
+// 128-row A tile, h buffers, TMEM and epilogue, but stages only half of every weight box (64 of the 128
+// rows), which halves the weight traffic through shared memory - the bound of the single-CTA kernel, whose
+// N = 128 MMAs move 12 KB of shared memory per 64 tensor cycles.  The leader (rank 0) issues all MMAs;
+// completion is multicast to both CTAs' barriers, "consumed" arrivals go to the leader's barriers.
+template <int PAIR>
 __global__ void __launch_bounds__(FF_THREADS, 1)
 ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW1,
                  const __grid_constant__ CUtensorMap tmapW2, const __grid_constant__ CUtensorMap tmapC, int M, int H,
@@ -82,10 +93,24 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
     const uint32_t sA = smem_u32(smem);                                  // A tile: H/64 slices of 16 KB
     const uint32_t sH = sA + (FF_MAX_H / FF_BK) * FF_BOX_BYTES;          // two h buffers (also the store staging)
     const uint32_t sW = sH + 2 * FF_HBUF_BYTES;                          // weight ring
+    constexpr int WBOX_ROWS = 128 / PAIR;                                // weight rows staged per CTA and box
+    constexpr int WBOX_BYTES = WBOX_ROWS * FF_BK * 2;
+    constexpr int FF_STAGES = FF_RING_BYTES / WBOX_BYTES;
+    const uint32_t cta_rank = PAIR == 2 ? cluster_ctarank() : 0u;
+    // per-column parameters, read by every epilogue thread for every element: kept in shared memory (as
+    // global loads they miss the small L1 left beside 228 KB of shared memory and each costs an L2 round trip
+    // on the epilogue's critical path)
+    const uint32_t sP = sW + FF_RING_BYTES;
+    const uint32_t sC1 = sP, sD1 = sP + 4 * FF_MAX_F, sB2 = sP + 8 * FF_MAX_F, sG = sB2 + 4 * FF_MAX_H;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (FF_MAX_H / FF_BK) * FF_BOX_BYTES + 2 * FF_HBUF_BYTES +
-                                                 FF_STAGES * FF_BOX_BYTES);
+                                                 FF_RING_BYTES + FF_PARAM_BYTES);
     const uint32_t bar0 = smem_u32(bars);
     auto bar = [&](int slot) { return bar0 + 8u * static_cast<uint32_t>(slot); };
+    // the same barrier in the leader CTA (shared::cluster address); the leader's own for PAIR == 1
+    auto lead_bar = [&](int slot) { return PAIR == 2 ? mapa_u32(bar(slot), 0) : bar(slot); };
+    auto arrive_lead = [&](int slot) {
+        if (PAIR == 2) mbar_arrive_cluster(lead_bar(slot)); else mbar_arrive(bar(slot));
+    };
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(bars + FB_COUNT);
 
     const int warp = threadIdx.x >> 5;
@@ -97,31 +122,48 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
         tma_prefetch_desc(&tmapW2);
         tma_prefetch_desc(&tmapC);
         for (int s = 0; s < FF_STAGES; ++s) {
-            mbar_init(bar(s), 1);
-            mbar_init(bar(FF_STAGES + s), 1);
+            mbar_init(bar(s), PAIR);                 // full: one arrival per CTA's producer (on the leader)
+            mbar_init(bar(FF_MAX_STAGES + s), 1);    // empty
         }
-        mbar_init(bar(FB_A_FULL), 1);
+        mbar_init(bar(FB_A_FULL), PAIR);
         mbar_init(bar(FB_A_EMPTY), 1);
         mbar_init(bar(FB_HACC_FULL), 1);
-        mbar_init(bar(FB_HACC_EMPTY), FF_EPI_WARPS);
-        mbar_init(bar(FB_SH_FULL0), FF_EPI_WARPS);
-        mbar_init(bar(FB_SH_FULL1), FF_EPI_WARPS);
+        mbar_init(bar(FB_HACC_EMPTY), FF_EPI_WARPS * PAIR);
+        mbar_init(bar(FB_SH_FULL0), FF_EPI_WARPS + (PAIR - 1));  // leader's warps + the peer's relay
+        mbar_init(bar(FB_SH_FULL1), FF_EPI_WARPS + (PAIR - 1));
         mbar_init(bar(FB_SH_EMPTY0), 1);
         mbar_init(bar(FB_SH_EMPTY1), 1);
         mbar_init(bar(FB_OUT_FULL), 1);
-        mbar_init(bar(FB_OUT_EMPTY), FF_EPI_WARPS);
+        mbar_init(bar(FB_OUT_EMPTY), FF_EPI_WARPS * PAIR);
+        mbar_init(bar(FB_SH_LOCAL0), FF_EPI_WARPS);
+        mbar_init(bar(FB_SH_LOCAL1), FF_EPI_WARPS);
         fence_mbar_init();
     }
+    for (int i = threadIdx.x; i < F; i += FF_THREADS) {
+        sts_f32(sC1 + 4 * i, __ldg(a.c1 + i));
+        sts_f32(sD1 + 4 * i, __ldg(a.d1 + i));
+    }
+    for (int i = threadIdx.x; i < H; i += FF_THREADS) {
+        sts_f32(sB2 + 4 * i, __ldg(a.b2 + i) + __ldg(a.beta + i));  // b2 + beta: one constant per column
+        sts_f32(sG + 4 * i, __ldg(a.gamma + i));
+    }
     if (warp == 1) {
-        tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
-        tmem_relinquish();
+        if (PAIR == 2) {
+            tmem_alloc_pair(smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
+            tmem_relinquish_pair();
+        } else {
+            tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
+            tmem_relinquish();
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const int num_tiles = (M + FF_BM - 1) / FF_BM;
+    // a tile = 128 * PAIR rows, one per CTA (pair); this CTA's rows are its rank's half
+    const int num_tiles = (M + FF_BM * PAIR - 1) / (FF_BM * PAIR);
+    const int tile0 = blockIdx.x / PAIR, tile_step = gridDim.x / PAIR;
     const int num_kb = H / FF_BK;   // K slices of G1
     const int nb_out = H / 128;     // 128-column blocks of OUT
     const int FC = F / FF_CH;       // chunks
@@ -132,20 +174,37 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             int stage = 0;
             uint32_t phase = 0;
             uint32_t t = 0;
+            // one weight box: rows [c1, c1 + 128) of the map; a CTA of a pair stages its half of them
             auto push = [&](const CUtensorMap* m, int c0, int c1) {
-                mbar_wait(bar(FF_STAGES + stage), phase ^ 1);
-                mbar_arrive_expect_tx(bar(stage), FF_BOX_BYTES);
-                tma_load_2d(sW + stage * FF_BOX_BYTES, m, bar(stage), c0, c1);
+                mbar_wait(bar(FF_MAX_STAGES + stage), phase ^ 1);
+                if (PAIR == 2) {
+                    const uint32_t lf = lead_bar(stage);
+                    if (cta_rank == 0) mbar_arrive_expect_tx(bar(stage), WBOX_BYTES * 2); else mbar_arrive_cluster(lf);
+                    tma_load_2d_pair(sW + stage * WBOX_BYTES, m, lf, c0, c1 + static_cast<int>(cta_rank) * WBOX_ROWS);
+                } else {
+                    mbar_arrive_expect_tx(bar(stage), WBOX_BYTES);
+                    tma_load_2d(sW + stage * WBOX_BYTES, m, bar(stage), c0, c1);
+                }
                 if (++stage == FF_STAGES) {
                     stage = 0;
                     phase ^= 1;
                 }
             };
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+            for (int tile = tile0; tile < num_tiles; tile += tile_step, ++t) {
                 mbar_wait(bar(FB_A_EMPTY), (t & 1) ^ 1);
-                mbar_arrive_expect_tx(bar(FB_A_FULL), num_kb * FF_BOX_BYTES);
-                for (int kb = 0; kb < num_kb; ++kb)
-                    tma_load_2d(sA + kb * FF_BOX_BYTES, &tmapA, bar(FB_A_FULL), kb * FF_BK, tile * FF_BM);
+                const int arow = (tile * PAIR + static_cast<int>(cta_rank)) * FF_BM;
+                if (PAIR == 2) {
+                    const uint32_t lf = lead_bar(FB_A_FULL);
+                    if (cta_rank == 0)
+                        mbar_arrive_expect_tx(bar(FB_A_FULL), num_kb * FF_BOX_BYTES * 2);
+                    else
+                        mbar_arrive_cluster(lf);
+                    for (int kb = 0; kb < num_kb; ++kb) tma_load_2d_pair(sA + kb * FF_BOX_BYTES, &tmapA, lf, kb * FF_BK, arow);
+                } else {
+                    mbar_arrive_expect_tx(bar(FB_A_FULL), num_kb * FF_BOX_BYTES);
+                    for (int kb = 0; kb < num_kb; ++kb)
+                        tma_load_2d(sA + kb * FF_BOX_BYTES, &tmapA, bar(FB_A_FULL), kb * FF_BK, arow);
+                }
                 for (int j = 0; j <= FC; ++j) {  // same order as the MMA issuer: G1(j), then G2(j-1)
                     if (j < FC)
                         for (int kb = 0; kb < num_kb; ++kb) push(&tmapW1, kb * FF_BK, j * FF_CH);
@@ -156,9 +215,15 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (elect_one()) {
-            constexpr uint32_t idesc = umma_idesc_bf16(FF_BM, 128);
+        // ===== MMA issuer (the pair's leader only) =====
+        if (cta_rank == 0 && elect_one()) {
+            constexpr uint32_t idesc = umma_idesc_bf16(FF_BM * PAIR, 128);
+            auto mma = [&](uint32_t d, uint64_t da, uint64_t db, uint32_t accumulate) {
+                if (PAIR == 2) umma_bf16_pair(d, da, db, idesc, accumulate); else umma_bf16(d, da, db, idesc, accumulate);
+            };
+            auto commit = [&](int slot) {
+                if (PAIR == 2) umma_commit_pair(bar(slot)); else umma_commit(bar(slot));
+            };
             int stage = 0;
             uint32_t phase = 0;
             uint32_t t = 0, g = 0;  // tiles / chunks done by this CTA (barrier parities)
@@ -172,20 +237,20 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                     for (int nb = 0; nb < nb_out; ++nb) {
                         mbar_wait(bar(stage), phase);
                         tc_fence_after();
-                        const uint64_t db = umma_desc_sw128(sW + stage * FF_BOX_BYTES);
+                        const uint64_t db = umma_desc_sw128(sW + stage * WBOX_BYTES);
 #pragma unroll
                         for (int k = 0; k < FF_BK / 16; ++k)
-                            umma_bf16(tmem_base + nb * 128, da + 2 * k, db + 2 * k, idesc, (jj | ks | k) != 0 ? 1u : 0u);
-                        umma_commit(bar(FF_STAGES + stage));
+                            mma(tmem_base + nb * 128, da + 2 * k, db + 2 * k, (jj | ks | k) != 0 ? 1u : 0u);
+                        commit(FF_MAX_STAGES + stage);
                         if (++stage == FF_STAGES) {
                             stage = 0;
                             phase ^= 1;
                         }
                     }
                 }
-                umma_commit(bar(FB_SH_EMPTY0 + b));  // the h buffer may be rewritten when these MMAs retire
+                commit(FB_SH_EMPTY0 + b);  // the h buffer may be rewritten when these MMAs retire
             };
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
+            for (int tile = tile0; tile < num_tiles; tile += tile_step, ++t) {
                 mbar_wait(bar(FB_A_FULL), t & 1);
                 tc_fence_after();
                 for (int j = 0; j < FC; ++j, ++g) {
@@ -195,43 +260,61 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                         mbar_wait(bar(stage), phase);
                         tc_fence_after();
                         const uint64_t da = umma_desc_sw128(sA + kb * FF_BOX_BYTES);
-                        const uint64_t db = umma_desc_sw128(sW + stage * FF_BOX_BYTES);
+                        const uint64_t db = umma_desc_sw128(sW + stage * WBOX_BYTES);
 #pragma unroll
                         for (int k = 0; k < FF_BK / 16; ++k)
-                            umma_bf16(tmem_base + FF_HACC_COL, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-                        umma_commit(bar(FF_STAGES + stage));
+                            mma(tmem_base + FF_HACC_COL, da + 2 * k, db + 2 * k, (kb | k) != 0 ? 1u : 0u);
+                        commit(FF_MAX_STAGES + stage);
                         if (++stage == FF_STAGES) {
                             stage = 0;
                             phase ^= 1;
                         }
                     }
-                    umma_commit(bar(FB_HACC_FULL));
-                    if (j == FC - 1) umma_commit(bar(FB_A_EMPTY));  // last read of the A tile
+                    commit(FB_HACC_FULL);
+                    if (j == FC - 1) commit(FB_A_EMPTY);  // last read of the A tile
                     if (j >= 1) g2(j - 1, g - 1);
                 }
                 g2(FC - 1, g - 1);
-                umma_commit(bar(FB_OUT_FULL));
+                commit(FB_OUT_FULL);
+            }
+        } else if (PAIR == 2 && cta_rank == 1 && elect_one()) {
+            // ===== peer CTA: relay "h chunk written" to the leader =====
+            // The peer's epilogue warps arrive on a local barrier; one releasing cluster-scope arrive per chunk
+            // (a MEMBAR.ALL.GPU, kept off the epilogue warps) publishes their shared-memory writes to the
+            // leader's MMA thread.
+            uint32_t g = 0;
+            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+                for (int j = 0; j < FC; ++j, ++g) {
+                    const uint32_t b = g & 1, u = g >> 1;
+                    mbar_wait(bar(FB_SH_LOCAL0 + b), u & 1);
+                    fence_proxy_async_smem();
+                    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(
+                                     lead_bar(FB_SH_FULL0 + b))
+                                 : "memory");
+                }
             }
         }
     } else {
         // ===== epilogue warps =====
-        // Warp e owns TMEM lane quadrant (warp & 3) = 32 tile rows; thread = row.  Of a 128-column chunk it
-        // converts columns [64 * half, 64 * half + 64) = K slice `half` of the h buffer; of OUT it owns the
-        // column half [H/2 * half, +H/2) in blocks of 32 columns (TMA stores through 32x32 staging blocks,
-        // as in gemm_tcgen05.cu; the staging lives in h buffer 0, which is idle during the final epilogue).
+        // Sixteen warps (four per scheduler: the epilogue is a chain of dependent TMEM / global loads, fp32
+        // math and MUFU, and with two warps per scheduler it ran at an IPC of 0.13 per warp and bounded the
+        // kernel).  Warp e owns TMEM lane quadrant (warp & 3) = 32 tile rows, thread = row, and column
+        // quarter cq = e / 4: 32 of a chunk's 128 columns (half of K slice cq / 2 of the h buffer), and
+        // H / 4 columns of OUT in blocks of 32 (TMA stores through 32x32 staging blocks, as in
+        // gemm_tcgen05.cu; the staging occupies the h buffers, which are idle during the final epilogue).
         const int ew = warp - 2;
         const int quad = warp & 3;
-        const int half = ew >> 2;
+        const int cq = ew >> 2;
         const int r = quad * 32 + lane;  // row inside the tile
         const uint32_t swz = static_cast<uint32_t>(r & 7);
         const uint32_t stg_addr = sH + ew * 4096;
         const uint32_t sw64 = (static_cast<uint32_t>(lane) >> 1) & 3;  // SWIZZLE_64B of the store staging
         const uint32_t tlane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        const int nch_out = H / 2 / 32;
+        const int nch_out = H / 4 / 32;
         uint32_t t = 0, g = 0;
         int buf = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++t) {
-            const int row0 = tile * FF_BM + quad * 32;
+        for (int tile = tile0; tile < num_tiles; tile += tile_step, ++t) {
+            const int row0 = (tile * PAIR + static_cast<int>(cta_rank)) * FF_BM + quad * 32;
             const int grow = row0 + lane;
             const bool row_ok = grow < M;
             // LayerNorm statistics of this thread's row of tmp (LN1 feeds both the FFN and the residual)
@@ -251,99 +334,89 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                 rstd = row_ok ? rsqrtf(var + a.eps) : 1.f;
                 nm = -mean * rstd;
             }
-            uint32_t va[32], vb[32];
+            uint32_t v[32];
             // ---- chunks: Hacc -> GELU -> h buffer ----
             for (int j = 0; j < FC; ++j, ++g) {
                 const uint32_t b = g & 1, u = g >> 1;
+                const int col0 = j * FF_CH + cq * 32;
+                const uint32_t cp = sC1 + 4 * col0, dp = sD1 + 4 * col0;
                 mbar_wait(bar(FB_HACC_FULL), g & 1);
                 tc_fence_after();
-                const uint32_t tcol = tlane + FF_HACC_COL + half * 64;
-                tmem_ld_32x32(tcol, va);
-                tmem_ld_32x32(tcol + 32, vb);
+                tmem_ld_32x32(tlane + FF_HACC_COL + cq * 32, v);
                 mbar_wait(bar(FB_SH_EMPTY0 + b), (u & 1) ^ 1);  // G2 of two chunks ago has read this buffer
-                const uint32_t hrow = sH + b * FF_HBUF_BYTES + half * FF_BOX_BYTES + static_cast<uint32_t>(r) * 128;
-                const int col0 = j * FF_CH + half * 64;
+                const uint32_t hrow =
+                    sH + b * FF_HBUF_BYTES + (cq >> 1) * FF_BOX_BYTES + static_cast<uint32_t>(r) * 128;
                 tmem_ld_wait();
-                // both loads have landed: the accumulator can be overwritten by G1 of the next chunk
+                // the load has landed: this warp's part of the accumulator may be overwritten by the next G1
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar(FB_HACC_EMPTY));
+                if (lane == 0) arrive_lead(FB_HACC_EMPTY);
+                const uint64_t rstd2 = pk2(rstd, rstd), nm2 = pk2(nm, nm);
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
-                    uint32_t(&v)[32] = c ? vb : va;
-                    const float4* cp = reinterpret_cast<const float4*>(a.c1 + col0 + c * 32);
-                    const float4* dp = reinterpret_cast<const float4*>(a.d1 + col0 + c * 32);
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float4 c0 = __ldg(cp + 2 * i), c1 = __ldg(cp + 2 * i + 1);
-                        const float4 d0 = __ldg(dp + 2 * i), d1 = __ldg(dp + 2 * i + 1);
-                        const float cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-                        const float dd[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-                        float x[8];
-#pragma unroll
-                        for (int e = 0; e < 8; ++e)
-                            x[e] = fmaf(rstd, __uint_as_float(v[8 * i + e]), fmaf(nm, cc[e], dd[e]));
-#pragma unroll
-                        for (int e = 0; e < 8; e += 2) gelu2(x[e], x[e + 1]);
-                        // K-major SWIZZLE_128B: 16-byte chunk index XOR (row & 7)
-                        const uint32_t chunk = static_cast<uint32_t>(c * 4 + i) ^ swz;
-                        sts_u32x4(hrow + chunk * 16, pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]),
-                                  pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
-                    }
+                for (int i = 0; i < 4; ++i) {
+                    const float4 c0 = lds_f32x4(cp + 32 * i), c1 = lds_f32x4(cp + 32 * i + 16);
+                    const float4 d0 = lds_f32x4(dp + 32 * i), d1 = lds_f32x4(dp + 32 * i + 16);
+                    // h = gelu(rstd * acc + (nm * c1 + d1)), two elements per instruction
+                    const uint64_t h0 = gelu2_pk(fma2(rstd2, pk2u(v[8 * i + 0], v[8 * i + 1]), fma2(nm2, pk2(c0.x, c0.y), pk2(d0.x, d0.y))));
+                    const uint64_t h1 = gelu2_pk(fma2(rstd2, pk2u(v[8 * i + 2], v[8 * i + 3]), fma2(nm2, pk2(c0.z, c0.w), pk2(d0.z, d0.w))));
+                    const uint64_t h2 = gelu2_pk(fma2(rstd2, pk2u(v[8 * i + 4], v[8 * i + 5]), fma2(nm2, pk2(c1.x, c1.y), pk2(d1.x, d1.y))));
+                    const uint64_t h3 = gelu2_pk(fma2(rstd2, pk2u(v[8 * i + 6], v[8 * i + 7]), fma2(nm2, pk2(c1.z, c1.w), pk2(d1.z, d1.w))));
+                    // K-major SWIZZLE_128B: 16-byte chunk index XOR (row & 7)
+                    const uint32_t chunk = static_cast<uint32_t>((cq & 1) * 4 + i) ^ swz;
+                    sts_u32x4(hrow + chunk * 16, pack_bf16x2_pk(h0), pack_bf16x2_pk(h1), pack_bf16x2_pk(h2), pack_bf16x2_pk(h3));
                 }
                 fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core's smem reads
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar(FB_SH_FULL0 + b));
+                if (lane == 0) mbar_arrive(bar((PAIR == 2 && cta_rank == 1 ? FB_SH_LOCAL0 : FB_SH_FULL0) + b));
             }
             // ---- final: OUT + b2 + LN1(tmp) -> x, with row statistics ----
-            const int col_base = half * (H / 2);
+            const int col_base = cq * (H / 4);
             const __nv_bfloat16* rrow = a.residual + static_cast<size_t>(row_ok ? grow : 0) * H + col_base;
-            float osum = 0.f, osq = 0.f;
+            uint64_t osum2 = pk2(0.f, 0.f), osq2 = pk2(0.f, 0.f);
+            uint32_t res[16], res_next[16];
+            ldg256(rrow, res_next);  // residual of block 0, in flight while the last chunks finish
+            ldg256(rrow + 16, res_next + 8);
             mbar_wait(bar(FB_OUT_FULL), t & 1);
             tc_fence_after();
             const uint32_t tout = tlane + col_base;
-            tmem_ld_32x32(tout, va);
             for (int c = 0; c < nch_out; ++c) {
-                uint32_t res[16];
-                ldg256(rrow + c * 32, res);
-                ldg256(rrow + c * 32 + 16, res + 8);
-                tmem_ld_wait();
-                // ping-pong without run-time register indexing: copy, then prefetch the next block
-                uint32_t v[32];
+                tmem_ld_32x32(tout + c * 32, v);
 #pragma unroll
-                for (int i = 0; i < 32; ++i) v[i] = va[i];
-                if (c + 1 < nch_out) {
-                    tmem_ld_32x32(tout + (c + 1) * 32, va);
-                } else {
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(bar(FB_OUT_EMPTY));  // OUT may be overwritten by the next tile
+                for (int i = 0; i < 16; ++i) res[i] = res_next[i];
+                if (c + 1 < nch_out) {  // next block's residual while this one is processed
+                    ldg256(rrow + (c + 1) * 32, res_next);
+                    ldg256(rrow + (c + 1) * 32 + 16, res_next + 8);
                 }
                 const int col = col_base + c * 32;
-                const float4* bp = reinterpret_cast<const float4*>(a.b2 + col);
-                const float4* gp = reinterpret_cast<const float4*>(a.gamma + col);
-                const float4* ep = reinterpret_cast<const float4*>(a.beta + col);
+                const uint32_t bp = sB2 + 4 * col, gp = sG + 4 * col;
                 if (lane == 0) tma_store_wait_read<1>();  // the block filled two rounds ago has been read
+                tmem_ld_wait();
+                if (c + 1 == nch_out) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) arrive_lead(FB_OUT_EMPTY);  // OUT may be overwritten by the next tile
+                }
                 __syncwarp();
                 const uint32_t blk = stg_addr + buf * 2048 + lane * 64;
+                const uint64_t rstd2 = pk2(rstd, rstd), nm2 = pk2(nm, nm);
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const float4 b0 = __ldg(bp + 2 * i), b1 = __ldg(bp + 2 * i + 1);
-                    const float4 g0 = __ldg(gp + 2 * i), g1 = __ldg(gp + 2 * i + 1);
-                    const float4 e0 = __ldg(ep + 2 * i), e1 = __ldg(ep + 2 * i + 1);
-                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-                    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-                    const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
-                    float x[8];
+                    const float4 b0 = lds_f32x4(bp + 32 * i), b1 = lds_f32x4(bp + 32 * i + 16);
+                    const float4 g0 = lds_f32x4(gp + 32 * i), g1 = lds_f32x4(gp + 32 * i + 16);
+                    const uint64_t bb[4] = {pk2(b0.x, b0.y), pk2(b0.z, b0.w), pk2(b1.x, b1.y), pk2(b1.z, b1.w)};
+                    const uint64_t gg[4] = {pk2(g0.x, g0.y), pk2(g0.z, g0.w), pk2(g1.x, g1.y), pk2(g1.z, g1.w)};
+                    uint32_t o[4];
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const float raw = (e & 1) ? bf16_hi(res[4 * i + (e >> 1)]) : bf16_lo(res[4 * i + (e >> 1)]);
-                        x[e] = __uint_as_float(v[8 * i + e]) + bb[e] + fmaf(raw, rstd * gg[e], fmaf(nm, gg[e], ee[e]));
-                        osum += x[e];
-                        osq = fmaf(x[e], x[e], osq);
+                    for (int e = 0; e < 4; ++e) {
+                        // x = acc + (b2 + beta) + gamma * (raw * rstd - mean * rstd), two columns at a time
+                        const uint32_t w = res[4 * i + e];
+                        const uint64_t raw = pk2u(w << 16, w & 0xffff0000u);
+                        const uint64_t x = fma2(gg[e], fma2(raw, rstd2, nm2), add2(pk2u(v[8 * i + 2 * e], v[8 * i + 2 * e + 1]), bb[e]));
+                        osum2 = add2(osum2, x);
+                        osq2 = fma2(x, x, osq2);
+                        o[e] = pack_bf16x2_pk(x);
                     }
-                    sts_u32x4(blk + ((static_cast<uint32_t>(i) ^ sw64) * 16), pack_bf16x2(x[0], x[1]),
-                              pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
+                    sts_u32x4(blk + ((static_cast<uint32_t>(i) ^ sw64) * 16), o[0], o[1], o[2], o[3]);
                 }
                 fence_proxy_async_smem();
                 __syncwarp();
@@ -353,13 +426,14 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
                 }
                 buf ^= 1;
             }
-            if (row_ok) {
-                float2* so = reinterpret_cast<float2*>(a.stats_out) + static_cast<size_t>(grow) * a.p_out;
-                so[half] = make_float2(osum, osq);
-                for (int p = half + 2; p < a.p_out; p += 2) so[p] = make_float2(0.f, 0.f);
+            if (row_ok) {  // one partial per column quarter (p_out == 4)
+                float s0, s1, q0, q1;
+                upk2(osum2, s0, s1);
+                upk2(osq2, q0, q1);
+                reinterpret_cast<float2*>(a.stats_out)[static_cast<size_t>(grow) * a.p_out + cq] = make_float2(s0 + s1, q0 + q1);
             }
-            // the staging blocks sit in h buffer 0: every warp's stores must have been read before any warp
-            // writes the next tile's first chunk there
+            // the staging blocks sit in the h buffers: every warp's stores must have been read before any warp
+            // writes the next tile's chunks there
             if (lane == 0) tma_store_wait_read<0>();
             asm volatile("bar.sync 1, %0;" ::"n"(FF_EPI_WARPS * 32) : "memory");
         }
@@ -367,10 +441,10 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (PAIR == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 512);
+        if (PAIR == 2) tmem_dealloc_pair(tmem_base, 512); else tmem_dealloc(tmem_base, 512);
     }
 }
 
@@ -378,7 +452,53 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
 
 bool ffn_fused_supported(int H, int F) {
     static const bool off = getenv("LSC_FFN_UNFUSED") != nullptr;  // debug: keep the two-GEMM path
-    return !off && H > 0 && H <= FF_MAX_H && H % 128 == 0 && F > 0 && F % FF_CH == 0;
+    return !off && H > 0 && H <= FF_MAX_H && H % 128 == 0 && F > 0 && F <= FF_MAX_F && F % FF_CH == 0;
+}
+
+// LSC_FFN_PAIR=0 (debug) runs the fused kernel on single CTAs.
+static bool ffn_pair_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("LSC_FFN_PAIR");
+        return e == nullptr || atoi(e) != 0;
+    }();
+    return on;
+}
+
+// Rows of the TMA boxes of the W1' / W2 maps: 128, or 64 with CTA pairs (each CTA stages half a box).
+int ffn_fused_w_box_rows() { return ffn_pair_enabled() ? 64 : 128; }
+
+template <int PAIR>
+static int ffn_launch_impl(const CUtensorMap& tmapA, const CUtensorMap& tmapW1, const CUtensorMap& tmapW2,
+                           const CUtensorMap& tmapC, int M, int H, int F, const FfnArgs& a, int num_sms,
+                           cudaStream_t stream) {
+    constexpr int SMEM = (FF_MAX_H / FF_BK) * FF_BOX_BYTES + 2 * FF_HBUF_BYTES + FF_RING_BYTES + FF_PARAM_BYTES + 256 + 1024;
+    static_assert(SMEM <= 227 * 1024, "fused FFN: shared memory budget");
+    static bool configured[64] = {};
+    auto kern = ffn_fused_kernel<PAIR>;
+    int dev = 0;
+    LSC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+        LSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
+    const int tiles = (M + FF_BM * PAIR - 1) / (FF_BM * PAIR);
+    int grid = tiles * PAIR < num_sms ? tiles * PAIR : num_sms;
+    grid -= grid % PAIR;
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(grid);
+    lc.blockDim = dim3(FF_THREADS);
+    lc.dynamicSmemBytes = SMEM;
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = PAIR;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    LSC_CUDA(cudaLaunchKernelEx(&lc, kern, tmapA, tmapW1, tmapW2, tmapC, M, H, F, a));
+    LSC_CUDA(cudaGetLastError());
+    return 1;
 }
 
 int ffn_fused_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW1, const CUtensorMap& tmapW2,
@@ -387,25 +507,15 @@ int ffn_fused_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW1, const 
                      int p_out, const __nv_bfloat16* residual, float eps, int num_sms, cudaStream_t stream) {
     if (M <= 0) return 0;
     if (!ffn_fused_supported(H, F)) return fail(LSC_E_UNSUPPORTED, "fused FFN: unsupported hidden / ffn size");
-    if (!c1 || !d1 || !b2 || !gamma || !beta || !stats_in || !stats_out || !residual || p_in < 1 || p_out < 2)
+    if (!c1 || !d1 || !b2 || !gamma || !beta || !stats_in || !stats_out || !residual || p_in < 1 || p_out != 4)
         return fail(LSC_E_INVALID, "fused FFN: missing argument");
-    constexpr int SMEM = (FF_MAX_H / FF_BK) * FF_BOX_BYTES + 2 * FF_HBUF_BYTES + FF_STAGES * FF_BOX_BYTES + 256 + 1024;
-    static bool configured[64] = {};
-    int dev = 0;
-    LSC_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !configured[dev]) {
-        LSC_CUDA(cudaFuncSetAttribute(ffn_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-        if (dev >= 0 && dev < 64) configured[dev] = true;
-    }
     FfnArgs a;
     a.c1 = c1; a.d1 = d1; a.b2 = b2; a.gamma = gamma; a.beta = beta;
     a.stats_in = stats_in; a.stats_out = stats_out; a.residual = residual;
     a.p_in = p_in; a.p_out = p_out; a.inv_h = 1.0f / static_cast<float>(H); a.eps = eps;
-    const int tiles = (M + FF_BM - 1) / FF_BM;
-    const int grid = tiles < num_sms ? tiles : num_sms;
-    ffn_fused_kernel<<<grid, FF_THREADS, SMEM, stream>>>(tmapA, tmapW1, tmapW2, tmapC, M, H, F, a);
-    LSC_CUDA(cudaGetLastError());
-    return 1;
+    if (ffn_pair_enabled() && num_sms >= 2)
+        return ffn_launch_impl<2>(tmapA, tmapW1, tmapW2, tmapC, M, H, F, a, num_sms, stream);
+    return ffn_launch_impl<1>(tmapA, tmapW1, tmapW2, tmapC, M, H, F, a, num_sms, stream);
 }
 
 }  // namespace lsc

@@ -13,6 +13,7 @@
 // Three mbarrier pipelines: smem full/empty (TMA <-> MMA) and TMEM full/empty (MMA <-> epilogue).
 #include <cuda_fp16.h>
 
+#include <cstdio>
 #include <cstdlib>
 
 #include "common.h"
@@ -31,23 +32,26 @@ constexpr int TMEM_COLS = 512;
 constexpr int ACC_STRIDE = 256;  // TMEM columns between the two accumulator stages
 constexpr int STAGING_BYTES = EPI_WARPS * 2 * 2048;  // per warp: two 32x32 bf16 blocks (TMA store sources)
 
-template <int BN>
+// PAIR = 2: CTA pairs (cta_group::2).  A tile of the pair = 256 rows x BN; each CTA stages its own 128 rows
+// of A and BN / 2 rows of W, so a stage is smaller and the ring deeper.
+template <int BN, int PAIR = 1>
 struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
-    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int B_BYTES = (BN / PAIR) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = (BN <= 128) ? 6 : 4;
+    static constexpr int STAGES = PAIR == 2 ? (BN <= 192 ? 6 : 5) : ((BN <= 128) ? 6 : 4);
     static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + STAGING_BYTES;
     static constexpr int SMEM_BYTES = BAR_OFFSET + 256 + 1024;  // + barriers + alignment slack
 };
 
-template <int BN, int EPI>
+template <int BN, int EPI, int PAIR>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
                const __grid_constant__ CUtensorMap tmapC, const float* __restrict__ bias,
                const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int f16_from_col, const LnArgs ln) {
-    using cfg = Cfg<BN>;
+    using cfg = Cfg<BN, PAIR>;
     constexpr int STAGES = cfg::STAGES;
+    const uint32_t cta_rank = PAIR == 2 ? cluster_ctarank() : 0u;
     extern __shared__ uint8_t smem_raw[];
     // aligned by pointer arithmetic on the shared array (an integer round trip would turn every access
     // through it into a generic-address one)
@@ -69,43 +73,61 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         tma_prefetch_desc(&tmapW);
         tma_prefetch_desc(&tmapC);
         for (int s = 0; s < STAGES; ++s) {
-            mbar_init(bar_full + 8 * s, 1);
+            mbar_init(bar_full + 8 * s, PAIR);  // the leader's barrier: one arrival per CTA of the pair
             mbar_init(bar_empty + 8 * s, 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
-            mbar_init(bar_tempty + 8 * a, EPI_WARPS);  // one arrive per epilogue warp
+            mbar_init(bar_tempty + 8 * a, EPI_WARPS * PAIR);  // one arrive per epilogue warp (of both CTAs)
         }
         fence_mbar_init();
     }
     if (warp == 1) {
-        tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
-        tmem_relinquish();
+        if (PAIR == 2) {
+            tmem_alloc_pair(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
+            tmem_relinquish_pair();
+        } else {
+            tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
+            tmem_relinquish();
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const int m_tiles = (M + BM - 1) / BM;
+    // tiles are BM * PAIR rows x BN columns, one per CTA (pair); this CTA's rows are its rank's half
+    const int m_tiles = (M + BM * PAIR - 1) / (BM * PAIR);
     const int n_tiles = N / BN;
     const int num_tiles = m_tiles * n_tiles;
     const int num_kb = K / BK;
+    const int tile0 = blockIdx.x / PAIR, tile_step = gridDim.x / PAIR;
 
     if (warp == 0) {
         // ===== TMA producer =====
         if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
                 const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                     const uint32_t sA = smem_base + stage * cfg::STAGE_BYTES;
                     const uint32_t sB = sA + cfg::A_BYTES;
-                    mbar_arrive_expect_tx(bar_full + 8 * stage, cfg::STAGE_BYTES);
-                    tma_load_2d(sA, &tmapA, bar_full + 8 * stage, kb * BK, m_blk * BM);
-                    tma_load_2d(sB, &tmapW, bar_full + 8 * stage, kb * BK, n_blk * BN);
+                    if (PAIR == 2) {
+                        // both CTAs' bytes are counted on the leader's barrier
+                        const uint32_t lead_full = mapa_u32(bar_full + 8 * stage, 0);
+                        if (cta_rank == 0)
+                            mbar_arrive_expect_tx(bar_full + 8 * stage, cfg::STAGE_BYTES * 2);
+                        else
+                            mbar_arrive_cluster(lead_full);
+                        tma_load_2d_pair(sA, &tmapA, lead_full, kb * BK, (m_blk * 2 + cta_rank) * BM);
+                        tma_load_2d_pair(sB, &tmapW, lead_full, kb * BK, n_blk * BN + cta_rank * (BN / 2));
+                    } else {
+                        mbar_arrive_expect_tx(bar_full + 8 * stage, cfg::STAGE_BYTES);
+                        tma_load_2d(sA, &tmapA, bar_full + 8 * stage, kb * BK, m_blk * BM);
+                        tma_load_2d(sB, &tmapW, bar_full + 8 * stage, kb * BK, n_blk * BN);
+                    }
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -114,14 +136,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (elect_one()) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+        // ===== MMA issuer (the pair's leader only) =====
+        if (cta_rank == 0 && elect_one()) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BM * PAIR, BN);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
                 mbar_wait(bar_tempty + 8 * acc, acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * ACC_STRIDE;
@@ -134,15 +156,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {
                         // +32 bytes per K=16 step inside the 128-byte swizzled row (encoded >>4)
-                        umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                        if (PAIR == 2)
+                            umma_bf16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                        else
+                            umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
-                    umma_commit(bar_empty + 8 * stage);  // frees the smem slot when the MMAs retire
+                    // frees the smem slot (in both CTAs) when the MMAs retire
+                    if (PAIR == 2) umma_commit_pair(bar_empty + 8 * stage); else umma_commit(bar_empty + 8 * stage);
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                umma_commit(bar_tfull + 8 * acc);  // accumulator ready for the epilogue
+                // accumulator ready for the epilogue (of both CTAs)
+                if (PAIR == 2) umma_commit_pair(bar_tfull + 8 * acc); else umma_commit(bar_tfull + 8 * acc);
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
             }
@@ -167,9 +194,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         int buf = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        // TMEM "empty" arrivals go to the leader's barrier (the leader issues the MMAs)
+        const uint32_t lead_tempty = PAIR == 2 ? mapa_u32(bar_tempty, 0) : bar_tempty;
+        auto release_acc = [&](int which) {
+            if (PAIR == 2) mbar_arrive_cluster(lead_tempty + 8 * which); else mbar_arrive(bar_tempty + 8 * which);
+        };
+        for (int tile = tile0; tile < num_tiles; tile += tile_step) {
             const int m_blk = tile / n_tiles, n_blk = tile % n_tiles;
-            const int row0 = m_blk * BM + quad * 32;
+            const int row0 = (m_blk * PAIR + static_cast<int>(cta_rank)) * BM + quad * 32;
             const int grow = row0 + lane;
             const bool row_ok = grow < M;
             const int col_base = n_blk * BN + half * (BN / 2);
@@ -204,7 +236,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             if (EPI == EPI_DISCARD) {  // debug: measure the TMA + MMA main loop alone
                 __syncwarp();
                 tc_fence_before();
-                if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+                if (lane == 0) release_acc(acc);
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
                 continue;
@@ -224,7 +256,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 if (keep == 0x12345678u && bias != nullptr) *const_cast<float*>(bias) = 0.f;  // never true in practice
                 __syncwarp();
                 tc_fence_before();
-                if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+                if (lane == 0) release_acc(acc);
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
                 continue;
@@ -323,7 +355,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             // every TMEM read of this tile by this warp has completed (tmem_ld_wait above)
             __syncwarp();
             tc_fence_before();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+            if (lane == 0) release_acc(acc);
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
@@ -331,20 +363,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (PAIR == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
+        if (PAIR == 2) tmem_dealloc_pair(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
-template <int BN, int EPI>
-int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
+template <int BN, int EPI, int PAIR>
+int launch_pair(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
                 const __nv_bfloat16* residual, int M, int N, int K, int f16_from_col, const LnArgs& ln, int num_sms,
                 cudaStream_t stream) {
-    using cfg = Cfg<BN>;
+    using cfg = Cfg<BN, PAIR>;
     static bool configured[64] = {};  // per instantiation and per device
-    auto kern = gemm_tc_kernel<BN, EPI>;
+    auto kern = gemm_tc_kernel<BN, EPI, PAIR>;
     int dev = 0;
     LSC_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !configured[dev]) {
@@ -352,12 +384,51 @@ int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtens
                                       cfg::SMEM_BYTES));
         if (dev >= 0 && dev < 64) configured[dev] = true;
     }
-    const int m_tiles = (M + BM - 1) / BM;
+    const int m_tiles = (M + BM * PAIR - 1) / (BM * PAIR);
     const int num_tiles = m_tiles * (N / BN);
-    const int grid = num_tiles < num_sms ? num_tiles : num_sms;
-    kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln);
+    int grid = num_tiles * PAIR < num_sms ? num_tiles * PAIR : num_sms;
+    grid -= grid % PAIR;
+    if (PAIR == 1) {
+        kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln);
+    } else {
+        // CTA pairs: clusters of two CTAs, scheduled on the two SMs of a TPC
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3(grid);
+        lc.blockDim = dim3(GEMM_THREADS);
+        lc.dynamicSmemBytes = cfg::SMEM_BYTES;
+        lc.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = PAIR;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        lc.attrs = attr;
+        lc.numAttrs = 1;
+        LSC_CUDA(cudaLaunchKernelEx(&lc, kern, tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln));
+    }
     LSC_CUDA(cudaGetLastError());
     return 1;
+}
+
+// CTA pairs pay off when the tile row is long (QKV, FFN): +6 % on the main loop and a deeper ring; the
+// narrow N = H GEMM (two tiles per row, epilogue-bound) is faster on single CTAs.  LSC_GEMM_PAIR=0 (debug)
+// keeps every GEMM on single CTAs.
+bool gemm_use_pair(int N, int bn) {
+    static const bool on = [] {
+        const char* e = getenv("LSC_GEMM_PAIR");
+        return e == nullptr || atoi(e) != 0;
+    }();
+    return on && bn != 128 && bn > 0 && N / bn >= 4;
+}
+
+template <int BN, int EPI>
+int launch_inst(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC, const float* bias,
+                const __nv_bfloat16* residual, int M, int N, int K, int f16_from_col, const LnArgs& ln, int num_sms,
+                cudaStream_t stream) {
+    // the pair kernel wants W boxes of BN / 2 rows: see gemm_tc_w_box_rows()
+    if (BN != 128 && gemm_use_pair(N, BN) && num_sms >= 2)
+        return launch_pair<BN, EPI, 2>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
+    return launch_pair<BN, EPI, 1>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln, num_sms, stream);
 }
 
 template <int BN>
@@ -404,6 +475,14 @@ int gemm_tc_block_n(int N) {
     if (N % 256 == 0) return 256;
     if (N % 128 == 0) return 128;
     return 0;
+}
+
+// Rows of the TMA box the weight map of an N-column GEMM must have: BN on single CTAs, BN / 2 for CTA pairs
+// (each CTA of a pair stages half of the tile's weight rows).
+int gemm_tc_w_box_rows(int N) {
+    const int bn = gemm_tc_block_n(N);
+    if (bn == 0) return 0;
+    return gemm_use_pair(N, bn) ? bn / 2 : bn;
 }
 
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
