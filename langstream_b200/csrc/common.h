@@ -123,6 +123,7 @@ struct LnArgs {
 // tcgen05 GEMM: C[M,N] = epi(A[M,K]·W[N,K]^T + bias).  tmapA: box 128 rows; tmapW: box BN rows,
 // where BN = gemm_tc_block_n(N).  Returns number of kernel launches (1) or <0 on error.
 int gemm_tc_block_n(int N);
+int gemm_tc_stats_parts(int N);  // per-row statistic partials written by an EPI_RES_LN GEMM of N columns
 int gemm_tc_w_box_rows(int N);  // rows of the weight map's TMA box (BN, or BN / 2 with CTA pairs)
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
                    const float* bias, const __nv_bfloat16* residual, int M, int N, int K, int epilogue,

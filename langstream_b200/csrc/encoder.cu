@@ -70,7 +70,7 @@ struct lsc_encoder {
     float* d_out = nullptr;
     float* stats_x = nullptr;   // [cap_tokens][stats_p][2] partial row statistics of x / tmp (LN folding)
     float* stats_1 = nullptr;
-    int stats_p = 0;    // partials per row of stats_1 (written by the attention-output GEMM: 2 * H / BN)
+    int stats_p = 0;    // partials per row of stats_1 (written by the attention-output GEMM)
     int stats_px = 0;   // partials per row of stats_x (4 when the fused feed-forward kernel writes it)
     std::atomic<int64_t> launches{0};
     Profiler prof;  // classes: 0 embed+LN, 1 GEMM, 2 attention, 3 LayerNorm, 4 pool
@@ -365,7 +365,7 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
         const float* prev_ln2_g = nullptr;
         const float* prev_ln2_b = nullptr;
         if (cfg->gemm_impl == 0) {
-            e->stats_p = 2 * static_cast<int>(H) / gemm_tc_block_n(static_cast<int>(H));
+            e->stats_p = gemm_tc_stats_parts(static_cast<int>(H));
             e->stats_px = ffn_fused_supported(static_cast<int>(H), static_cast<int>(F)) ? 4 : e->stats_p;
         }
         for (int l = 0; l < cfg->layers; ++l) {

@@ -26,11 +26,22 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int EPI_WARPS = 8;
-constexpr int GEMM_THREADS = 64 + EPI_WARPS * 32;  // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 constexpr int TMEM_COLS = 512;
 constexpr int ACC_STRIDE = 256;  // TMEM columns between the two accumulator stages
-constexpr int STAGING_BYTES = EPI_WARPS * 2 * 2048;  // per warp: two 32x32 bf16 blocks (TMA store sources)
+
+// Epilogue warps: BN = 192 (every encoder shape) uses twelve - three per TMEM lane quadrant and scheduler, each
+// owning 64 of the tile's columns; the epilogue, not the main loop, bounds these kernels and is a chain of
+// dependent loads and fp32 math, so warps are what hides its latency.  Other widths keep eight (BN / 2 columns).
+template <int BN>
+struct Epi {
+    static constexpr int WARPS = BN == 192 ? 12 : 8;
+    static constexpr int PARTS = WARPS / 4;              // column parts of a tile (one warp per quadrant and part)
+    static constexpr int COLS = BN / PARTS;              // columns per warp
+    static constexpr int NCH = COLS / 32;                // 32-column chunks per warp
+    static constexpr int THREADS = 64 + WARPS * 32;      // warp 0 TMA, warp 1 MMA, the rest epilogue
+    static constexpr int STAGING_BYTES = WARPS * 2 * 2048;   // per warp: two 32x32 bf16 blocks (TMA store sources)
+    static constexpr int PARAM_BYTES = WARPS * COLS * 3 * 4;  // per warp: up to three fp32 vectors of its columns
+};
 
 // PAIR = 2: CTA pairs (cta_group::2).  A tile of the pair = 256 rows x BN; each CTA stages its own 128 rows
 // of A and BN / 2 rows of W, so a stage is smaller and the ring deeper.
@@ -39,13 +50,27 @@ struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = (BN / PAIR) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = PAIR == 2 ? (BN <= 192 ? 6 : 5) : ((BN <= 128) ? 6 : 4);
-    static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + STAGING_BYTES;
-    static constexpr int SMEM_BYTES = BAR_OFFSET + 256 + 1024;  // + barriers + alignment slack
+    static constexpr int FIXED_BYTES = Epi<BN>::STAGING_BYTES + Epi<BN>::PARAM_BYTES + 256 + 1024;  // + barriers + alignment
+    static constexpr int FIT = (227 * 1024 - FIXED_BYTES) / STAGE_BYTES;
+    static constexpr int STAGES = FIT > 6 ? 6 : FIT;
+    static constexpr int STAGING_OFFSET = STAGES * STAGE_BYTES;
+    static constexpr int PARAM_OFFSET = STAGING_OFFSET + Epi<BN>::STAGING_BYTES;
+    static constexpr int BAR_OFFSET = PARAM_OFFSET + Epi<BN>::PARAM_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED_BYTES;
+    static_assert(STAGES >= 3, "gemm: shared memory budget");
 };
 
+__device__ __forceinline__ void sts_u32x4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_f16x2_pk(uint64_t v) {
+    float a, b;
+    upk2(v, a, b);
+    return pack_f16x2(a, b);
+}
+
 template <int BN, int EPI, int PAIR>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(Epi<BN>::THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
                const __grid_constant__ CUtensorMap tmapC, const float* __restrict__ bias,
                const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int f16_from_col, const LnArgs ln) {
@@ -57,7 +82,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     // through it into a generic-address one)
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
-    uint8_t* staging = smem + STAGES * cfg::STAGE_BYTES;  // 1024-byte aligned
+    constexpr int EPI_WARPS = Epi<BN>::WARPS;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + cfg::BAR_OFFSET);
     const uint32_t bar_full = smem_u32(bars);
     const uint32_t bar_empty = bar_full + 8 * STAGES;
@@ -176,20 +201,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         }
     } else {
         // ===== epilogue warps =====
-        // Warp e owns TMEM lane quadrant (warp & 3) = 32 tile rows and one half of the tile's columns,
-        // in chunks of 32 columns; thread = row.  Per chunk: tcgen05.ld -> bias (+GELU | +residual) in
-        // fp32 -> bf16 -> a 32x32 block in shared memory (SWIZZLE_64B, conflict-free 16-byte stores) ->
-        // one TMA store issued by lane 0.  The stores bypass the LSU, clip the M tail in hardware and
-        // cost 2 KB of smem write + 2 KB of smem read per chunk (the MMA main loop itself runs at the
-        // shared-memory bandwidth limit, so the epilogue's smem traffic is kept to that minimum).
-        // The TMEM load of chunk c+1 is in flight while chunk c is processed; two staging blocks per
+        // Warp e owns TMEM lane quadrant (warp & 3) = 32 tile rows and column part e / 4 of the tile, in
+        // chunks of 32 columns; thread = row.  Per chunk: tcgen05.ld -> epilogue math in packed fp32x2 ->
+        // bf16 -> a 32x32 block in shared memory (SWIZZLE_64B, conflict-free 16-byte stores) -> one TMA
+        // store issued by lane 0.  The stores bypass the LSU, clip the M tail in hardware and cost 2 KB of
+        // smem write + 2 KB of smem read per chunk.  Everything with a long latency is issued ahead of its
+        // use: the per-column vectors (bias, LN-fold c, gamma, beta) go to the warp's own shared-memory
+        // cache at the top of the tile, before the accumulator is waited for; the TMEM load and the
+        // residual rows of chunk c + 1 are in flight while chunk c is processed; two staging blocks per
         // warp let a TMA store drain while the next block is filled.
-        constexpr int NCH = BN / 2 / 32;
+        constexpr int NCH = Epi<BN>::NCH;
+        constexpr int COLS = Epi<BN>::COLS;
+        constexpr bool kRes = EPI == EPI_BIAS_RESIDUAL || EPI == EPI_RES_LN;
+        constexpr bool kLnIn = EPI == EPI_LNIN_BIAS || EPI == EPI_LNIN_GELU;
+        constexpr bool kGelu = EPI == EPI_BIAS_GELU || EPI == EPI_LNIN_GELU;
         const int ew = warp - 2;
         const int quad = warp & 3;
-        const int half = ew >> 2;
-        uint8_t* stg = staging + ew * 4096;
-        const uint32_t stg_addr = smem_u32(stg);
+        const int part = ew >> 2;
+        const uint32_t stg_addr = smem_base + cfg::STAGING_OFFSET + ew * 4096;
+        const uint32_t prm = smem_base + cfg::PARAM_OFFSET + ew * (COLS * 3 * 4);  // [3][COLS] fp32
         const uint32_t sw = (static_cast<uint32_t>(lane) >> 1) & 3;  // SWIZZLE_64B: chunk ^= (row >> 1) & 3
         int buf = 0;
         int acc = 0;
@@ -204,13 +234,36 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             const int row0 = (m_blk * PAIR + static_cast<int>(cta_rank)) * BM + quad * 32;
             const int grow = row0 + lane;
             const bool row_ok = grow < M;
-            const int col_base = n_blk * BN + half * (BN / 2);
-            const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC_STRIDE +
-                                   half * (BN / 2);
-            constexpr bool kRes = EPI == EPI_BIAS_RESIDUAL || EPI == EPI_RES_LN;
-            constexpr bool kLnIn = EPI == EPI_LNIN_BIAS || EPI == EPI_LNIN_GELU;
-            constexpr bool kGelu = EPI == EPI_BIAS_GELU || EPI == EPI_LNIN_GELU;
+            const int col_base = n_blk * BN + part * COLS;
+            const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC_STRIDE + part * COLS;
+            if (EPI == EPI_DISCARD) {  // debug: measure the TMA + MMA main loop alone
+                mbar_wait(bar_tfull + 8 * acc, acc_phase);
+                tc_fence_after();
+                __syncwarp();
+                tc_fence_before();
+                if (lane == 0) release_acc(acc);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+                continue;
+            }
+            // per-column vectors of this warp's columns -> its shared-memory cache (the previous tile's reads
+            // of the cache are over: every lane is past its last chunk)
+            __syncwarp();
+#pragma unroll
+            for (int k = lane; k < COLS; k += 32) {
+                sts_f32(prm + 4 * k, __ldg(bias + col_base + k));
+                if (kLnIn) sts_f32(prm + 4 * (COLS + k), __ldg(ln.c + col_base + k));
+                if (EPI == EPI_RES_LN) {
+                    sts_f32(prm + 4 * (COLS + k), __ldg(ln.gamma + col_base + k));
+                    sts_f32(prm + 4 * (2 * COLS + k), __ldg(ln.beta + col_base + k));
+                }
+            }
             const __nv_bfloat16* rrow = kRes ? residual + static_cast<size_t>(row_ok ? grow : 0) * N + col_base : nullptr;
+            uint32_t res[16], res_next[16];
+            if (kRes) {  // residual of chunk 0
+                ldg256(rrow, res_next);
+                ldg256(rrow + 16, res_next + 8);
+            }
             // LayerNorm folding: row statistics of the tensor being normalised (the A operand for
             // kLnIn, the residual for EPI_RES_LN) from its per-row partial (sum, sum of squares).
             float rstd = 1.f, nm = 0.f;  // nm = -mean * rstd
@@ -229,18 +282,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 rstd = row_ok ? rsqrtf(var + ln.eps) : 1.f;
                 nm = -mean * rstd;
             }
-            float osum = 0.f, osq = 0.f;  // EPI_RES_LN: statistics of the rows this thread writes
+            const uint64_t rstd2 = pk2(rstd, rstd), nm2 = pk2(nm, nm);
+            uint64_t osum2 = pk2(0.f, 0.f), osq2 = pk2(0.f, 0.f);  // EPI_RES_LN: statistics of the rows written
+            __syncwarp();  // the parameter cache is complete
             mbar_wait(bar_tfull + 8 * acc, acc_phase);
             tc_fence_after();
             uint32_t va[32], vb[32];
-            if (EPI == EPI_DISCARD) {  // debug: measure the TMA + MMA main loop alone
-                __syncwarp();
-                tc_fence_before();
-                if (lane == 0) release_acc(acc);
-                acc ^= 1;
-                if (acc == 0) acc_phase ^= 1;
-                continue;
-            }
             tmem_ld_32x32(tbase, va);
             if (EPI == EPI_LOADONLY) {  // debug: main loop + TMEM reads, nothing else
                 uint32_t keep = 0;
@@ -265,77 +312,71 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             for (int c = 0; c < NCH; ++c) {
                 uint32_t(&v)[32] = (c & 1) ? vb : va;
                 uint32_t(&vnext)[32] = (c & 1) ? va : vb;
-                uint32_t res[16];
                 if (kRes) {
-                    ldg256(rrow + c * 32, res);
-                    ldg256(rrow + c * 32 + 16, res + 8);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) res[i] = res_next[i];
+                    if (c + 1 < NCH) {
+                        ldg256(rrow + (c + 1) * 32, res_next);
+                        ldg256(rrow + (c + 1) * 32 + 16, res_next + 8);
+                    }
                 }
                 tmem_ld_wait();
-                if (c + 1 < NCH) tmem_ld_32x32(tbase + (c + 1) * 32, vnext);
+                if (c + 1 < NCH) {
+                    tmem_ld_32x32(tbase + (c + 1) * 32, vnext);
+                } else {
+                    // every TMEM read of this tile by this warp has been issued and has completed
+                    __syncwarp();
+                    tc_fence_before();
+                    if (lane == 0) release_acc(acc);
+                }
                 const int col = col_base + c * 32;
-                const float4* bp = reinterpret_cast<const float4*>(bias + col);
-                const float4* cp = reinterpret_cast<const float4*>((kLnIn ? ln.c : bias) + col);
-                const float4* gp = reinterpret_cast<const float4*>((EPI == EPI_RES_LN ? ln.gamma : bias) + col);
-                const float4* ep = reinterpret_cast<const float4*>((EPI == EPI_RES_LN ? ln.beta : bias) + col);
+                const uint32_t p0 = prm + 4 * (c * 32), p1 = p0 + 4 * COLS, p2 = p1 + 4 * COLS;
                 // the block we are about to fill was the source of the TMA store issued two chunks ago
                 if (lane == 0) tma_store_wait_read<1>();
                 __syncwarp();
-                uint8_t* blk = stg + buf * 2048 + lane * 64;
+                const uint32_t blk = stg_addr + buf * 2048 + lane * 64;
                 const bool as_f16 = col >= f16_from_col;  // V third of the QKV output
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {  // 4 x 16 bytes = 8 columns each
-                    const float4 b0 = __ldg(bp + 2 * i), b1 = __ldg(bp + 2 * i + 1);
-                    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-                    float x[8];
-                    if (kLnIn) {
-                        // LN(a) . W^T + b  ==  rstd * (a . W'^T) - rstd * mean * c + d,  W' = W diag(gamma)
-                        const float4 c0 = __ldg(cp + 2 * i), c1 = __ldg(cp + 2 * i + 1);
-                        const float cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-#pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            x[j] = fmaf(rstd, __uint_as_float(v[8 * i + j]), fmaf(nm, cc[j], bb[j]));
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) x[j] = __uint_as_float(v[8 * i + j]) + bb[j];
-                    }
-                    if (kGelu) {
-#pragma unroll
-                        for (int j = 0; j < 8; j += 2) gelu2(x[j], x[j + 1]);
-                    }
-                    if (EPI == EPI_BIAS_RESIDUAL) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            x[2 * j] += bf16_lo(res[4 * i + j]);
-                            x[2 * j + 1] += bf16_hi(res[4 * i + j]);
-                        }
+                    const float4 b0 = lds_f32x4(p0 + 32 * i), b1 = lds_f32x4(p0 + 32 * i + 16);
+                    const uint64_t bb[4] = {pk2(b0.x, b0.y), pk2(b0.z, b0.w), pk2(b1.x, b1.y), pk2(b1.z, b1.w)};
+                    uint64_t q1[4], q2[4];  // second / third vector (LN-fold c | gamma, beta)
+                    if (kLnIn || EPI == EPI_RES_LN) {
+                        const float4 c0 = lds_f32x4(p1 + 32 * i), c1 = lds_f32x4(p1 + 32 * i + 16);
+                        q1[0] = pk2(c0.x, c0.y); q1[1] = pk2(c0.z, c0.w); q1[2] = pk2(c1.x, c1.y); q1[3] = pk2(c1.z, c1.w);
                     }
                     if (EPI == EPI_RES_LN) {
-                        // residual = LayerNorm(raw) computed on the fly: raw * (rstd*gamma) + (beta - mean*rstd*gamma)
-                        const float4 g0 = __ldg(gp + 2 * i), g1 = __ldg(gp + 2 * i + 1);
-                        const float4 e0 = __ldg(ep + 2 * i), e1 = __ldg(ep + 2 * i + 1);
-                        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-                        const float ee[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+                        const float4 e0 = lds_f32x4(p2 + 32 * i), e1 = lds_f32x4(p2 + 32 * i + 16);
+                        q2[0] = pk2(e0.x, e0.y); q2[1] = pk2(e0.z, e0.w); q2[2] = pk2(e1.x, e1.y); q2[3] = pk2(e1.z, e1.w);
+                    }
+                    uint32_t o[4];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float raw = (j & 1) ? bf16_hi(res[4 * i + (j >> 1)]) : bf16_lo(res[4 * i + (j >> 1)]);
-                            x[j] += fmaf(raw, rstd * gg[j], fmaf(nm, gg[j], ee[j]));
-                            osum += x[j];
-                            osq = fmaf(x[j], x[j], osq);
+                    for (int e = 0; e < 4; ++e) {  // two columns per instruction
+                        const uint64_t a2 = pk2u(v[8 * i + 2 * e], v[8 * i + 2 * e + 1]);
+                        uint64_t x;
+                        if (kLnIn) {
+                            // LN(a) . W^T + b  ==  rstd * (a . W'^T) - rstd * mean * c + d,  W' = W diag(gamma)
+                            x = fma2(rstd2, a2, fma2(nm2, q1[e], bb[e]));
+                        } else {
+                            x = add2(a2, bb[e]);
                         }
+                        if (kGelu) x = gelu2_pk(x);
+                        if (kRes) {
+                            const uint32_t w = res[4 * i + e];
+                            const uint64_t raw = pk2u(w << 16, w & 0xffff0000u);
+                            if (EPI == EPI_RES_LN) {
+                                // + LayerNorm(raw) = gamma * (raw * rstd - mean * rstd) + beta, and the statistics
+                                // of what is written (the next LayerNorm is folded into its consumer)
+                                x = fma2(q1[e], fma2(raw, rstd2, nm2), add2(x, q2[e]));
+                                osum2 = add2(osum2, x);
+                                osq2 = fma2(x, x, osq2);
+                            } else {
+                                x = add2(x, raw);
+                            }
+                        }
+                        o[e] = as_f16 ? pack_f16x2_pk(x) : pack_bf16x2_pk(x);
                     }
-                    uint4 o;
-                    if (as_f16) {
-                        o.x = pack_f16x2(x[0], x[1]);
-                        o.y = pack_f16x2(x[2], x[3]);
-                        o.z = pack_f16x2(x[4], x[5]);
-                        o.w = pack_f16x2(x[6], x[7]);
-                    } else {
-                        o.x = pack_bf16x2(x[0], x[1]);
-                        o.y = pack_bf16x2(x[2], x[3]);
-                        o.z = pack_bf16x2(x[4], x[5]);
-                        o.w = pack_bf16x2(x[6], x[7]);
-                    }
-                    *reinterpret_cast<uint4*>(blk + ((static_cast<uint32_t>(i) ^ sw) * 16)) = o;
+                    sts_u32x4(blk + ((static_cast<uint32_t>(i) ^ sw) * 16), o[0], o[1], o[2], o[3]);
                 }
                 fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA engine
                 __syncwarp();
@@ -346,16 +387,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 buf ^= 1;
             }
             if (EPI == EPI_RES_LN && row_ok) {
-                // partial (sum, sum of squares) of this row over this warp's columns; the consumer adds
-                // the 2*N/BN partials of a row
+                // partial (sum, sum of squares) of this row over this warp's columns; the consumer adds the
+                // PARTS * N / BN partials of a row
+                float s0, s1, t0, t1;
+                upk2(osum2, s0, s1);
+                upk2(osq2, t0, t1);
                 float2* so = reinterpret_cast<float2*>(ln.stats_out) +
-                             static_cast<size_t>(grow) * (2 * n_tiles) + (n_blk * 2 + half);
-                *so = make_float2(osum, osq);
+                             static_cast<size_t>(grow) * (Epi<BN>::PARTS * n_tiles) + (n_blk * Epi<BN>::PARTS + part);
+                *so = make_float2(s0 + s1, t0 + t1);
             }
-            // every TMEM read of this tile by this warp has completed (tmem_ld_wait above)
-            __syncwarp();
-            tc_fence_before();
-            if (lane == 0) release_acc(acc);
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
@@ -389,12 +429,12 @@ int launch_pair(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtens
     int grid = num_tiles * PAIR < num_sms ? num_tiles * PAIR : num_sms;
     grid -= grid % PAIR;
     if (PAIR == 1) {
-        kern<<<grid, GEMM_THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln);
+        kern<<<grid, Epi<BN>::THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln);
     } else {
         // CTA pairs: clusters of two CTAs, scheduled on the two SMs of a TPC
         cudaLaunchConfig_t lc = {};
         lc.gridDim = dim3(grid);
-        lc.blockDim = dim3(GEMM_THREADS);
+        lc.blockDim = dim3(Epi<BN>::THREADS);
         lc.dynamicSmemBytes = cfg::SMEM_BYTES;
         lc.stream = stream;
         cudaLaunchAttribute attr[1];
@@ -483,6 +523,16 @@ int gemm_tc_w_box_rows(int N) {
     const int bn = gemm_tc_block_n(N);
     if (bn == 0) return 0;
     return gemm_use_pair(N, bn) ? bn / 2 : bn;
+}
+
+// Number of per-row statistic partials an EPI_RES_LN GEMM with N output columns writes.
+int gemm_tc_stats_parts(int N) {
+    switch (gemm_tc_block_n(N)) {
+        case 192: return Epi<192>::PARTS * (N / 192);
+        case 256: return Epi<256>::PARTS * (N / 256);
+        case 128: return Epi<128>::PARTS * (N / 128);
+        default: return 0;
+    }
 }
 
 int gemm_tc_launch(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtensorMap& tmapC,
