@@ -263,27 +263,44 @@ def run_cuda(args):
     prof = enc.read_profile()
     enc.set_profiling(False)
 
-    # roofline of the dominant kernel (the tcgen05 GEMM): algorithmic dense FLOPs / event-timed GEMM time
+    # roofline of the dominant kernel: the fused feed-forward kernel (two of the four GEMMs of a layer, half of
+    # the step) when the model shape supports it, else the tcgen05 GEMM class.  Algorithmic dense FLOPs of the
+    # launches of that class / their event-timed duration.
     total_flop, dense_flop = flops_per_sequence(spec, SEQ_LEN)
+    H, F, L = spec.hidden, spec.ffn, spec.layers
+    tokens = N_SEQ * SEQ_LEN
+    ffn_flop_step = 4.0 * tokens * H * F * L            # FFN-up + FFN-down
+    gemm_flop_step = dense_flop * N_SEQ                 # all four GEMM shapes
     gemm_ms, gemm_launches = prof["gemm"]
-    gemm_flops_per_launch = dense_flop * N_SEQ * args.steps / max(gemm_launches, 1)
-    gemm_tflops = dense_flop * N_SEQ * args.steps / (gemm_ms / 1000.0) / 1e12 if gemm_ms > 0 else 0.0
+    ffn_ms, ffn_launches = prof["ffn_fused"]
     peak_tf = pk["bf16_tflops_sustained"]
+    if ffn_launches > 0:
+        dom_name = "ffn_fused_kernel (tcgen05 cta_group::2: FFN-up + GELU + FFN-down + residual, LayerNorm folded in)"
+        dom_ms, dom_launches, dom_flop = ffn_ms, ffn_launches, ffn_flop_step * args.steps
+        traffic_key = "ffn_fused_kernel"
+        other_flop = (gemm_flop_step - ffn_flop_step) * args.steps
+    else:
+        dom_name = "gemm_tc_kernel (tcgen05/TMEM/TMA, all 4 encoder GEMM shapes, LayerNorm folded in)"
+        dom_ms, dom_launches, dom_flop = gemm_ms, gemm_launches, gemm_flop_step * args.steps
+        traffic_key = "gemm_tc_kernel"
+        other_flop = 0.0
+    dom_tflops = dom_flop / (dom_ms / 1000.0) / 1e12 if dom_ms > 0 else 0.0
     traffic = None
     tpath = ROOT / "profiles" / "r01_traffic.json"
     if tpath.exists():
         try:
-            traffic = json.loads(tpath.read_text())["gemm_tc_kernel"]["dram_bytes_per_launch_avg"]
+            traffic = json.loads(tpath.read_text())[traffic_key]["dram_bytes_per_launch_avg"]
         except Exception:
             traffic = None
     roofline = {
-        "bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05/TMEM/TMA, all 4 encoder GEMM shapes, LayerNorm folded in)",
-        "achieved": gemm_tflops, "peak": peak_tf, "unit": "TFLOP/s",
-        "frac": gemm_tflops / peak_tf if peak_tf else None, "traffic": traffic,
-        "traffic_source": "ncu --set full capture, profiles/r01_ncu_full_encoder.csv (dram read+write, average of the 4 shapes)",
+        "bound": "tensor", "kernel": dom_name,
+        "achieved": dom_tflops, "peak": peak_tf, "unit": "TFLOP/s",
+        "frac": dom_tflops / peak_tf if peak_tf else None, "traffic": traffic,
+        "traffic_source": "ncu --set full capture under profiles/ (dram read+write per launch)",
         "peak_source": pk_src + ", sustained bf16 (kernel timed inside a long step)",
-        "flops_per_launch": gemm_flops_per_launch,
-        "avg_launch_ms": gemm_ms / max(gemm_launches, 1),
+        "flops_per_launch": dom_flop / max(dom_launches, 1),
+        "avg_launch_ms": dom_ms / max(dom_launches, 1),
+        "other_gemm_tflops": (other_flop / (gemm_ms / 1000.0) / 1e12) if (other_flop > 0 and gemm_ms > 0) else None,
         "kernel_share_of_step": {k: v[0] / max(sum(x[0] for x in prof.values()), 1e-9) for k, v in prof.items()},
         "ms_per_step_with_event_profiling": ms_profiled / args.steps,
         "whole_step_tflops": total_flop * N_SEQ * args.steps / (ms_total / 1000.0) / 1e12,

@@ -125,7 +125,7 @@ int lsc_encoder_embed_dev(lsc_encoder* enc, const int32_t* d_token_ids, const in
  * Measurement aid (no reference counterpart): when enabled, every kernel launch of this handle is
  * bracketed by CUDA events on its stream.  lsc_encoder_read_profile waits for them and returns the
  * milliseconds and launch counts accumulated since the previous read, per kernel class:
- * 0 embedding gather+LayerNorm, 1 GEMM, 2 attention, 3 LayerNorm, 4 mean-pool+L2.
+ * 0 embedding gather+LayerNorm, 1 GEMM, 2 attention, 3 LayerNorm, 4 mean-pool+L2, 5 fused feed-forward block.
  */
 int lsc_encoder_set_profiling(lsc_encoder* enc, int enabled);
 int lsc_encoder_read_profile(lsc_encoder* enc, float* ms_by_class, int64_t* launches_by_class,

@@ -166,7 +166,7 @@ class Encoder:
     def launch_count(self) -> int:
         return int(lib().lsc_encoder_launch_count(self._h))
 
-    PROFILE_CLASSES = ("embed_ln", "gemm", "attention", "layernorm", "pool_l2")
+    PROFILE_CLASSES = ("embed_ln", "gemm", "attention", "layernorm", "pool_l2", "ffn_fused")
 
     def set_profiling(self, enabled: bool):
         check(lib().lsc_encoder_set_profiling(self._h, int(enabled)))

@@ -262,7 +262,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                 LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, tc_tmp, e->tmp, T, H, H, EPI_RES_LN, H, ln_o, st));
                 if (ffn_fused_supported(H, F)) {
                     // x = GELU(LN1(tmp).W1^T + b1).W2^T + b2 + LN1(tmp) in one kernel; statistics of x -> stats_x
-                    LSC_LAUNCH(1, ffn_fused_launch(tm_tmp, w.tm_1f, w.tm_2f, tc_x, T, H, F, w.c_1, w.d_1, w.b_2, w.ln1_g,
+                    LSC_LAUNCH(5, ffn_fused_launch(tm_tmp, w.tm_1f, w.tm_2f, tc_x, T, H, F, w.c_1, w.d_1, w.b_2, w.ln1_g,
                                                    w.ln1_b, e->stats_1, P, e->stats_x, PX, e->tmp, c.ln_eps, e->num_sms, st));
                     continue;
                 }
