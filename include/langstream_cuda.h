@@ -252,6 +252,35 @@ int lsc_index_load(const char* path, int device, lsc_index** out);
  *  API/database/VectorDatabaseWriter.java:38). */
 void lsc_index_destroy(lsc_index* idx);
 
+/* ---- re-rank (the step after query-vector-db in the reference's chatbot pipeline) --------- */
+
+/*
+ * Replaces: ReRankAgent.rerankMMR and what it calls (langstream-agents/langstream-ai-agents/src/main/java/
+ * ai/langstream/ai/agents/rerank/ReRankAgent.java:155-252 MMR loop + diversity, :254-273 and :361-372
+ * cosine / norm / dot product, :275-343 BM25 and IDF), algorithm "MMR".
+ * Picks up to max_docs of n_docs documents: each round takes the document with the highest
+ * lambda * BM25(query, doc | documents still in the pool) - (1 - lambda) * mean cosine(doc, picked),
+ * first maximum wins.  The host does the text side (ReRankAgent.tokenise = split on \s+, :314-316) and
+ * passes, per document, its length in tokens (doc_len[n_docs]) and the frequency of each QUERY token
+ * (term_freq[n_docs][n_terms], one column per query token in query order, duplicates included);
+ * doc_vecs[n_docs][dim] are the document embeddings (fp32).  Arithmetic follows the reference's types and
+ * evaluation order (fp32 sequential sums for cosine, fp64 for BM25 / diversity / score), so the order is
+ * the reference's, not an approximation of it.  out_order[0 .. *out_count) receives indices into the input
+ * list.  Limits: n_docs <= 128 (the reference's default `max` is 100), n_terms <= 64.
+ * Documents must have non-empty text and embeddings (the reference filters those out and then indexes the
+ * unfiltered list with the filtered position, :198-217 — not reproduced).
+ * Host buffers; uses the current device; blocks until done.
+ */
+int lsc_rerank_mmr(const float* doc_vecs, int32_t n_docs, int32_t dim, const int32_t* term_freq,
+                   const int32_t* doc_len, int32_t n_terms, int32_t max_docs, double lambda, double k1,
+                   double b, int32_t* out_order, int32_t* out_count);
+
+/* Same with device pointers (e.g. rows gathered from an index on the device); enqueues one kernel on
+ * `stream` and returns.  *d_out_count < 0 reports the reference's "topDocument is null" condition. */
+int lsc_rerank_mmr_dev(const float* d_doc_vecs, int32_t n_docs, int32_t dim, const int32_t* d_term_freq,
+                       const int32_t* d_doc_len, int32_t n_terms, int32_t max_docs, double lambda, double k1,
+                       double b, int32_t* d_out_order, int32_t* d_out_count, void* stream);
+
 /* ---- debug / verification hooks (not part of the product path) --------------------------- */
 
 /*

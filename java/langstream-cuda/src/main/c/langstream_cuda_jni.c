@@ -77,3 +77,15 @@ JNIEXPORT jlong JNICALL Java_ai_langstream_cuda_LangstreamCuda_indexLoad(JNIEnv*
 JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_indexDestroy(JNIEnv* env, jclass c, jlong ix) {
     lsc_index_destroy((lsc_index*)(intptr_t)ix);
 }
+
+JNIEXPORT jint JNICALL Java_ai_langstream_cuda_LangstreamCuda_rerankMmr(
+        JNIEnv* env, jclass c, jobject vecs, jint n, jint dim, jobject tf, jobject len, jint terms, jint max_docs,
+        jdouble lambda, jdouble k1, jdouble b, jobject out) {
+    int32_t count = 0;
+    int rc = lsc_rerank_mmr((const float*)(*env)->GetDirectBufferAddress(env, vecs), n, dim,
+                            (const int32_t*)(*env)->GetDirectBufferAddress(env, tf),
+                            (const int32_t*)(*env)->GetDirectBufferAddress(env, len), terms, max_docs, lambda, k1, b,
+                            (int32_t*)(*env)->GetDirectBufferAddress(env, out), &count);
+    if (rc != LSC_OK) throw_lsc(env, rc);
+    return count;
+}

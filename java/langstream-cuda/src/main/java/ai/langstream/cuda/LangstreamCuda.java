@@ -51,4 +51,14 @@ public final class LangstreamCuda {
     public static native long indexLoad(String path, int device);
 
     public static native void indexDestroy(long index);
+
+    /**
+     * lsc_rerank_mmr: MMR re-rank (ReRankAgent.rerankMMR). termFreq is [nDocs][nTerms] (frequency of each
+     * query token per document), docLen the token count per document; returns how many indices were
+     * written to outOrder.
+     */
+    public static native int rerankMmr(
+            java.nio.FloatBuffer docVecs, int nDocs, int dim, java.nio.IntBuffer termFreq,
+            java.nio.IntBuffer docLen, int nTerms, int maxDocs, double lambda, double k1, double b,
+            java.nio.IntBuffer outOrder);
 }

@@ -77,6 +77,8 @@ SIGNATURES = {
     "lsc_index_save": (C.c_int, [_vp, C.c_char_p]),
     "lsc_index_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(_vp)]),
     "lsc_index_destroy": (None, [_vp]),
+    "lsc_rerank_mmr": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
+    "lsc_rerank_mmr_dev": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp, _vp]),
     "lsc_debug_attention_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "lsc_debug_gemm_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
 }
@@ -295,3 +297,19 @@ def debug_attention_dev(d_qkv, d_cu_seqlens, n_seq, total_tokens, hidden, heads,
 def debug_gemm_dev(d_A, d_W, d_bias, d_residual, d_C, M, N, K, epilogue, impl, stream=0):
     check(lib().lsc_debug_gemm_dev(_ptr(d_A), _ptr(d_W), _ptr(d_bias), _ptr(d_residual), _ptr(d_C), M, N, K,
                                    epilogue, impl, stream))
+
+
+def rerank_mmr(doc_vecs, term_freq, doc_len, max_docs: int, lam: float, k1: float, b: float):
+    """lsc_rerank_mmr on host arrays: doc_vecs [n, dim] fp32, term_freq [n, t] int32, doc_len [n] int32.
+    Returns the picked indices in MMR order."""
+    doc_vecs = _np.ascontiguousarray(doc_vecs, _np.float32)
+    n = int(doc_vecs.shape[0])
+    dim = int(doc_vecs.shape[1]) if doc_vecs.ndim == 2 and n > 0 else 1
+    term_freq = _np.ascontiguousarray(term_freq, _np.int32).reshape(n, -1) if n > 0 else _np.zeros((0, 0), _np.int32)
+    t = int(term_freq.shape[1]) if n > 0 else 0
+    doc_len = _np.ascontiguousarray(doc_len, _np.int32)
+    order = _np.empty(max(n, 1), _np.int32)
+    count = _np.zeros(1, _np.int32)
+    check(lib().lsc_rerank_mmr(_ptr(doc_vecs), n, dim, _ptr(term_freq), _ptr(doc_len), t, int(max_docs),
+                               float(lam), float(k1), float(b), _ptr(order), _ptr(count)))
+    return [int(i) for i in order[: int(count[0])]]

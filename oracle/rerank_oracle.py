@@ -17,7 +17,14 @@ from .topk_oracle import cosine_scalar
 
 
 def _tokenise(text: str) -> List[str]:
-    return re.split(r"\s+", text)
+    """ReRankAgent.tokenise (:314-316) = Java's text.split("\\s+"): trailing empty strings are dropped, a
+    leading one (text starting with whitespace) is kept, and the empty text gives one empty token."""
+    parts = re.split(r"\s+", text)
+    while len(parts) > 1 and parts[-1] == "":
+        parts.pop()
+    if parts == [""] and text != "":  # text of whitespace only: Java returns an empty array
+        return []
+    return parts
 
 
 def _bm25(docs: Sequence[Tuple[str, Sequence[float]]], query_text: str, k1: float, b: float) -> List[float]:

@@ -34,8 +34,17 @@ def test_rerank_it_pipeline_on_gpu(native_lib, cuda_device):
     assert related[0] == {"text": "text1", "embeddings_vector": [1.0, 2.0, 3.0, 4.0, 5.0]}
     docs = [(d["text"], np.array(d["embeddings_vector"], np.float32)) for d in related]
     m = fx["mmr"]
+    # ... -> re-rank on the device (CudaReRankAgent), the oracle's order and the reference's expected list
+    from langstream_b200.rerank import CudaReRankAgent
+    agent = CudaReRankAgent()
+    agent.init({"max": m["max"], "field": "value.related_documents", "query-text": "value.question",
+                "query-embeddings": "value.question_embeddings", "output-field": "value.related_documents",
+                "text-field": "record.text", "embeddings-field": "record.embeddings_vector", "algorithm": "MMR",
+                "lambda": m["lambda"], "k1": m["k1"], "b": m["b"]})
+    out = agent.process_record(Record(value={"question": fx["query_text"], "question_embeddings": fx["query_embeddings"],
+                                             "related_documents": related}))
     order = rerank_oracle.rerank_mmr(docs, int(m["max"]), fx["query_text"], m["lambda"], m["k1"], m["b"])
-    assert [related[i] for i in order] == fx["expected_related_documents"]
+    assert out[0].value["related_documents"] == [related[i] for i in order] == fx["expected_related_documents"]
     # delete on null value, then the row is gone
     w.upsert(Record(value=None, key=None), {})  # pk evaluates to (None, None): unknown -> ignored
     assert len(ds.fetch_data(fx["sql"], [fx["query_embeddings"]])) == 10
