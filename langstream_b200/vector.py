@@ -110,6 +110,103 @@ class CudaVectorTable:
             self.rows[rid] = dict(row)
             self.index.upsert(np.array([rid], np.int64), self._pad(v)[None, :])
 
+    def _assign_ids(self, pks: List[Tuple]) -> np.ndarray:
+        ids = np.empty(len(pks), np.int64)
+        for i, pk in enumerate(pks):
+            rid = self.id_of_pk.get(pk)
+            if rid is None:
+                rid = self._next_id
+                self._next_id += 1
+                self.id_of_pk[pk] = rid
+            ids[i] = rid
+        return ids
+
+    def upsert_many(self, pks: List[Tuple], rows: List[dict]) -> None:
+        """One native call for a whole batch (the reference does one SQL round trip
+        per record, JdbcWriter.java:139-179).  A primary key repeated inside the batch keeps its last row."""
+        if len(pks) != len(rows):
+            raise ValueError("pks and rows differ in length")
+        if not pks:
+            return
+        last = {pk: i for i, pk in enumerate(pks)}
+        keep = sorted(last.values())
+        vecs = np.zeros((len(keep), self.store_dim), np.float32)
+        for j, i in enumerate(keep):
+            vec = rows[i].get(self.vector_column)
+            if vec is None:
+                raise ValueError(f"column {self.vector_column!r} is null")
+            v = np.asarray(vec, np.float32).reshape(-1)
+            if v.size != self.dim:
+                raise ValueError(f"vector has {v.size} dimensions, table {self.name!r} has {self.dim}")
+            vecs[j, : self.dim] = v
+        with self.lock:
+            ids = self._assign_ids([pks[i] for i in keep])
+            for rid, i in zip(ids, keep):
+                self.rows[int(rid)] = dict(rows[i])
+            self.index.upsert(ids, vecs)
+
+    def upsert_from_device(self, pks: List[Tuple], rows: List[dict], d_vectors, stream: int = 0) -> None:
+        """Feed the index straight from device memory - e.g. the [n, dim] fp32 output of the embeddings
+        service - instead of List<Double> -> List<Float> -> SQL (JstlFunctions.java:93-112).  `rows` hold the
+        other columns; the vector column of the host rows is filled from one batched read-back so that
+        `SELECT embeddings_vector` keeps working.  Primary keys must be distinct within the batch."""
+        n = len(pks)
+        if n != len(rows) or len(set(pks)) != n:
+            raise ValueError("pks must be distinct and match rows")
+        if self.store_dim != self.dim:
+            raise ValueError("device-fed upserts need a dimension that is a multiple of 64")
+        if tuple(d_vectors.shape) != (n, self.dim):
+            raise ValueError(f"expected a [{n}, {self.dim}] device tensor")
+        host = d_vectors.detach().to("cpu").numpy()  # one copy for the whole batch
+        with self.lock:
+            ids = self._assign_ids(list(pks))
+            for j, rid in enumerate(ids):
+                row = dict(rows[j])
+                row[self.vector_column] = host[j]
+                self.rows[int(rid)] = row
+            self.index.upsert_dev(ids, d_vectors, n, stream)
+
+    # -- persistence: the index file of lsc_index_save + the host rows next to it ---------------------
+    def save(self, directory) -> None:
+        """Write <directory>/<name>.lscidx (ids + bf16 rows, lsc_index_save) and <name>.rows.json; the
+        directory is the agent's persistent state directory (AgentContext.java:64-66)."""
+        from pathlib import Path
+        d = Path(directory)
+        d.mkdir(parents=True, exist_ok=True)
+        with self.lock:
+            self.index.save(str(d / f"{self.name}.lscidx"))
+            meta = {"name": self.name, "dim": self.dim, "vector_column": self.vector_column, "next_id": self._next_id,
+                    "pks": [[list(pk), rid] for pk, rid in self.id_of_pk.items()],
+                    "rows": {str(rid): {k: (np.asarray(v).tolist() if isinstance(v, np.ndarray) else v)
+                                        for k, v in row.items()} for rid, row in self.rows.items()}}
+            tmp = d / f"{self.name}.rows.json.tmp"
+            tmp.write_text(json.dumps(meta))
+            tmp.replace(d / f"{self.name}.rows.json")
+
+    @classmethod
+    def load(cls, directory, name: str, device: int = 0, index_loader=None) -> "CudaVectorTable":
+        from pathlib import Path
+        d = Path(directory)
+        meta = json.loads((d / f"{name}.rows.json").read_text())
+        t = cls.__new__(cls)
+        t.name, t.dim, t.vector_column = meta["name"], int(meta["dim"]), meta["vector_column"]
+        t.store_dim = (t.dim + 63) // 64 * 64
+        load = index_loader or (lambda path, dev, dim: _native.Index.load(path, dev, dim))
+        t.index = load(str(d / f"{name}.lscidx"), device, t.store_dim)
+        t.rows = {int(k): v for k, v in meta["rows"].items()}
+        t.id_of_pk = {tuple(pk): int(rid) for pk, rid in meta["pks"]}
+        t._next_id = int(meta["next_id"])
+        t.lock = threading.Lock()
+        if len(t.index) != len(t.rows):
+            raise ValueError(f"table {name!r}: index file holds {len(t.index)} rows, row file {len(t.rows)}")
+        return t
+
+    @staticmethod
+    def exists_on_disk(directory, name: str) -> bool:
+        from pathlib import Path
+        d = Path(directory)
+        return (d / f"{name}.rows.json").exists() and (d / f"{name}.lscidx").exists()
+
     def _pad(self, v: np.ndarray) -> np.ndarray:
         if v.size == self.store_dim:
             return np.ascontiguousarray(v, np.float32)
@@ -151,6 +248,19 @@ def get_table(name: str, dim: Optional[int] = None, vector_column: Optional[str]
             t = CudaVectorTable(name, dim, vector_column, device, index_factory)
             _TABLES[name] = t
         return t
+
+
+def table_exists(name: str) -> bool:
+    with _TABLES_LOCK:
+        return name in _TABLES
+
+
+def register_table(table: CudaVectorTable) -> None:
+    with _TABLES_LOCK:
+        old = _TABLES.get(table.name)
+        _TABLES[table.name] = table
+    if old is not None and old is not table:
+        old.close()
 
 
 def drop_table(name: str) -> None:
@@ -268,9 +378,10 @@ class CudaVectorDatabaseWriter:
     (`table-name`, `fields: [{name, expression, primary-key}]`, JdbcWriter.java:74-95), plus
     `vector-column` (default: the first field whose value is a list) and `dimensions`."""
 
-    def __init__(self, datasource_config: dict, index_factory=None):
+    def __init__(self, datasource_config: dict, index_factory=None, index_loader=None):
         self.datasource_config = dict(datasource_config or {})
         self._index_factory = index_factory
+        self._index_loader = index_loader
         self.table_name: Optional[str] = None
         self.primary_key: Dict[str, str] = {}
         self.columns: Dict[str, str] = {}
@@ -278,6 +389,40 @@ class CudaVectorDatabaseWriter:
         self.dim: Optional[int] = None
         self._table: Optional[CudaVectorTable] = None
         self._lock = threading.Lock()
+        self.state_dir = None
+
+    def upsert_batch(self, records: List[Record]) -> "Future[None]":
+        """All records of a batch in one native call; null values (deletes) are applied in order around it.
+        The future completes once every row is queryable, like `upsert`."""
+        handle: Future = Future()
+        try:
+            with self._lock:
+                pks, rows = [], []
+
+                def flush():
+                    if pks:
+                        self._ensure_table(rows[0]).upsert_many(list(pks), list(rows))
+                        pks.clear()
+                        rows.clear()
+
+                for record in records:
+                    pk = tuple(evaluate(e, record) for e in self.primary_key.values())
+                    if record.value is not None:
+                        row = {n: evaluate(e, record) for n, e in self.primary_key.items()}
+                        row.update({n: evaluate(e, record) for n, e in self.columns.items()})
+                        pks.append(pk)
+                        rows.append(row)
+                    else:
+                        flush()
+                        if self._table is None and table_exists(self.table_name):
+                            self._table = get_table(self.table_name)
+                        if self._table is not None:
+                            self._table.delete(pk)
+                flush()
+            handle.set_result(None)
+        except Exception as e:  # noqa: BLE001
+            handle.set_exception(e)
+        return handle
 
     def initialise(self, agent_configuration: dict) -> None:
         cfg = dict(agent_configuration or {})
@@ -291,6 +436,12 @@ class CudaVectorDatabaseWriter:
             raise ValueError("at least one field must be marked primary-key")
         self.vector_column = cfg.get("vector-column")
         self.dim = cfg.get("dimensions")
+        # restore the table from the agent's persistent state directory, if any
+        self.state_dir = cfg.get("persistent-state-directory")
+        if self.state_dir and not table_exists(self.table_name) and \
+                CudaVectorTable.exists_on_disk(self.state_dir, self.table_name):
+            register_table(CudaVectorTable.load(self.state_dir, self.table_name,
+                                                int(self.datasource_config.get("device", 0)), self._index_loader))
 
     def upsert(self, record: Record, context: Dict[str, Any]) -> "Future[None]":
         handle: Future = Future()
@@ -328,15 +479,82 @@ class CudaVectorDatabaseWriter:
         return self._table
 
     def close(self) -> None:
+        # durable before the agent goes away: the source offsets were committed when the futures completed
+        if self.state_dir and self.table_name and table_exists(self.table_name):
+            get_table(self.table_name).save(self.state_dir)
+
+
+class CudaTableAssetManager:
+    """AssetManager for `asset-type: "cuda-table"`, the counterpart of `jdbc-table`
+    (JdbcAssetsManagerProvider.java:33-144): `assets:` in an application can create / drop a GPU table.
+    Asset config: `table-name`, `dimensions`, `vector-column`, optional `datasource.configuration.device`
+    and `persistent-state-directory` (an existing saved table counts as existing and is loaded on deploy)."""
+
+    def __init__(self, index_factory=None, index_loader=None):
+        self._index_factory, self._index_loader = index_factory, index_loader
+        self.config: Dict[str, Any] = {}
+
+    def initialize(self, asset_definition: Dict[str, Any]) -> None:
+        self.config = dict(asset_definition.get("config", asset_definition) or {})
+        if not self.config.get("table-name"):
+            raise ValueError("table-name is required")
+
+    def _device(self) -> int:
+        ds = (self.config.get("datasource") or {}).get("configuration") or {}
+        return int(ds.get("device", 0))
+
+    def asset_exists(self) -> bool:
+        name, d = self.config["table-name"], self.config.get("persistent-state-directory")
+        return table_exists(name) or bool(d and CudaVectorTable.exists_on_disk(d, name))
+
+    def deploy_asset(self) -> None:
+        name, d = self.config["table-name"], self.config.get("persistent-state-directory")
+        if table_exists(name):
+            return
+        if d and CudaVectorTable.exists_on_disk(d, name):
+            register_table(CudaVectorTable.load(d, name, self._device(), self._index_loader))
+            return
+        dim, col = self.config.get("dimensions"), self.config.get("vector-column")
+        if not dim or not col:
+            raise ValueError("dimensions and vector-column are required to create a cuda-table")
+        get_table(name, int(dim), str(col), self._device(), self._index_factory)
+
+    def delete_asset_if_exists(self) -> bool:
+        if not self.asset_exists():
+            return False
+        name, d = self.config["table-name"], self.config.get("persistent-state-directory")
+        drop_table(name)
+        if d:
+            from pathlib import Path
+            for suffix in (".lscidx", ".rows.json"):
+                p = Path(d) / f"{name}{suffix}"
+                if p.exists():
+                    p.unlink()
+        return True
+
+    def close(self) -> None:
         pass
 
 
+class CudaAssetManagerProvider:
+    def __init__(self, index_factory=None, index_loader=None):
+        self._index_factory, self._index_loader = index_factory, index_loader
+
+    def supports(self, asset_type: str) -> bool:
+        return asset_type == "cuda-table"
+
+    def create_instance(self, asset_type: str) -> CudaTableAssetManager:
+        if asset_type != "cuda-table":
+            raise ValueError(asset_type)  # IllegalArgumentException in the reference
+        return CudaTableAssetManager(self._index_factory, self._index_loader)
+
+
 class CudaVectorDatabaseWriterProvider:
-    def __init__(self, index_factory=None):
-        self._index_factory = index_factory
+    def __init__(self, index_factory=None, index_loader=None):
+        self._index_factory, self._index_loader = index_factory, index_loader
 
     def supports(self, data_source_config: dict) -> bool:
         return (data_source_config or {}).get("service") == "cuda"
 
     def create_implementation(self, datasource_config: dict) -> CudaVectorDatabaseWriter:
-        return CudaVectorDatabaseWriter(datasource_config, self._index_factory)
+        return CudaVectorDatabaseWriter(datasource_config, self._index_factory, self._index_loader)

@@ -43,6 +43,19 @@ class FakeIndex:
         ids = np.where(slots >= 0, np.asarray(self.ids, np.int64)[np.maximum(slots, 0)], -1)
         return ids, scores
 
+    def save(self, path):
+        np.savez(path + ".npz", dim=self.dim, ids=np.asarray(self.ids, np.int64),
+                 rows=np.stack(self.rows) if self.rows else np.zeros((0, self.dim), np.float32))
+        open(path, "wb").close()  # the native file name exists too
+
+    @classmethod
+    def load(cls, path, device=0, dim=None):
+        z = np.load(path + ".npz")
+        ix = cls(int(z["dim"]), device)
+        ix.ids = [int(i) for i in z["ids"]]
+        ix.rows = [r.copy() for r in z["rows"]]
+        return ix
+
     def close(self):
         pass
 

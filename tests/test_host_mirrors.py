@@ -162,3 +162,50 @@ def test_split_by_tokens_covers_everything_once():
         rows = [shard_rows(1000003, world, r) for r in range(world)]
         assert rows[0][0] == 0 and rows[-1][1] == 1000003 and all(a[1] == b[0] for a, b in zip(rows, rows[1:]))
     assert split_by_tokens(np.array([0]), 4) == [(0, 0)] * 4   # empty batch
+
+
+def test_batched_sink_persistence_and_asset_manager(fake_tables, tmp_path):
+    """batched upserts, the table restored from the agent's persistent state
+    directory, and a `cuda-table` asset mirroring `jdbc-table` (JdbcAssetsManagerProvider.java:33-144)."""
+    from langstream_b200 import vector
+    from langstream_b200.vector import (CudaAssetManagerProvider, CudaVectorDataSource,
+                                        CudaVectorDatabaseWriterProvider, Record)
+
+    loader = lambda path, dev, dim: FakeIndex.load(path, dev, dim)  # noqa: E731
+    cfg = {"table-name": "docs", "persistent-state-directory": str(tmp_path), "fields": [
+        {"name": "id", "expression": "key.id", "primary-key": True},
+        {"name": "vector", "expression": "fn:toListOfFloat(value.vector)"},
+        {"name": "text", "expression": "value.text"}]}
+    w = CudaVectorDatabaseWriterProvider(fake_tables, loader).create_implementation({"service": "cuda"})
+    w.initialise(cfg)
+    rng = np.random.default_rng(3)
+    vecs = rng.standard_normal((12, 8)).astype(np.float32)
+    recs = [Record(key={"id": i}, value={"vector": vecs[i].tolist(), "text": f"t{i}"}) for i in range(12)]
+    recs.insert(6, Record(key={"id": 2}, value=None))                      # delete in the middle of the batch
+    recs.append(Record(key={"id": 3}, value={"vector": vecs[0].tolist(), "text": "t3 again"}))  # later row wins
+    assert w.upsert_batch(recs).result(5) is None
+    ds = CudaVectorDataSource(fake_tables)
+    ds.initialize({"service": "cuda"})
+    sql = "SELECT id,text FROM docs ORDER BY cosine_similarity(vector, CAST(? AS FLOAT ARRAY)) DESC LIMIT 20"
+    got = ds.fetch_data(sql, [vecs[0].tolist()])
+    assert len(got) == 11 and {"id": 2, "text": "t2"} not in got
+    assert got[0] == {"id": 0, "text": "t0"} and got[1] == {"id": 3, "text": "t3 again"}   # tie: earlier row first
+    w.close()                                                                 # saves the table
+    assert (tmp_path / "docs.lscidx").exists() and (tmp_path / "docs.rows.json").exists()
+    vector.drop_table("docs")
+    # a new agent instance restores it
+    w2 = CudaVectorDatabaseWriterProvider(fake_tables, loader).create_implementation({"service": "cuda"})
+    w2.initialise(cfg)
+    assert ds.fetch_data(sql, [vecs[0].tolist()]) == got
+    # assets: exists (loaded / on disk), delete, re-create empty
+    am = CudaAssetManagerProvider(fake_tables, loader)
+    assert am.supports("cuda-table") and not am.supports("jdbc-table")
+    a = am.create_instance("cuda-table")
+    a.initialize({"config": {"table-name": "docs", "dimensions": 8, "vector-column": "vector",
+                             "persistent-state-directory": str(tmp_path)}})
+    assert a.asset_exists()
+    assert a.delete_asset_if_exists() is True and not a.asset_exists()
+    assert a.delete_asset_if_exists() is False
+    assert not (tmp_path / "docs.lscidx").exists()
+    a.deploy_asset()
+    assert a.asset_exists() and ds.fetch_data(sql, [vecs[0].tolist()]) == []

@@ -74,3 +74,52 @@ def test_embeddings_service_on_gpu(native_lib, cuda_device):
     cos = (got * want).sum(1) / (np.linalg.norm(got, axis=1) * np.linalg.norm(want, axis=1))
     assert cos.min() >= 0.999 and np.abs(got - want).max() <= 2e-3
     provider.close()
+
+
+def test_gpu_resident_sink_and_persistence(native_lib, cuda_device, tmp_path):
+    """SURVEY.md §8(f) row 2 on the CUDA handles: embeddings stay on the device between the encoder and the
+    index (`upsert_from_device`), a batched host upsert, save to / restore from the persistent state
+    directory, and the `cuda-table` asset."""
+    import torch
+    from langstream_b200 import vector, weights as W
+    from langstream_b200._native import Encoder
+    from langstream_b200.vector import CudaAssetManagerProvider, CudaVectorDataSource, CudaVectorTable
+
+    vector.drop_table("chunks")
+    spec = W.MINILM_L6
+    enc = Encoder(spec, W.random_init(spec, 0))
+    n = 96
+    ids, cu = W.synthetic_token_ids(n, 32, seed=11, min_len=8)
+    dev = torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    d_out = torch.empty(n, spec.hidden, device=dev)
+    enc.embed_dev(torch.from_numpy(ids).to(dev), torch.from_numpy(cu).to(dev), n, int(cu[-1]), 32, d_out, st)
+    torch.cuda.synchronize()
+    a = CudaAssetManagerProvider().create_instance("cuda-table")
+    a.initialize({"config": {"table-name": "chunks", "dimensions": spec.hidden, "vector-column": "embeddings_vector",
+                             "persistent-state-directory": str(tmp_path)}})
+    assert not a.asset_exists()
+    a.deploy_asset()
+    t = vector.get_table("chunks")
+    half = n // 2
+    t.upsert_from_device([(i,) for i in range(half)], [{"chunk": i, "text": f"text {i}"} for i in range(half)],
+                         d_out[:half], st)
+    host = d_out[half:].cpu().numpy()
+    t.upsert_many([(i,) for i in range(half, n)],
+                  [{"chunk": i, "text": f"text {i}", "embeddings_vector": host[i - half].tolist()} for i in range(half, n)])
+    ds = CudaVectorDataSource()
+    ds.initialize({"service": "cuda"})
+    sql = "SELECT chunk,text FROM chunks ORDER BY cosine_similarity(embeddings_vector, CAST(? AS FLOAT ARRAY)) DESC LIMIT 3"
+    emb = d_out.cpu().numpy()
+    for probe in (0, half - 1, half, n - 1):       # every row finds itself first, device-fed or host-fed
+        got = ds.fetch_data(sql, [emb[probe].tolist()])
+        assert got[0] == {"chunk": probe, "text": f"text {probe}"}
+    before = [ds.fetch_data(sql, [emb[p].tolist()]) for p in (3, 70)]
+    t.save(tmp_path)
+    vector.drop_table("chunks")
+    assert a.asset_exists()                        # on disk
+    a.deploy_asset()                               # restores it
+    assert len(vector.get_table("chunks").index) == n
+    assert [ds.fetch_data(sql, [emb[p].tolist()]) for p in (3, 70)] == before
+    assert a.delete_asset_if_exists() and not CudaVectorTable.exists_on_disk(tmp_path, "chunks")
+    enc.close()
