@@ -95,7 +95,9 @@ int grow_buf(T** p, int64_t* cap, int64_t need, int64_t floor_) {
 }
 
 int ensure_query_buffers(lsc_index* ix, int B, int k) {
-    const int64_t bpad = (static_cast<int64_t>(B) + TK_QROWS - 1) / TK_QROWS * TK_QROWS;
+    // padded to whole 128-query blocks; to whole 256-query blocks when the CTA-pair scan may run
+    const int64_t qblk = B > TK_QROWS ? 2 * TK_QROWS : TK_QROWS;
+    const int64_t bpad = (static_cast<int64_t>(B) + qblk - 1) / qblk * qblk;
     if (bpad > ix->cap_q) {
         LSC_CUDA(cudaDeviceSynchronize());
         if (ix->d_qbf) cudaFree(ix->d_qbf);
@@ -134,20 +136,33 @@ int search_dev(lsc_index* ix, const float* d_queries, int B, int k, int64_t* d_o
         return LSC_OK;
     }
     LSC_TRY(ensure_query_buffers(ix, B, k));
-    const int bpad = (B + TK_QROWS - 1) / TK_QROWS * TK_QROWS;
+    const int qblk = B > TK_QROWS ? 2 * TK_QROWS : TK_QROWS;
+    const int bpad = (B + qblk - 1) / qblk * qblk;
     LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st));
     const int n_rows = static_cast<int>(ix->n);
     const bool rows_kernel = topk_scan_rows_supported(ix->dim, k);
-    const int grid = rows_kernel ? topk_scan_rows_grid(n_rows, ix->num_sms) : topk_scan_grid(n_rows, ix->num_sms);
-    for (int qb = 0; qb * TK_QROWS < B; ++qb) {
-        const int nq = std::min(TK_QROWS, B - qb * TK_QROWS);
-        const size_t off = static_cast<size_t>(qb) * grid * TK_QROWS * k;
-        if (rows_kernel)
-            LSC_LAUNCH(1, topk_scan_rows_launch(ix->tmapQ, ix->tmapC128, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
-                                                ix->d_cand_scores + off, ix->d_cand_idx + off, st));
-        else
-            LSC_LAUNCH(1, topk_scan_launch(ix->tmapQ, ix->tmapC, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
-                                           ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+    const bool pair = rows_kernel && B > TK_QROWS && topk_scan_rows_pair_supported(ix->dim, k, ix->num_sms);
+    const int grid = pair ? topk_scan_rows_pair_grid(n_rows, ix->num_sms)
+                          : (rows_kernel ? topk_scan_rows_grid(n_rows, ix->num_sms) : topk_scan_grid(n_rows, ix->num_sms));
+    if (pair) {
+        // 256 queries per pass over the corpus (two query blocks of the candidate scratch per launch)
+        for (int q0 = 0; q0 < B; q0 += 2 * TK_QROWS) {
+            const int nq = std::min(2 * TK_QROWS, B - q0);
+            const size_t off = static_cast<size_t>(q0 / TK_QROWS) * grid * TK_QROWS * k;
+            LSC_LAUNCH(1, topk_scan_rows_pair_launch(ix->tmapQ, ix->tmapC128, q0, nq, n_rows, ix->dim, k, grid,
+                                                     ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+        }
+    } else {
+        for (int qb = 0; qb * TK_QROWS < B; ++qb) {
+            const int nq = std::min(TK_QROWS, B - qb * TK_QROWS);
+            const size_t off = static_cast<size_t>(qb) * grid * TK_QROWS * k;
+            if (rows_kernel)
+                LSC_LAUNCH(1, topk_scan_rows_launch(ix->tmapQ, ix->tmapC128, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
+                                                    ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+            else
+                LSC_LAUNCH(1, topk_scan_launch(ix->tmapQ, ix->tmapC, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
+                                               ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+        }
     }
     LSC_LAUNCH(2, topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, d_out_ids,
                                       d_out_scores, st));

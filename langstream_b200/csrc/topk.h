@@ -22,6 +22,12 @@ int topk_scan_rows_grid(int n_rows, int num_sms);
 int topk_scan_rows_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows,
                           int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream);
 
+// CTA-pair variant: up to 256 queries per pass (see topk_rows.cu); grid from topk_scan_rows_pair_grid.
+bool topk_scan_rows_pair_supported(int dim, int k, int num_sms);
+int topk_scan_rows_pair_grid(int n_rows, int num_sms);
+int topk_scan_rows_pair_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows,
+                               int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream);
+
 // Merge the scan scratch [qblocks][parts][128][k] into [B][k]; slots are mapped through slot_ids.
 int topk_merge_scan_launch(const float* cand_scores, const int32_t* cand_idx, int parts, int B, int k,
                            const int64_t* slot_ids, int64_t* out_ids, float* out_scores,

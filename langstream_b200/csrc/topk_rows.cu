@@ -45,7 +45,6 @@ constexpr int TR_MAX_STAGES = 8;
 constexpr int TR_ACC_STRIDE = 128;                     // TMEM columns per accumulator stage (N <= 128)
 constexpr int TR_BUF = 32;                             // candidate buffer entries per query (= one per lane)
 constexpr int TR_TRIG = 16;                            // compact a query once its buffer holds this many
-constexpr int TR_FIXED_EXTRA = TK_QROWS * (TR_BUF * 8 + 8) + 256 + 1024;  // buffers, thresholds, counters, barriers, alignment
 
 // One warp merges the n (<= 32) buffered candidates of a query into its sorted top-k list (k <= 16) by
 // all-pairs ranking.  Order: higher score first, equal scores by lower row number (the reference's stable
@@ -87,6 +86,12 @@ __device__ __forceinline__ void compact_query(uint32_t ls, uint32_t li, uint32_t
     __syncwarp();
 }
 
+// PAIR = 2 (query blocks of more than 128 queries): a cluster of two CTAs scans 256 corpus rows per tile
+// against 256 queries with cta_group::2 MMAs (M = 256 rows, N = 256 queries).  Each CTA streams its own 128
+// rows and keeps its own 128 queries resident - exactly the B-operand half a CTA pair stages - so one pass
+// over the corpus serves twice the queries for the same HBM traffic and shared memory; each CTA selects for
+// all 256 queries over its own rows (two 32-query chunks per warp, 16-entry candidate buffers).
+template <int PAIR>
 __global__ void __launch_bounds__(TR_THREADS, 1)
 topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constant__ CUtensorMap tmapC,
                       int q_row0, int nq, int n_rows, int dim, int k, int stages, uint32_t idesc,
@@ -95,6 +100,12 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     // aligned by pointer arithmetic on the shared array (an integer round trip would turn every access
     // through it into a generic-address one)
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    constexpr int NQ = TK_QROWS * PAIR;             // queries this CTA selects for
+    constexpr int BUF = PAIR == 2 ? 16 : TR_BUF;    // candidate buffer entries per query
+    constexpr int TRIG = BUF / 2;
+    constexpr int CPW = PAIR;                       // 32-query chunks per selection warp
+    constexpr int ACC = TR_ACC_STRIDE * PAIR;       // TMEM columns per accumulator stage
+    const uint32_t cta_rank = PAIR == 2 ? cluster_ctarank() : 0u;
     const int num_kb = dim / TR_BK;
     const uint32_t sQ = smem_u32(smem);
     const uint32_t sC = sQ + num_kb * TR_QBLK_BYTES;
@@ -103,12 +114,12 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     // current k-th score, number of buffered candidates
     // (all held as 32-bit shared-window addresses, see ptx.cuh)
     const uint32_t lists_s = smem_u32(after_ring);
-    const uint32_t lists_i = lists_s + 4 * TK_QROWS * k;
-    const uint32_t buf_s = lists_i + 4 * TK_QROWS * k;
-    const uint32_t buf_i = buf_s + 4 * TK_QROWS * TR_BUF;
-    const uint32_t thrs = buf_i + 4 * TK_QROWS * TR_BUF;
-    const uint32_t cnt = thrs + 4 * TK_QROWS;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * TK_QROWS * k + 8 * TK_QROWS * TR_BUF + 8 * TK_QROWS);
+    const uint32_t lists_i = lists_s + 4 * NQ * k;
+    const uint32_t buf_s = lists_i + 4 * NQ * k;
+    const uint32_t buf_i = buf_s + 4 * NQ * BUF;
+    const uint32_t thrs = buf_i + 4 * NQ * BUF;
+    const uint32_t cnt = thrs + 4 * NQ;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * NQ * k + 8 * NQ * BUF + 8 * NQ);
     const uint32_t bar_full = smem_u32(bars);
     const uint32_t bar_empty = bar_full + 8 * TR_MAX_STAGES;
     const uint32_t bar_tfull = bar_empty + 8 * TR_MAX_STAGES;
@@ -124,50 +135,74 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
         tma_prefetch_desc(&tmapQ);
         tma_prefetch_desc(&tmapC);
         for (int s = 0; s < stages; ++s) {
-            mbar_init(bar_full + 8 * s, 1);
+            mbar_init(bar_full + 8 * s, PAIR);  // the leader's: one arrival per CTA's producer
             mbar_init(bar_empty + 8 * s, 1);
         }
+        const int scanning_warps = 4 * (((nq + 31) / 32 + CPW - 1) / CPW);
         for (int a = 0; a < 2; ++a) {
             mbar_init(bar_tfull + 8 * a, 1);
-            mbar_init(bar_tempty + 8 * a, 4 * ((nq + 31) / 32));  // one arrival per scanning warp
+            mbar_init(bar_tempty + 8 * a, scanning_warps * PAIR);  // one arrival per scanning warp (of both CTAs)
         }
-        mbar_init(bar_q, 1);
+        mbar_init(bar_q, PAIR);
         fence_mbar_init();
     }
     if (warp == 1) {
-        tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), 256);
-        tmem_relinquish();
+        if (PAIR == 2) {
+            tmem_alloc_pair(smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
+            tmem_relinquish_pair();
+        } else {
+            tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), 256);
+            tmem_relinquish();
+        }
     }
-    for (int i = threadIdx.x; i < TK_QROWS * k; i += TR_THREADS) {
+    for (int i = threadIdx.x; i < NQ * k; i += TR_THREADS) {
         sts_f32(lists_s + 4 * i, -INFINITY);
         sts_s32(lists_i + 4 * i, -1);
     }
-    for (int i = threadIdx.x; i < TK_QROWS; i += TR_THREADS) {
+    for (int i = threadIdx.x; i < NQ; i += TR_THREADS) {
         sts_f32(thrs + 4 * i, -INFINITY);
         sts_s32(cnt + 4 * i, 0);
     }
     if (threadIdx.x == 0) sts_s32(again_epoch, -1);
     tc_fence_before();
-    __syncthreads();
+    if (PAIR == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    const int num_tiles = (n_rows + TR_BM - 1) / TR_BM;
+    // a tile = 128 * PAIR corpus rows, one per CTA (pair); this CTA's rows are its rank's half
+    const int num_tiles = (n_rows + TR_BM * PAIR - 1) / (TR_BM * PAIR);
+    const int tile0 = blockIdx.x / PAIR, tile_step = gridDim.x / PAIR;
 
     if (warp == 0) {
         if (elect_one()) {
-            mbar_arrive_expect_tx(bar_q, num_kb * TR_QBLK_BYTES);
-            for (int kb = 0; kb < num_kb; ++kb)
-                tma_load_2d(sQ + kb * TR_QBLK_BYTES, &tmapQ, bar_q, kb * TR_BK, q_row0);
+            const uint32_t lead_q = PAIR == 2 ? mapa_u32(bar_q, 0) : bar_q;
+            if (PAIR == 2) {
+                // each CTA keeps its half of the 256 queries: rows [q_row0 + 128 * rank, + 128)
+                if (cta_rank == 0) mbar_arrive_expect_tx(bar_q, num_kb * TR_QBLK_BYTES * 2); else mbar_arrive_cluster(lead_q);
+                for (int kb = 0; kb < num_kb; ++kb)
+                    tma_load_2d_pair(sQ + kb * TR_QBLK_BYTES, &tmapQ, lead_q, kb * TR_BK,
+                                     q_row0 + static_cast<int>(cta_rank) * TK_QROWS);
+            } else {
+                mbar_arrive_expect_tx(bar_q, num_kb * TR_QBLK_BYTES);
+                for (int kb = 0; kb < num_kb; ++kb)
+                    tma_load_2d(sQ + kb * TR_QBLK_BYTES, &tmapQ, bar_q, kb * TR_BK, q_row0);
+            }
             const uint64_t pol = policy_evict_first();
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                    mbar_arrive_expect_tx(bar_full + 8 * stage, TR_STAGE_BYTES);
-                    tma_load_2d_hint(sC + stage * TR_STAGE_BYTES, &tmapC, bar_full + 8 * stage, kb * TR_BK,
-                                     tile * TR_BM, pol);
+                    if (PAIR == 2) {
+                        const uint32_t lf = mapa_u32(bar_full + 8 * stage, 0);
+                        if (cta_rank == 0) mbar_arrive_expect_tx(bar_full + 8 * stage, TR_STAGE_BYTES * 2); else mbar_arrive_cluster(lf);
+                        tma_load_2d_pair_hint(sC + stage * TR_STAGE_BYTES, &tmapC, lf, kb * TR_BK,
+                                              (tile * 2 + static_cast<int>(cta_rank)) * TR_BM, pol);
+                    } else {
+                        mbar_arrive_expect_tx(bar_full + 8 * stage, TR_STAGE_BYTES);
+                        tma_load_2d_hint(sC + stage * TR_STAGE_BYTES, &tmapC, bar_full + 8 * stage, kb * TR_BK,
+                                         tile * TR_BM, pol);
+                    }
                     if (++stage == stages) {
                         stage = 0;
                         phase ^= 1;
@@ -176,53 +211,58 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
             }
         }
     } else if (warp == 1) {
-        if (elect_one()) {
+        if (cta_rank == 0 && elect_one()) {  // the pair's leader issues all MMAs
             mbar_wait(bar_q, 0);
             tc_fence_after();
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
                 mbar_wait(bar_tempty + 8 * acc, acc_phase ^ 1);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * TR_ACC_STRIDE;
+                const uint32_t d_tmem = tmem_base + acc * ACC;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(bar_full + 8 * stage, phase);
                     tc_fence_after();
                     const uint64_t da = umma_desc_sw128(sC + stage * TR_STAGE_BYTES);  // corpus rows: M
                     const uint64_t db = umma_desc_sw128(sQ + kb * TR_QBLK_BYTES);      // queries: N
 #pragma unroll
-                    for (int kk = 0; kk < TR_BK / 16; ++kk)
-                        umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
-                    umma_commit(bar_empty + 8 * stage);
+                    for (int kk = 0; kk < TR_BK / 16; ++kk) {
+                        if (PAIR == 2)
+                            umma_bf16_pair(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
+                        else
+                            umma_bf16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0 ? 1u : 0u);
+                    }
+                    if (PAIR == 2) umma_commit_pair(bar_empty + 8 * stage); else umma_commit(bar_empty + 8 * stage);
                     if (++stage == stages) {
                         stage = 0;
                         phase ^= 1;
                     }
                 }
-                umma_commit(bar_tfull + 8 * acc);
+                if (PAIR == 2) umma_commit_pair(bar_tfull + 8 * acc); else umma_commit(bar_tfull + 8 * acc);
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
             }
         }
     } else {
-        // ===== selection: warp (quadrant, chunk); lane = corpus row, columns = the chunk's 32 queries =====
+        // ===== selection: warp (quadrant, chunk group); lane = corpus row, columns = 32 queries per chunk =====
         const int quad = warp & 3;
         const int sw = warp - 2;   // selection warp 0..15; it owns the queries q with q % 16 == sw for compaction
-        const int c = sw >> 2;     // query chunk this warp scans
+        const int cg = sw >> 2;    // chunk group: this warp scans chunks cg * CPW .. cg * CPW + CPW - 1
         const int nchunks = (nq + 31) / 32;
-        const bool scans = c < nchunks;
-        const int qlim = nq - c * 32;  // queries of this chunk that exist
-        const uint32_t qmask = qlim >= 32 ? 0xffffffffu : (qlim > 0 ? ((1u << qlim) - 1u) : 0u);
-        const int myq = lane * TR_SEL_WARPS + sw;  // lanes 0..7: the queries this warp compacts
+        const bool scans = cg * CPW < nchunks;
+        const int myq = lane * TR_SEL_WARPS + sw;  // lanes 0 .. NQ / 16 - 1: the queries this warp compacts
+        const uint32_t lead_tempty = PAIR == 2 ? mapa_u32(bar_tempty, 0) : bar_tempty;
         int acc = 0;
         uint32_t acc_phase = 0;
         int epoch = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const int32_t row = tile * TR_BM + quad * 32 + lane;
-            const uint32_t tcol = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * TR_ACC_STRIDE + c * 32;
-            uint32_t pend = 0u;  // (row, query) pairs whose append found the buffer full
+        for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+            const int32_t row = (tile * PAIR + static_cast<int>(cta_rank)) * TR_BM + quad * 32 + lane;
+            const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC;
+            uint32_t pend[CPW];  // (row, query) pairs whose append found the buffer full
+#pragma unroll
+            for (int cc = 0; cc < CPW; ++cc) pend[cc] = 0u;
             bool released = !scans;
             if (scans) {
                 mbar_wait(bar_tfull + 8 * acc, acc_phase);
@@ -230,7 +270,15 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
             }
             for (int round = 0;; ++round, ++epoch) {
                 // ---- append phase ----
-                if (scans && (round == 0 || __any_sync(0xffffffffu, pend != 0u))) {
+                bool mine_pending = false;
+#pragma unroll
+                for (int cc = 0; cc < CPW; ++cc) {
+                    const int c = cg * CPW + cc;
+                    if (c >= nchunks) continue;
+                    if (round > 0 && !__any_sync(0xffffffffu, pend[cc] != 0u)) continue;  // warp-uniform
+                    const uint32_t tcol = tbase + c * 32;
+                    const int qlim = nq - c * 32;  // queries of this chunk that exist
+                    const uint32_t qmask = qlim >= 32 ? 0xffffffffu : ((1u << qlim) - 1u);
                     uint32_t v[32];
                     tmem_ld_32x32(tcol, v);
                     tmem_ld_wait();
@@ -245,8 +293,8 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                         m |= (__uint_as_float(v[j4 * 4 + 3]) > t.w ? 1u : 0u) << (j4 * 4 + 3);
                     }
                     m &= row < n_rows ? qmask : 0u;
-                    if (round > 0) m &= pend;
-                    pend = 0u;
+                    if (round > 0) m &= pend[cc];
+                    uint32_t full = 0u;
                     uint32_t any = __reduce_or_sync(0xffffffffu, m);
                     while (any) {  // warp-uniform; rare once the lists have warmed up
                         const int j = __ffs(any) - 1;
@@ -256,35 +304,39 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                         if ((m >> j) & 1u) {
                             const int q = c * 32 + j;
                             const int pos = atoms_add_s32(cnt + 4 * q, 1);
-                            if (pos < TR_BUF) {
-                                sts_f32(buf_s + 4 * (q * TR_BUF + pos), __uint_as_float(sc));
-                                sts_s32(buf_i + 4 * (q * TR_BUF + pos), row);
+                            if (pos < BUF) {
+                                sts_f32(buf_s + 4 * (q * BUF + pos), __uint_as_float(sc));
+                                sts_s32(buf_i + 4 * (q * BUF + pos), row);
                             } else {
-                                pend |= 1u << j;
+                                full |= 1u << j;
                             }
                         }
                     }
+                    pend[cc] = full;
+                    mine_pending = mine_pending || full != 0u;
                 }
-                if (pend != 0u) sts_s32(again_epoch, epoch);
-                if (!released && !__any_sync(0xffffffffu, pend != 0u)) {
+                if (mine_pending) sts_s32(again_epoch, epoch);
+                if (!released && !__any_sync(0xffffffffu, mine_pending)) {
                     // this warp is done with its part of the tile's accumulator
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_tempty + 8 * acc);
+                    if (lane == 0) {
+                        if (PAIR == 2) mbar_arrive_cluster(lead_tempty + 8 * acc); else mbar_arrive(bar_tempty + 8 * acc);
+                    }
                     released = true;
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
                 // ---- compaction phase: buffers are stable until the second barrier ----
                 const bool again = lds_s32(again_epoch) == epoch;
-                const int n_my = (lane < TK_QROWS / TR_SEL_WARPS && myq < nq) ? lds_s32(cnt + 4 * myq) : 0;
-                uint32_t need = __ballot_sync(0xffffffffu, n_my >= TR_TRIG);
+                const int n_my = (lane < NQ / TR_SEL_WARPS && myq < nq) ? lds_s32(cnt + 4 * myq) : 0;
+                uint32_t need = __ballot_sync(0xffffffffu, n_my >= TRIG);
                 while (need) {
                     const int l = __ffs(need) - 1;
                     need &= need - 1;
                     const int q = l * TR_SEL_WARPS + sw;
                     int n = __shfl_sync(0xffffffffu, n_my, l);
-                    n = n < TR_BUF ? n : TR_BUF;
-                    compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * TR_BUF, buf_i + 4 * q * TR_BUF,
+                    n = n < BUF ? n : BUF;
+                    compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * BUF, buf_i + 4 * q * BUF,
                                   thrs + 4 * q, k, n);
                     if (lane == 0) sts_s32(cnt + 4 * q, 0);
                 }
@@ -297,22 +349,24 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
         }
         // ---- flush what is left in the buffers, then the CTA's lists are final ----
         {
-            const int n_my = (lane < TK_QROWS / TR_SEL_WARPS && myq < nq) ? lds_s32(cnt + 4 * myq) : 0;
+            const int n_my = (lane < NQ / TR_SEL_WARPS && myq < nq) ? lds_s32(cnt + 4 * myq) : 0;
             uint32_t need = __ballot_sync(0xffffffffu, n_my > 0);
             while (need) {
                 const int l = __ffs(need) - 1;
                 need &= need - 1;
                 const int q = l * TR_SEL_WARPS + sw;
                 int n = __shfl_sync(0xffffffffu, n_my, l);
-                n = n < TR_BUF ? n : TR_BUF;
-                compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * TR_BUF, buf_i + 4 * q * TR_BUF,
+                n = n < BUF ? n : BUF;
+                compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * BUF, buf_i + 4 * q * BUF,
                               thrs + 4 * q, k, n);
             }
         }
         asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
+        // candidates as [query block][CTA][128][k] (the layout topk_merge_kernel reads)
         for (int i = sw * 32 + lane; i < nq * k; i += 32 * TR_SEL_WARPS) {
             const int q = i / k, pp = i % k;
-            const size_t base = (static_cast<size_t>(blockIdx.x) * TK_QROWS + q) * k;
+            const size_t base =
+                ((static_cast<size_t>(q >> 7) * gridDim.x + blockIdx.x) * TK_QROWS + static_cast<size_t>(q & 127)) * k;
             const int32_t r = lds_s32(lists_i + 4 * i);
             cand_scores[base + pp] = r >= 0 ? lds_f32(lists_s + 4 * i) : -INFINITY;
             cand_idx[base + pp] = r;
@@ -320,14 +374,21 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (PAIR == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 256);
+        if (PAIR == 2) tmem_dealloc_pair(tmem_base, 512); else tmem_dealloc(tmem_base, 256);
     }
 }
 
 }  // namespace
+
+// fixed shared memory of the kernel: resident query block, per-query lists / buffers / thresholds / counters,
+// barriers, alignment slack
+static int rows_fixed_bytes(int dim, int k, int pair) {
+    const int nq = TK_QROWS * pair, buf = pair == 2 ? 16 : TR_BUF;
+    return (dim / TR_BK) * TR_QBLK_BYTES + nq * k * 8 + nq * buf * 8 + nq * 8 + 256 + 1024;
+}
 
 int topk_scan_rows_grid(int n_rows, int num_sms) {
     const int tiles = (n_rows + TR_BM - 1) / TR_BM;
@@ -337,32 +398,76 @@ int topk_scan_rows_grid(int n_rows, int num_sms) {
 bool topk_scan_rows_supported(int dim, int k) {
     static const bool legacy = getenv("LSC_TOPK_LEGACY") != nullptr;  // debug: force the query-major kernel
     if (legacy || k > 16 || dim % TR_BK != 0 || dim <= 0 || dim > 512) return false;
-    const int fixed = (dim / TR_BK) * TR_QBLK_BYTES + TK_QROWS * k * 8 + TR_FIXED_EXTRA;
-    return (227 * 1024 - fixed) / TR_STAGE_BYTES >= 3;
+    return (227 * 1024 - rows_fixed_bytes(dim, k, 1)) / TR_STAGE_BYTES >= 3;
+}
+
+// CTA pairs: 256 queries per pass.  LSC_TOPK_PAIR=0 (debug) keeps 128-query passes.
+bool topk_scan_rows_pair_supported(int dim, int k, int num_sms) {
+    static const bool off = [] {
+        const char* e = getenv("LSC_TOPK_PAIR");
+        return e != nullptr && atoi(e) == 0;
+    }();
+    if (off || num_sms < 2 || !topk_scan_rows_supported(dim, k)) return false;
+    return (227 * 1024 - rows_fixed_bytes(dim, k, 2)) / TR_STAGE_BYTES >= 3;
+}
+
+int topk_scan_rows_pair_grid(int n_rows, int num_sms) {
+    const int tile_pairs = (n_rows + 2 * TR_BM - 1) / (2 * TR_BM);
+    const int clusters = tile_pairs < num_sms / 2 ? tile_pairs : num_sms / 2;
+    return 2 * clusters;
+}
+
+template <int PAIR>
+static int rows_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows, int dim,
+                       int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream) {
+    const int fixed = rows_fixed_bytes(dim, k, PAIR);
+    int stages = (227 * 1024 - fixed) / TR_STAGE_BYTES;
+    if (stages > TR_MAX_STAGES) stages = TR_MAX_STAGES;
+    if (stages < 3) return fail(LSC_E_UNSUPPORTED, "top-k (row-major): unsupported dim / k");
+    const size_t smem = static_cast<size_t>(fixed) + static_cast<size_t>(stages) * TR_STAGE_BYTES;
+    int n_mma = (nq + 15) / 16 * 16;
+    if (n_mma < 16) n_mma = 16;
+    if (PAIR == 2) n_mma = 256;  // each CTA supplies 128 query rows (zero rows past the end of the batch)
+    const uint32_t idesc = umma_idesc_bf16(TR_BM * PAIR, static_cast<uint32_t>(n_mma));
+    static bool configured[64] = {};
+    auto kern = topk_scan_rows_kernel<PAIR>;
+    int dev = 0;
+    LSC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+        LSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(grid);
+    lc.blockDim = dim3(TR_THREADS);
+    lc.dynamicSmemBytes = smem;
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = PAIR;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    LSC_CUDA(cudaLaunchKernelEx(&lc, kern, tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, stages, idesc, cand_scores, cand_idx));
+    LSC_CUDA(cudaGetLastError());
+    return 1;
 }
 
 // tmapC here must have a box of 128 rows x 64 columns (the query-major kernel uses 256-row boxes).
 int topk_scan_rows_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows,
                           int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream) {
     if (!topk_scan_rows_supported(dim, k)) return fail(LSC_E_UNSUPPORTED, "top-k (row-major): unsupported dim / k");
-    const int fixed = (dim / TR_BK) * TR_QBLK_BYTES + TK_QROWS * k * 8 + TR_FIXED_EXTRA;
-    int stages = (227 * 1024 - fixed) / TR_STAGE_BYTES;
-    if (stages > TR_MAX_STAGES) stages = TR_MAX_STAGES;
-    const size_t smem = static_cast<size_t>(fixed) + static_cast<size_t>(stages) * TR_STAGE_BYTES;
-    int n_mma = (nq + 15) / 16 * 16;
-    if (n_mma < 16) n_mma = 16;
-    const uint32_t idesc = umma_idesc_bf16(TR_BM, static_cast<uint32_t>(n_mma));
-    static bool configured[64] = {};
-    int dev = 0;
-    LSC_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !configured[dev]) {
-        LSC_CUDA(cudaFuncSetAttribute(topk_scan_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        if (dev >= 0 && dev < 64) configured[dev] = true;
-    }
-    topk_scan_rows_kernel<<<grid, TR_THREADS, smem, stream>>>(tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, stages, idesc,
-                                                            cand_scores, cand_idx);
-    LSC_CUDA(cudaGetLastError());
-    return 1;
+    return rows_launch<1>(tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, grid, cand_scores, cand_idx, stream);
+}
+
+// Up to 256 queries [q_row0, q_row0 + nq) per pass on CTA pairs; the query matrix behind tmapQ must have rows up
+// to q_row0 + 256 (zeros past the batch) or end before them (TMA fills with zeros).  Candidates are written as
+// two query blocks: cand + (qb * grid + cta) * 128 * k for qb = 0, 1.
+int topk_scan_rows_pair_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows,
+                               int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream) {
+    if (grid < 2 || grid % 2 != 0) return fail(LSC_E_INVALID, "top-k (row-major, pairs): grid must be even");
+    return rows_launch<2>(tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, grid, cand_scores, cand_idx, stream);
 }
 
 }  // namespace lsc

@@ -51,7 +51,9 @@ def test_golden_small_corpus(native_lib, cuda_device):
 
 @pytest.mark.parametrize("n,B,k", [(1, 1, 1), (5, 3, 10), (255, 1, 10), (256, 2, 10), (257, 64, 10),
                                    (40000, 1, 10), (40000, 64, 20), (100003, 130, 10), (30000, 300, 32),
-                                   (5000, 7, 128)])
+                                   (5000, 7, 128),
+                                   # more than one query block, k <= 16: the CTA-pair scan (256 queries per pass)
+                                   (300, 129, 10), (129, 256, 10), (100003, 257, 10), (5000, 512, 16), (70000, 1000, 10)])
 def test_search_matches_oracle(native_lib, cuda_device, n, B, k):
     from langstream_b200._native import Index
     from oracle import topk_oracle
