@@ -322,6 +322,36 @@ def run_cuda(args):
     varlen = {"value": world * N_SEQ * args.steps / (ms_var / 1000.0), "unit": "embeddings/s",
               "lengths": "UniformInt[16,128] packed", "tokens_per_step": Tv}
 
+    # config 3 of SURVEY.md 8(d), as an extra figure (not the headline): the base shape (12 layers, H = 768,
+    # 12 heads of 64, FFN 3072) at 512 tokens per sequence; one pass = 512 sequences (262,144 tokens, the
+    # pass size the host API cuts larger batches into), so 4096 x 512 is eight such passes per GPU.
+    base = None
+    if not args.no_base:
+        bspec = W.BERT_BASE
+        benc = Encoder(bspec, W.random_init(bspec, 0), device=local_rank)
+        b_n, b_s = 512, 512
+        b_ids, b_cu = W.synthetic_token_ids(b_n, b_s, seed=99 + rank)
+        db_ids, db_cu = torch.from_numpy(b_ids).to(dev), torch.from_numpy(b_cu).to(dev)
+        db_out = torch.empty(b_n, bspec.hidden, device=dev)
+        for _ in range(2):
+            benc.embed_dev(db_ids, db_cu, b_n, int(b_cu[-1]), b_s, db_out, stream)
+        barrier()
+        reps = 3
+        ev0.record()
+        for _ in range(reps):
+            benc.embed_dev(db_ids, db_cu, b_n, int(b_cu[-1]), b_s, db_out, stream)
+        ev1.record()
+        barrier()
+        ms_base = max_over_ranks(ev0.elapsed_time(ev1))
+        b_total, _ = flops_per_sequence(bspec, b_s)
+        base = {"value": world * b_n * reps / (ms_base / 1000.0), "unit": "embeddings/s",
+                "workload": "base shape 12L/768/12h/3072, 512 sequences x 512 tokens per pass",
+                "ms_per_pass": ms_base / reps,
+                "whole_pass_tflops": b_total * b_n * reps / (ms_base / 1000.0) / 1e12}
+        benc.close()
+        del db_ids, db_cu, db_out
+        torch.cuda.empty_cache()
+
     # e2e: the C-ABI host-buffer call, pinned host memory, copies inside the timed region
     h_ids = torch.from_numpy(ids).pin_memory()
     h_cu = torch.from_numpy(cu).pin_memory()
@@ -429,7 +459,7 @@ def run_cuda(args):
                        "parallelism": f"dp{world} (one replica per GPU, no collective)",
                        "l2": "per-step working set ~1.1 GB of activations >> 126 MB L2; no explicit flush"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
-            "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "topk": topk,
+            "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "base_512": base, "topk": topk,
         }
         emit(line)
     enc.close()
@@ -446,6 +476,7 @@ def main():
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
     ap.add_argument("--no-topk", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-base", action="store_true", help="skip the base-shape (config 3) extra figure")
     ap.add_argument("--topk-rows", type=int, default=TOPK_ROWS)
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
