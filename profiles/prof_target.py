@@ -1,7 +1,7 @@
 """Short workloads for ncu (kept tiny: ncu replays every kernel ~40x under --set full).
 
     python profiles/prof_target.py encoder   # 2 passes of MiniLM-L6 over 1024 x 128 tokens
-    python profiles/prof_target.py topk      # 10M x 384 corpus, B=1 and B=64 top-10, 2 searches each
+    python profiles/prof_target.py topk      # 10M x 384 corpus, B=1, 64 and 256 top-10, 2 searches each
 """
 import sys
 from pathlib import Path
@@ -35,7 +35,7 @@ else:
         m = min(chunk, n - o)
         v = torch.randn(m, 384, device=dev, generator=torch.Generator(device=dev).manual_seed(42 + o // chunk))
         ix.upsert_dev(np.arange(o, o + m, dtype=np.int64), v, m, st)
-    for B in (1, 64):
+    for B in (1, 64, 256):  # 256: the CTA-pair scan
         q = torch.randn(B, 384, device=dev, generator=torch.Generator(device=dev).manual_seed(43))
         oi = torch.empty(B, 10, dtype=torch.int64, device=dev)
         os_ = torch.empty(B, 10, dtype=torch.float32, device=dev)
