@@ -96,10 +96,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const int32_t* 
         tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), 512);
         tmem_relinquish();
     }
+    if (threadIdx.x == 0) pdl_launch_dependents();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // the QKV GEMM has finished
 
     auto item_len = [&](int item, int& t0) {
         const int seq = item / heads;
@@ -323,8 +325,18 @@ int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int
     const long long n_items = static_cast<long long>(heads) * n_seq;
     const int grid = static_cast<int>(n_items < num_sms ? n_items : num_sms);
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(AT_D));
-    attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, stream>>>(tm, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
-                                                             scale_log2e);
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(grid);
+    lc.blockDim = dim3(AT_THREADS);
+    lc.dynamicSmemBytes = AT_SMEM;
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // see pdl_wait() in ptx.cuh
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc_kernel, tm, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
+                                                             scale_log2e));
     LSC_CUDA(cudaGetLastError());
     return 1;
 }

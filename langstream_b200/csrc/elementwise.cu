@@ -9,6 +9,23 @@
 
 namespace lsc {
 
+// <<<>>> with the programmatic-stream-serialization attribute (the kernels call pdl_wait() first thing)
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = grid;
+    lc.blockDim = block;
+    lc.dynamicSmemBytes = 0;
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    return cudaLaunchKernelEx(&lc, kern, static_cast<KArgs>(args)...);
+}
+
+
 namespace {
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -27,6 +44,9 @@ embed_ln_kernel(const int32_t* __restrict__ token_ids, const int32_t* __restrict
                 __nv_bfloat16* __restrict__ out, int32_t* __restrict__ seq_of_token,
                 float* __restrict__ stats_out, int stats_p) {
     constexpr int H = 128 * VPL;
+    // programmatic dependent launch (ptx.cuh): x / its statistics may still be read by the previous pass
+    pdl_launch_dependents();
+    pdl_wait();
     const int lane = threadIdx.x & 31;
     const int t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (t >= T) return;
@@ -129,6 +149,8 @@ __global__ void pool_l2_kernel(const __nv_bfloat16* __restrict__ x, const int32_
                                int H, float* __restrict__ out, const float* __restrict__ stats, int stats_p,
                                const float* __restrict__ gamma, const float* __restrict__ beta, float eps) {
     __shared__ float red[32];
+    pdl_launch_dependents();
+    pdl_wait();  // the last feed-forward kernel has finished (programmatic dependent launch, ptx.cuh)
     const int s = blockIdx.x;
     const int t0 = __ldg(cu_seqlens + s), t1 = __ldg(cu_seqlens + s + 1);
     const int j = threadIdx.x;
@@ -226,12 +248,12 @@ int embed_ln_launch(const int32_t* token_ids, const int32_t* cu_seqlens, int n_s
     const int wpb = 8;
     const int grid = (T + wpb - 1) / wpb;
     switch (H) {
-        case 128: embed_ln_kernel<1><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
-        case 256: embed_ln_kernel<2><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
-        case 384: embed_ln_kernel<3><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
-        case 512: embed_ln_kernel<4><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
-        case 768: embed_ln_kernel<6><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
-        case 1024: embed_ln_kernel<8><<<grid, 256, 0, stream>>>(token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p); break;
+        case 128: LSC_CUDA(launch_pdl(embed_ln_kernel<1>, dim3(grid), dim3(256), stream, token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p)); break;
+        case 256: LSC_CUDA(launch_pdl(embed_ln_kernel<2>, dim3(grid), dim3(256), stream, token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p)); break;
+        case 384: LSC_CUDA(launch_pdl(embed_ln_kernel<3>, dim3(grid), dim3(256), stream, token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p)); break;
+        case 512: LSC_CUDA(launch_pdl(embed_ln_kernel<4>, dim3(grid), dim3(256), stream, token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p)); break;
+        case 768: LSC_CUDA(launch_pdl(embed_ln_kernel<6>, dim3(grid), dim3(256), stream, token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p)); break;
+        case 1024: LSC_CUDA(launch_pdl(embed_ln_kernel<8>, dim3(grid), dim3(256), stream, token_ids, cu_seqlens, n_seq, T, max_position, vocab, word, pos, type0, gamma, beta, eps, out, seq_of_token, stats_out, stats_p)); break;
         default: return fail(LSC_E_UNSUPPORTED, "hidden size must be one of 128,256,384,512,768,1024");
     }
     LSC_CUDA(cudaGetLastError());
@@ -261,7 +283,7 @@ int pool_l2_launch(const __nv_bfloat16* x, const int32_t* cu_seqlens, int n_seq,
                    cudaStream_t stream) {
     if (n_seq <= 0) return 0;
     if (H % 64 != 0 || H / 2 > 1024) return fail(LSC_E_UNSUPPORTED, "pool: bad hidden size");
-    pool_l2_kernel<<<n_seq, H / 2, 0, stream>>>(x, cu_seqlens, H, out, stats, stats_p, gamma, beta, eps);
+    LSC_CUDA(launch_pdl(pool_l2_kernel, dim3(n_seq), dim3(H / 2), stream, x, cu_seqlens, H, out, stats, stats_p, gamma, beta, eps));
     LSC_CUDA(cudaGetLastError());
     return 1;
 }

@@ -156,10 +156,12 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             tmem_relinquish();
         }
     }
+    if (threadIdx.x == 0) pdl_launch_dependents();
     tc_fence_before();
     if (PAIR == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // tmp / its statistics are complete; the parameter staging above overlapped the producer's tail
 
     // a tile = 128 * PAIR rows, one per CTA (pair); this CTA's rows are its rank's half
     const int num_tiles = (M + FF_BM * PAIR - 1) / (FF_BM * PAIR);
@@ -489,13 +491,15 @@ static int ffn_launch_impl(const CUtensorMap& tmapA, const CUtensorMap& tmapW1, 
     lc.blockDim = dim3(FF_THREADS);
     lc.dynamicSmemBytes = SMEM;
     lc.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = PAIR;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // see pdl_wait() in ptx.cuh
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = attr;
-    lc.numAttrs = 1;
+    lc.numAttrs = 2;
     LSC_CUDA(cudaLaunchKernelEx(&lc, kern, tmapA, tmapW1, tmapW2, tmapC, M, H, F, a));
     LSC_CUDA(cudaGetLastError());
     return 1;

@@ -116,10 +116,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             tmem_relinquish();
         }
     }
+    if (threadIdx.x == 0) pdl_launch_dependents();
     tc_fence_before();
     if (PAIR == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // the producer of A / residual / statistics has finished; everything above overlapped its tail
 
     // tiles are BM * PAIR rows x BN columns, one per CTA (pair); this CTA's rows are its rank's half
     const int m_tiles = (M + BM * PAIR - 1) / (BM * PAIR);
@@ -428,24 +430,26 @@ int launch_pair(const CUtensorMap& tmapA, const CUtensorMap& tmapW, const CUtens
     const int num_tiles = m_tiles * (N / BN);
     int grid = num_tiles * PAIR < num_sms ? num_tiles * PAIR : num_sms;
     grid -= grid % PAIR;
-    if (PAIR == 1) {
-        kern<<<grid, Epi<BN>::THREADS, cfg::SMEM_BYTES, stream>>>(tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln);
-    } else {
-        // CTA pairs: clusters of two CTAs, scheduled on the two SMs of a TPC
-        cudaLaunchConfig_t lc = {};
-        lc.gridDim = dim3(grid);
-        lc.blockDim = dim3(Epi<BN>::THREADS);
-        lc.dynamicSmemBytes = cfg::SMEM_BYTES;
-        lc.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = PAIR;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        lc.attrs = attr;
-        lc.numAttrs = 1;
-        LSC_CUDA(cudaLaunchKernelEx(&lc, kern, tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln));
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(grid);
+    lc.blockDim = dim3(Epi<BN>::THREADS);
+    lc.dynamicSmemBytes = cfg::SMEM_BYTES;
+    lc.stream = stream;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // see pdl_wait() in ptx.cuh
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+    if (PAIR == 2) {  // CTA pairs: clusters of two CTAs, scheduled on the two SMs of a TPC
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = PAIR;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
     }
+    lc.attrs = attr;
+    lc.numAttrs = na;
+    LSC_CUDA(cudaLaunchKernelEx(&lc, kern, tmapA, tmapW, tmapC, bias, residual, M, N, K, f16_from_col, ln));
     LSC_CUDA(cudaGetLastError());
     return 1;
 }

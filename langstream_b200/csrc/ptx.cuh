@@ -54,6 +54,16 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// ---- programmatic dependent launch ---------------------------------------------------------
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its predecessor in
+// the stream is still running (its CTAs become resident as the predecessor's CTAs exit): everything up to
+// pdl_wait() - barrier set-up, TMEM allocation, staging of constant parameters - overlaps the predecessor's
+// tail and the launch latency; pdl_wait() returns once the predecessor has completed and its writes are
+// visible.  pdl_launch_dependents() lets the NEXT kernel be scheduled as soon as every CTA of this one has
+// issued it (or exited).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- mbarrier ----------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
