@@ -252,6 +252,36 @@ int lsc_index_load(const char* path, int device, lsc_index** out);
  *  API/database/VectorDatabaseWriter.java:38). */
 void lsc_index_destroy(lsc_index* idx);
 
+/* ---- host tokenizer (feeds lsc_encoder_embed; no GPU work) -------------------------------- */
+
+typedef struct lsc_tokenizer lsc_tokenizer;
+
+/*
+ * Replaces: the tokenizer half of DJL's TextEmbeddingTranslator, i.e. ai.djl.huggingface.tokenizers.
+ * HuggingFaceTokenizer = the HuggingFace `tokenizers` BERT pipeline (BertNormalizer, BertPreTokenizer,
+ * WordPiece, "[CLS] A [SEP]"), installed by TextEmbeddingTranslatorFactory at
+ * AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:20,155 and run
+ * inside predictor.predict (:194-196) one text at a time.
+ * vocab_txt / nbytes: the contents of the model's vocab.txt (one token per line, id = line number; must
+ * contain [UNK], [CLS], [SEP]).  do_lower_case also strips accents, as the library does when strip_accents
+ * is unset.  max_length: sequences are truncated to it, specials included (the model's max positions).
+ * n_threads <= 0: one per hardware thread.
+ */
+int lsc_tokenizer_create(const char* vocab_txt, size_t nbytes, int do_lower_case, int32_t max_length,
+                         int32_t n_threads, lsc_tokenizer** out);
+
+/*
+ * Tokenise n_texts UTF-8 texts (text_nbytes[i] bytes each, or NUL-terminated when text_nbytes is NULL) on
+ * the handle's threads and write them packed: token_ids[cu_seqlens[i] .. cu_seqlens[i+1]) are the ids of
+ * text i, cu_seqlens has n_texts + 1 entries - the layout lsc_encoder_embed takes.  capacity = room in
+ * token_ids (n_texts * max_length always suffices).  Thread-safe: the handle is read-only after creation.
+ */
+int lsc_tokenizer_encode(lsc_tokenizer* tok, const char* const* texts, const int32_t* text_nbytes,
+                         int32_t n_texts, int32_t* token_ids, int64_t capacity, int32_t* cu_seqlens);
+
+int32_t lsc_tokenizer_vocab_size(const lsc_tokenizer* tok);
+void lsc_tokenizer_destroy(lsc_tokenizer* tok);
+
 /* ---- re-rank (the step after query-vector-db in the reference's chatbot pipeline) --------- */
 
 /*

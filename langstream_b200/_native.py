@@ -77,6 +77,10 @@ SIGNATURES = {
     "lsc_index_save": (C.c_int, [_vp, C.c_char_p]),
     "lsc_index_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(_vp)]),
     "lsc_index_destroy": (None, [_vp]),
+    "lsc_tokenizer_create": (C.c_int, [C.c_char_p, C.c_size_t, C.c_int, _i32, _i32, C.POINTER(_vp)]),
+    "lsc_tokenizer_encode": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _i64, _vp]),
+    "lsc_tokenizer_vocab_size": (_i32, [_vp]),
+    "lsc_tokenizer_destroy": (None, [_vp]),
     "lsc_rerank_mmr": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
     "lsc_rerank_mmr_dev": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp, _vp]),
     "lsc_debug_attention_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
@@ -313,3 +317,54 @@ def rerank_mmr(doc_vecs, term_freq, doc_len, max_docs: int, lam: float, k1: floa
     check(lib().lsc_rerank_mmr(_ptr(doc_vecs), n, dim, _ptr(term_freq), _ptr(doc_len), t, int(max_docs),
                                float(lam), float(k1), float(b), _ptr(order), _ptr(count)))
     return [int(i) for i in order[: int(count[0])]]
+
+
+class WordPieceTokenizer:
+    """lsc_tokenizer_*: the BERT WordPiece pipeline of the HuggingFace `tokenizers` library (what DJL's
+    HuggingFaceTokenizer runs in the reference), multi-threaded, output packed for Encoder.embed."""
+
+    def __init__(self, vocab_txt, do_lower_case: bool = True, max_length: int = 512, n_threads: int = 0):
+        if isinstance(vocab_txt, str):
+            vocab_txt = vocab_txt.encode("utf-8")
+        h = _vp()
+        check(lib().lsc_tokenizer_create(vocab_txt, len(vocab_txt), int(do_lower_case), int(max_length), int(n_threads),
+                                         C.byref(h)))
+        self._h = h
+        self.max_length = int(max_length)
+
+    @classmethod
+    def from_file(cls, path, **kw):
+        with open(path, "rb") as f:
+            return cls(f.read(), **kw)
+
+    @property
+    def vocab_size(self) -> int:
+        return int(lib().lsc_tokenizer_vocab_size(self._h))
+
+    def encode_packed(self, texts):
+        """-> (token_ids int32 [total], cu_seqlens int32 [n + 1])"""
+        raw = [t.encode("utf-8") if isinstance(t, str) else bytes(t) for t in texts]
+        n = len(raw)
+        ptrs = (C.c_char_p * max(n, 1))(*raw)
+        lens = _np.asarray([len(r) for r in raw], _np.int32)
+        ids = _np.empty(max(n * self.max_length, 1), _np.int32)
+        cu = _np.zeros(n + 1, _np.int32)
+        check(lib().lsc_tokenizer_encode(self._h, C.cast(ptrs, _vp), _ptr(lens) if n else None, n, _ptr(ids),
+                                         int(ids.size), _ptr(cu)))
+        return ids[: int(cu[-1])].copy(), cu
+
+    def __call__(self, texts):
+        """The Tokenizer protocol of embeddings.py: a list of id lists."""
+        ids, cu = self.encode_packed(texts)
+        return [ids[cu[i]: cu[i + 1]].tolist() for i in range(len(cu) - 1)]
+
+    def close(self):
+        if self._h:
+            lib().lsc_tokenizer_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass

@@ -35,7 +35,7 @@ def _nvcc() -> str:
 
 
 def _newest_header() -> float:
-    hdrs = list(CSRC.glob("*.h")) + list(CSRC.glob("*.cuh")) + [ROOT.parent / "include" / "langstream_cuda.h"]
+    hdrs = list(CSRC.glob("*.h")) + list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inc")) + [ROOT.parent / "include" / "langstream_cuda.h"]
     return max(h.stat().st_mtime for h in hdrs)
 
 

@@ -186,7 +186,11 @@ class CudaServiceProvider:
     def get_embeddings_service(self, additional_configuration: dict) -> EmbeddingsService:
         """Step keys as in HuggingFaceProvider.getEmbeddingsService (HuggingFaceProvider.java:82-139):
         `model` names the architecture, `model-url` (file://…npy) points at a weight blob;
-        `options.random-init-seed` builds HuggingFace-default random weights instead (benchmarks)."""
+        `options.random-init-seed` builds HuggingFace-default random weights instead (benchmarks).
+        `options.vocab-file` (the model's vocab.txt) selects the native WordPiece tokenizer
+        (lsc_tokenizer_*: the BERT pipeline of the HuggingFace tokenizers library, multi-threaded), with
+        `options.do-lower-case` (default true) and `options.tokenizer-threads` (default: all cores); without it the
+        hashing stand-in is used (synthetic data)."""
         cfg = dict(additional_configuration or {})
         model = cfg.get("model")
         if not model or model not in KNOWN_ARCHITECTURES:
@@ -200,8 +204,15 @@ class CudaServiceProvider:
             blob = np.load(str(url)[len("file://"):]).astype(np.float32)
         else:
             blob = random_init(spec, seed=int(options.get("random-init-seed", 0)))
+        tokenizer = None
+        if options.get("vocab-file"):
+            tokenizer = _native.WordPieceTokenizer.from_file(
+                str(options["vocab-file"]), do_lower_case=bool(options.get("do-lower-case", True)),
+                max_length=spec.max_position, n_threads=int(options.get("tokenizer-threads", 0)))
+            if tokenizer.vocab_size > spec.vocab:
+                raise ValueError(f"vocab-file has {tokenizer.vocab_size} tokens, the model {spec.vocab}")
         svc = CudaEmbeddingsService(
-            spec, blob, device=int(self.provider_configuration.get("device", 0)),
+            spec, blob, tokenizer=tokenizer, device=int(self.provider_configuration.get("device", 0)),
             max_batch=int(cfg.get("batch-size", 1024)),
             flush_interval_ms=float(cfg.get("flush-interval", 2)),
         )

@@ -123,3 +123,32 @@ def test_gpu_resident_sink_and_persistence(native_lib, cuda_device, tmp_path):
     assert [ds.fetch_data(sql, [emb[p].tolist()]) for p in (3, 70)] == before
     assert a.delete_asset_if_exists() and not CudaVectorTable.exists_on_disk(tmp_path, "chunks")
     enc.close()
+
+
+def test_embeddings_service_with_native_tokenizer(native_lib, cuda_device, tmp_path):
+    """texts -> lsc_tokenizer_encode -> lsc_encoder_embed: the service with `options.vocab-file`; the vectors
+    equal the oracle's on the ids the HuggingFace tokenizer produces for the same texts."""
+    import sys
+    sys.path.insert(0, str(Path(__file__).parent))
+    import tokenizer_corpus as tc
+    transformers = pytest.importorskip("transformers")
+    from langstream_b200 import weights as W
+    from langstream_b200.embeddings import CudaServiceProviderProvider
+    from oracle.encoder_oracle import bert_numpy
+
+    vp = tmp_path / "vocab.txt"
+    vp.write_text(tc.vocab_text(), encoding="utf-8")
+    provider = CudaServiceProviderProvider().create_implementation({"cuda": {"device": 0}})
+    svc = provider.get_embeddings_service({"model": "all-MiniLM-L6-v2", "batch-size": 64, "flush-interval": 5,
+                                           "options": {"random-init-seed": 0, "vocab-file": str(vp)}})
+    texts = ["Hello, World!", "unable unablely the vector data base", tc.FIXED_TEXTS[4], "something to embed"]
+    got = np.asarray(svc.compute_embeddings(texts).result(timeout=60))
+    hf = transformers.BertTokenizer(str(vp), do_lower_case=True)
+    ids = hf(texts)["input_ids"]
+    spec = W.MINILM_L6
+    blob = W.random_init(spec, 0)
+    for i, seq in enumerate(ids):
+        ref = bert_numpy(spec, blob, np.asarray(seq, np.int32), np.asarray([0, len(seq)], np.int32))[0]
+        cos = float(np.dot(got[i], ref) / (np.linalg.norm(got[i]) * np.linalg.norm(ref)))
+        assert cos >= 0.999 and np.abs(got[i] - ref).max() <= 2e-3
+    provider.close()
