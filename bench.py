@@ -371,6 +371,37 @@ def run_cuda(args):
            "d2h_bytes_per_step": int(h_out_np.nbytes),
            "api": "lsc_encoder_embed (host token ids -> host fp32 embeddings)"}
 
+    # from texts: lsc_tokenizer_encode (native WordPiece, all host threads) + lsc_encoder_embed, per step 1024
+    # synthetic texts of 126 pseudo-words (= 128 tokens with [CLS] / [SEP]); extra figure, not the headline
+    text_e2e = None
+    try:
+        from langstream_b200._native import WordPieceTokenizer
+        words = [f"w{i}" for i in range(spec.vocab - 5)]
+        tok = WordPieceTokenizer("\n".join(["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words) + "\n",
+                                 max_length=SEQ_LEN, n_threads=0)
+        trng = np.random.default_rng(77 + rank)
+        texts = [" ".join(words[j] for j in trng.integers(0, len(words), SEQ_LEN - 2)) for _ in range(N_SEQ)]
+        t_ids, t_cu = tok.encode_packed(texts)
+        assert int(t_cu[-1]) == N_SEQ * SEQ_LEN
+        reps = max(3, min(args.steps, 10))
+        enc.embed(t_ids, t_cu, out=h_out_np)
+        barrier()
+        t0 = time.perf_counter()
+        tok_s = 0.0
+        for _ in range(reps):
+            a0 = time.perf_counter()
+            t_ids, t_cu = tok.encode_packed(texts)
+            tok_s += time.perf_counter() - a0
+            enc.embed(t_ids, t_cu, out=h_out_np)
+        torch.cuda.synchronize()
+        text_ms = max_over_ranks((time.perf_counter() - t0) * 1000.0)
+        text_e2e = {"value": world * N_SEQ * reps / (text_ms / 1000.0), "unit": "embeddings/s",
+                    "api": "lsc_tokenizer_encode + lsc_encoder_embed (host texts -> host fp32 embeddings), serial",
+                    "tokenizer_texts_per_s": N_SEQ * reps / tok_s, "tokenizer_threads": os.cpu_count()}
+        tok.close()
+    except Exception as e:  # noqa: BLE001 - an extra figure must not take the benchmark down
+        text_e2e = {"error": str(e)}
+
     # ---- top-k over a 10M x 384 corpus, row-sharded across ranks -------------------------------
     topk = None
     if not args.no_topk:
@@ -459,7 +490,7 @@ def run_cuda(args):
                        "parallelism": f"dp{world} (one replica per GPU, no collective)",
                        "l2": "per-step working set ~1.1 GB of activations >> 126 MB L2; no explicit flush"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
-            "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "base_512": base, "topk": topk,
+            "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "base_512": base, "text_e2e": text_e2e, "topk": topk,
         }
         emit(line)
     enc.close()
