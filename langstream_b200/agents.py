@@ -1,0 +1,372 @@
+"""Host-side mirrors of the callers on either side of the hot path:
+
+* `OrderedAsyncBatchExecutor`  - langstream-api/src/main/java/ai/langstream/api/util/OrderedAsyncBatchExecutor.java:39-177
+* `ComputeAIEmbeddingsStep`    - langstream-agents/langstream-ai-agents/src/main/java/com/datastax/oss/streaming/ai/
+                                 ComputeAIEmbeddingsStep.java:67-249 (`compute-ai-embeddings`)
+* `QueryStep`                  - .../ai/QueryStep.java:86-198 (`query-vector-db` / `query`)
+
+They keep the reference's configuration keys, ordering guarantees and error behaviour, and call the services of
+embeddings.py / vector.py (i.e. the C ABI) where the reference calls DJL / JDBC.  Records are the plain `Record`
+of vector.py (key, value, headers) with dict or JSON-text values.
+"""
+from __future__ import annotations
+
+import json
+import random
+import re
+import threading
+from concurrent.futures import Future
+from typing import Any, Callable, Dict, Generic, List, Optional, TypeVar
+
+from .vector import Record, evaluate
+
+T = TypeVar("T")
+
+
+class OrderedAsyncBatchExecutor(Generic[T]):
+    """Hash-bucketed batching with per-bucket ordering: items of a bucket are processed in arrival order, one
+    batch in flight per bucket; a batch is cut when `batch_size` items are waiting, on every add when
+    `flush_interval_ms <= 0` (OrderedAsyncBatchExecutor.java:113-118), or by the timer."""
+
+    class _Bucket:
+        def __init__(self, outer: "OrderedAsyncBatchExecutor"):
+            self.outer = outer
+            self.lock = threading.RLock()
+            self.pending: List[List[Any]] = []
+            self.current: List[Any] = []
+            self.processing = False
+
+        def add(self, item) -> None:
+            with self.lock:
+                self.current.append(item)
+                if len(self.current) >= self.outer.batch_size or self.outer.flush_interval_ms <= 0:
+                    self.schedule_current()
+
+        def schedule_current(self) -> None:
+            with self.lock:
+                if not self.current:
+                    return
+                batch, self.current = self.current, []
+                if not self.processing:
+                    self._execute(batch)
+                else:
+                    self.pending.append(batch)
+
+        def _execute(self, batch) -> None:
+            handle: Future = Future()
+            self.processing = True
+
+            def done(_):
+                with self.lock:
+                    self.processing = False
+                    if self.pending:
+                        self._execute(self.pending.pop(0))
+
+            handle.add_done_callback(done)
+            self.outer.processor(batch, handle)
+
+    def __init__(self, batch_size: int, processor: Callable[[List[T], Future], None], flush_interval_ms: float,
+                 num_buckets: int, hash_function: Callable[[T], int]):
+        self.batch_size = int(batch_size)
+        self.processor = processor
+        self.flush_interval_ms = float(flush_interval_ms)
+        self.num_buckets = max(1, int(num_buckets))
+        self.hash_function = hash_function
+        self._buckets = [self._Bucket(self) for _ in range(self.num_buckets)]
+        self._timer: Optional[threading.Timer] = None
+        self._stopped = False
+
+    def start(self) -> None:
+        if self.flush_interval_ms > 0:
+            self._arm()
+
+    def _arm(self) -> None:
+        if self._stopped:
+            return
+        self._timer = threading.Timer(self.flush_interval_ms / 1000.0, self._tick)
+        self._timer.daemon = True
+        self._timer.start()
+
+    def _tick(self) -> None:
+        self.flush()
+        self._arm()
+
+    def stop(self) -> None:
+        self._stopped = True
+        if self._timer is not None:
+            self._timer.cancel()
+        self.flush()
+
+    def flush(self) -> None:
+        for b in self._buckets:
+            b.schedule_current()
+
+    def add(self, item: T) -> None:
+        if self.num_buckets == 1:
+            bucket = self._buckets[0]
+        else:
+            h = int(self.hash_function(item))
+            # Java: Math.abs(hash % numBuckets) with a remainder that takes the sign of the dividend
+            r = abs(h) % self.num_buckets
+            bucket = self._buckets[r]
+        bucket.add(item)
+
+
+_MUSTACHE = re.compile(r"\{\{\{?\s*([^{}]+?)\s*\}?\}\}")
+
+
+def render_template(template: str, context: Dict[str, Any]) -> str:
+    """The subset of Mustache the embeddings step's `text` uses: `{{ value.a.b }}`, `{{ key.x }}`, `{{ record.f }}`,
+    `{{ properties.p }}`; a missing value renders as the empty string."""
+
+    def lookup(m):
+        cur: Any = context
+        for part in m.group(1).split("."):
+            if isinstance(cur, (str, bytes)):
+                try:
+                    cur = json.loads(cur)
+                except ValueError:
+                    return ""
+            cur = cur.get(part) if isinstance(cur, dict) else None
+            if cur is None:
+                return ""
+        return cur if isinstance(cur, str) else json.dumps(cur) if isinstance(cur, (dict, list)) else str(cur)
+
+    return _MUSTACHE.sub(lookup, template)
+
+
+def _as_obj(value):
+    if isinstance(value, (str, bytes)):
+        try:
+            return json.loads(value)
+        except ValueError:
+            return value
+    return value
+
+
+def set_result_field(record: Record, field_name: str, result) -> None:
+    """MutableRecord.setResultField for `value`, `value.x[.y]`, `key`, `key.x`, `properties.x`; a JSON-text
+    value stays JSON text."""
+    parts = field_name.split(".")
+    root = parts[0]
+    if root == "properties":
+        record.headers[".".join(parts[1:])] = result
+        return
+    if root not in ("value", "key"):
+        raise ValueError(f"Invalid fieldName: {field_name}")
+    cur = getattr(record, root)
+    if len(parts) == 1:
+        setattr(record, root, result)
+        return
+    was_text = isinstance(cur, (str, bytes))
+    obj = _as_obj(cur) if cur is not None else {}
+    if not isinstance(obj, dict):
+        raise ValueError(f"cannot set {field_name} on a non-structured {root}")
+    node = obj
+    for p in parts[1:-1]:
+        node = node.setdefault(p, {})
+    node[parts[-1]] = result
+    setattr(record, root, json.dumps(obj) if was_text else obj)
+
+
+class ComputeAIEmbeddingsStep:
+    """`compute-ai-embeddings`: render `text` per record (or per item of `loop-over`), one service call per
+    batch, result i written to record i as a list of doubles.  The whole batch fails together
+    (ComputeAIEmbeddingsStep.java:194-202, 225-229).  `process_async(record)` returns a future that completes
+    when the record carries its embeddings; the record is mutated in place, like MutableRecord."""
+
+    def __init__(self, text: str, embeddings_field_name: str, loop_over: Optional[str], batch_size: int,
+                 flush_interval_ms: float, concurrency: int, embeddings_service):
+        self.template = text
+        self.embeddings_field_name = embeddings_field_name
+        self.loop_over = loop_over or None
+        self.field_in_record: Optional[str] = None
+        if self.loop_over:
+            if not embeddings_field_name.startswith("record."):
+                raise ValueError("With loop-over the embeddings field but be something like record.xxx")
+            self.field_in_record = embeddings_field_name[7:]
+            if "." in self.field_in_record:
+                raise ValueError("With loop-over the embeddings field but be something like record.xxx,"
+                                 "it cannot be record.xxx.yyy")
+        self.embeddings_service = embeddings_service
+        self._rng = random.Random()
+        self.batch_executor: OrderedAsyncBatchExecutor = OrderedAsyncBatchExecutor(
+            batch_size, self._process_batch, flush_interval_ms, concurrency if concurrency > 0 else 1, self._hash)
+
+    @classmethod
+    def from_config(cls, config: Dict[str, Any], embeddings_service) -> "ComputeAIEmbeddingsStep":
+        """Step keys and defaults of ComputeAIEmbeddingsConfig (…/model/config/ComputeAIEmbeddingsConfig.java:27-52)."""
+        return cls(text=str(config["text"]), embeddings_field_name=str(config["embeddings-field"]),
+                   loop_over=config.get("loop-over"), batch_size=int(config.get("batch-size", 10)),
+                   flush_interval_ms=float(config.get("flush-interval", 0)), concurrency=int(config.get("concurrency", 4)),
+                   embeddings_service=embeddings_service)
+
+    def _hash(self, holder) -> int:
+        key = holder[0].key
+        if key is not None:
+            try:
+                return hash(json.dumps(key, sort_keys=True)) if isinstance(key, (dict, list)) else hash(key)
+            except TypeError:
+                return hash(str(key))
+        return self._rng.getrandbits(31)
+
+    def start(self) -> None:
+        self.batch_executor.start()
+
+    def process_async(self, record: Record) -> Future:
+        handle: Future = Future()
+        self.batch_executor.add((record, handle))
+        return handle
+
+    def process(self, record: Record, timeout: Optional[float] = 60) -> None:
+        fut = self.process_async(record)
+        self.batch_executor.flush()
+        fut.result(timeout)
+
+    def _process_batch(self, holders, completion: Future) -> None:
+        texts: List[str] = []
+        completions: List[Callable[[List[float]], None]] = []
+        try:
+            for record, handle in holders:
+                if self.loop_over is None:
+                    ctx = {"value": _as_obj(record.value), "key": _as_obj(record.key), "properties": record.headers}
+                    texts.append(render_template(self.template, ctx))
+
+                    def done(emb, record=record, handle=handle):
+                        set_result_field(record, self.embeddings_field_name, emb)
+                        handle.set_result(None)
+
+                    completions.append(done)
+                else:
+                    work = Record(key=record.key, value=_as_obj(record.value), headers=record.headers)
+                    nested = evaluate(self.loop_over, work)
+                    new_list = [dict(d) for d in nested]
+                    remaining = [len(new_list)]
+                    lock = threading.Lock()
+                    if not new_list:  # nothing to embed: the reference never completes such a record; complete it
+                        handle.set_result(None)
+                    for doc, new_map in zip(nested, new_list):
+                        texts.append(render_template(self.template, {"record": doc}))
+
+                        def done(emb, new_map=new_map, new_list=new_list, remaining=remaining, lock=lock, record=record,
+                                 handle=handle):
+                            new_map[self.field_in_record] = emb
+                            with lock:
+                                remaining[0] -= 1
+                                last = remaining[0] == 0
+                            if last:
+                                set_result_field(record, self.loop_over, new_list)
+                                handle.set_result(None)
+
+                        completions.append(done)
+        except Exception as error:  # noqa: BLE001 - we cannot fail only some records, because we must keep the order
+            self._error_for_all(holders, error)
+            completion.set_result(None)
+            return
+
+        def on_result(fut: Future):
+            try:
+                result = fut.result()
+                for done, emb in zip(completions, result):
+                    done(emb)
+            except Exception as error:  # noqa: BLE001
+                self._error_for_all(holders, error)
+            completion.set_result(None)
+
+        self.embeddings_service.compute_embeddings(texts).add_done_callback(on_result)
+
+    @staticmethod
+    def _error_for_all(holders, error) -> None:
+        for _, handle in holders:
+            if not handle.done():
+                handle.set_exception(error)
+
+    def close(self) -> None:
+        self.batch_executor.stop()
+        if self.embeddings_service is not None:
+            self.embeddings_service.close()
+
+
+class QueryStep:
+    """`query` / `query-vector-db` (QueryStep.java:86-198): evaluate `fields` into positional parameters, fetch, store
+    the list of row maps (or the first row with `only-first`) in `output-field`; `loop-over` runs one query per
+    item (the item is `record`) and concatenates the results; mode "execute" calls executeStatement."""
+
+    MODE_QUERY, MODE_EXECUTE = "query", "execute"
+
+    def __init__(self, data_source, query: str, fields: Optional[List[str]], output_field: str, only_first: bool = False,
+                 loop_over: Optional[str] = None, generated_keys: Optional[List[str]] = None, mode: Optional[str] = None):
+        self.data_source, self.query = data_source, query
+        self.fields = list(fields or [])
+        self.output_field, self.only_first = output_field, bool(only_first)
+        self.loop_over = loop_over or None
+        self.generated_keys = list(generated_keys or [])
+        self.mode = mode or self.MODE_QUERY
+
+    @classmethod
+    def from_config(cls, config: Dict[str, Any], data_source) -> "QueryStep":
+        return cls(data_source, str(config["query"]), config.get("fields"), str(config["output-field"]),
+                   bool(config.get("only-first", False)), config.get("loop-over"), config.get("generated-keys"),
+                   config.get("mode"))
+
+    def process(self, record: Record) -> None:
+        work = Record(key=_as_obj(record.key), value=_as_obj(record.value), headers=record.headers)
+        if self.mode == self.MODE_QUERY:
+            results = self._for_each(work, self._perform_query, flatten=True)
+            final = (results[0] if results else {}) if self.only_first else results
+        elif self.mode == self.MODE_EXECUTE:
+            final = self._for_each(work, self._execute, flatten=False) if self.loop_over else self._execute(work)
+        else:
+            raise RuntimeError(f"Unknown mode {self.mode}")
+        set_result_field(record, self.output_field, final)
+
+    def _for_each(self, work: Record, fn, flatten: bool):
+        if self.loop_over is None:
+            return fn(work)
+        nested = evaluate(self.loop_over, work) or []
+        out = []
+        for doc in nested:
+            r = fn(Record(value=doc))
+            if flatten:
+                out.extend(r)
+            else:
+                out.append(r)
+        return out
+
+    def _params(self, ctx: Record) -> List[Any]:
+        return [evaluate(f, ctx) for f in self.fields]
+
+    def _perform_query(self, ctx: Record) -> List[Dict[str, Any]]:
+        return self.data_source.fetch_data(self.query, self._params(ctx)) or []
+
+    def _execute(self, ctx: Record) -> Dict[str, Any]:
+        return self.data_source.execute_statement(self.query, self.generated_keys, self._params(ctx))
+
+
+class QueryVectorDBAgent:
+    """`query-vector-db` agent (VEC/QueryVectorDBAgent.java:50-79): resolve the datasource through the provider
+    registry, build a QueryStep, run it synchronously per record; exactly one output record per input record."""
+
+    def __init__(self, providers=None):
+        from .vector import CudaVectorDataSourceProvider
+        self.providers = list(providers) if providers is not None else [CudaVectorDataSourceProvider()]
+        self.step: Optional[QueryStep] = None
+        self.data_source = None
+
+    def init(self, configuration: Dict[str, Any]) -> None:
+        ds_config = dict(configuration.get("datasource") or {})
+        provider = next((p for p in self.providers if p.supports(ds_config)), None)
+        if provider is None:  # DataSourceProviderRegistry.java:27-45
+            raise ValueError(f"No DataSource found for resource {ds_config}")
+        self.data_source = provider.create_data_source_implementation(ds_config)
+        self.data_source.initialize(ds_config)
+        self.step = QueryStep.from_config(configuration, self.data_source)
+
+    def process_record(self, record: Record) -> List[Record]:
+        out = Record(key=record.key, value=record.value, headers=dict(record.headers))
+        self.step.process(out)
+        return [out]
+
+    def close(self) -> None:
+        if self.data_source is not None:
+            self.data_source.close()

@@ -152,3 +152,57 @@ def test_embeddings_service_with_native_tokenizer(native_lib, cuda_device, tmp_p
         cos = float(np.dot(got[i], ref) / (np.linalg.norm(got[i]) * np.linalg.norm(ref)))
         assert cos >= 0.999 and np.abs(got[i] - ref).max() <= 2e-3
     provider.close()
+
+
+def test_chatbot_flow_through_the_agent_mirrors(native_lib, cuda_device):
+    """The reference's docker-chatbot pipeline shape on the CUDA path end to end: compute-ai-embeddings (step with
+    batching) -> vector-db-sink -> query-vector-db -> re-rank, every stage through the agent mirrors."""
+    from langstream_b200 import vector
+    from langstream_b200.agents import ComputeAIEmbeddingsStep, QueryVectorDBAgent
+    from langstream_b200.embeddings import CudaServiceProviderProvider
+    from langstream_b200.rerank import CudaReRankAgent
+    from langstream_b200.vector import CudaVectorDatabaseWriter, Record
+
+    vector.drop_table("chunks2")
+    provider = CudaServiceProviderProvider().create_implementation({"cuda": {"device": 0}})
+    svc = provider.get_embeddings_service({"model": "all-MiniLM-L6-v2", "options": {"random-init-seed": 0},
+                                           "batch-size": 64, "flush-interval": 5})
+    step = ComputeAIEmbeddingsStep.from_config({"text": "{{ value.text }}", "embeddings-field": "value.embeddings_vector",
+                                                "batch-size": 16, "flush-interval": 10, "concurrency": 2}, svc)
+    step.start()
+    topics = ["stream", "vector", "kafka", "pulsar", "gpu", "tensor", "index", "query", "agent", "record"]
+    docs = [Record(key=f"doc{i}", value={"filename": f"doc{i}.pdf", "chunk_id": i,
+                                         "text": f"{topics[i % 10]} chunk number {i} about {topics[(i * 3) % 10]} things"})
+            for i in range(40)]
+    futs = [step.process_async(r) for r in docs]
+    for f in futs:
+        f.result(60)
+    assert all(len(r.value["embeddings_vector"]) == 384 for r in docs)
+    w = CudaVectorDatabaseWriter({"service": "cuda", "device": 0})
+    w.initialise({"table-name": "chunks2", "fields": [
+        {"name": "filename", "expression": "value.filename", "primary-key": True},
+        {"name": "chunk_id", "expression": "value.chunk_id", "primary-key": True},
+        {"name": "embeddings_vector", "expression": "fn:toListOfFloat(value.embeddings_vector)"},
+        {"name": "text", "expression": "value.text"}]})
+    assert w.upsert_batch(docs).result(30) is None
+    # a question identical to one chunk's text: that chunk must come back first, and survive the re-rank
+    question = Record(key="q", value={"question": docs[17].value["text"]})
+    qstep = ComputeAIEmbeddingsStep("{{ value.question }}", "value.question_embeddings", None, 1, 0, 1, svc)
+    qstep.process(question)
+    agent = QueryVectorDBAgent()
+    agent.init({"datasource": {"service": "cuda"},
+                "query": "SELECT text,embeddings_vector FROM chunks2 ORDER BY cosine_similarity(embeddings_vector, CAST(? AS FLOAT ARRAY)) DESC LIMIT 20",
+                "fields": ["value.question_embeddings"], "output-field": "value.related_documents"})
+    out = agent.process_record(question)[0]
+    related = out.value["related_documents"]
+    assert len(related) == 20 and related[0]["text"] == docs[17].value["text"]
+    rr = CudaReRankAgent()
+    rr.init({"max": 5, "field": "value.related_documents", "query-text": "value.question",
+             "query-embeddings": "value.question_embeddings", "output-field": "value.related_documents",
+             "text-field": "record.text", "embeddings-field": "record.embeddings_vector", "algorithm": "MMR"})
+    final = rr.process_record(out)[0].value["related_documents"]
+    assert len(final) == 5 and final[0]["text"] == docs[17].value["text"]
+    step.batch_executor.stop()
+    qstep.batch_executor.stop()
+    provider.close()
+    vector.drop_table("chunks2")
