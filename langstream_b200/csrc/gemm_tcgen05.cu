@@ -248,17 +248,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 if (acc == 0) acc_phase ^= 1;
                 continue;
             }
-            // per-column vectors of this warp's columns -> its shared-memory cache (the previous tile's reads
-            // of the cache are over: every lane is past its last chunk)
-            __syncwarp();
+            // Tile set-up: every global load of the set-up is issued before any of them is used, so the warp
+            // pays one memory latency per tile, not one per dependent step (the epilogue bounds these kernels;
+            // a loop "load partial, add" over the row statistics alone cost p_in round trips).
+            //  (1) the row's statistic partials, (2) the per-column vectors of this warp's columns,
+            //  (3) the residual rows of chunk 0.
+            constexpr int MAXP = 12;  // statistic partials per row loaded up front (12 = H 768 at BN 192); more: tail loop
+            constexpr bool kStats = kLnIn || EPI == EPI_RES_LN;
+            float2 spart[MAXP];
+            if (kStats) {
+                const float2* sp = reinterpret_cast<const float2*>(ln.stats_in) + static_cast<size_t>(row_ok ? grow : 0) * ln.p_in;
 #pragma unroll
-            for (int k = lane; k < COLS; k += 32) {
-                sts_f32(prm + 4 * k, __ldg(bias + col_base + k));
-                if (kLnIn) sts_f32(prm + 4 * (COLS + k), __ldg(ln.c + col_base + k));
-                if (EPI == EPI_RES_LN) {
-                    sts_f32(prm + 4 * (COLS + k), __ldg(ln.gamma + col_base + k));
-                    sts_f32(prm + 4 * (2 * COLS + k), __ldg(ln.beta + col_base + k));
-                }
+                for (int p = 0; p < MAXP; ++p) spart[p] = (row_ok && p < ln.p_in) ? __ldg(sp + p) : make_float2(0.f, 0.f);
+            }
+            constexpr int PPL = COLS / 32;  // columns per lane in the parameter cache
+            float pv0[PPL], pv1[PPL], pv2[PPL];
+#pragma unroll
+            for (int i = 0; i < PPL; ++i) {
+                const int k = lane + 32 * i;
+                pv0[i] = __ldg(bias + col_base + k);
+                pv1[i] = kLnIn ? __ldg(ln.c + col_base + k) : (EPI == EPI_RES_LN ? __ldg(ln.gamma + col_base + k) : 0.f);
+                pv2[i] = EPI == EPI_RES_LN ? __ldg(ln.beta + col_base + k) : 0.f;
             }
             const __nv_bfloat16* rrow = kRes ? residual + static_cast<size_t>(row_ok ? grow : 0) * N + col_base : nullptr;
             uint32_t res[16], res_next[16];
@@ -266,14 +276,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
                 ldg256(rrow, res_next);
                 ldg256(rrow + 16, res_next + 8);
             }
+            // per-column vectors -> the warp's shared-memory cache (the previous tile's reads of the cache are
+            // over: every lane is past its last chunk)
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < PPL; ++i) {
+                const int k = lane + 32 * i;
+                sts_f32(prm + 4 * k, pv0[i]);
+                if (kStats) sts_f32(prm + 4 * (COLS + k), pv1[i]);
+                if (EPI == EPI_RES_LN) sts_f32(prm + 4 * (2 * COLS + k), pv2[i]);
+            }
             // LayerNorm folding: row statistics of the tensor being normalised (the A operand for
             // kLnIn, the residual for EPI_RES_LN) from its per-row partial (sum, sum of squares).
             float rstd = 1.f, nm = 0.f;  // nm = -mean * rstd
-            if (kLnIn || EPI == EPI_RES_LN) {
+            if (kStats) {
                 float sum = 0.f, sq = 0.f;
+#pragma unroll
+                for (int p = 0; p < MAXP; ++p) {
+                    sum += spart[p].x;
+                    sq += spart[p].y;
+                }
                 if (row_ok) {
                     const float2* sp = reinterpret_cast<const float2*>(ln.stats_in) + static_cast<size_t>(grow) * ln.p_in;
-                    for (int p = 0; p < ln.p_in; ++p) {
+                    for (int p = MAXP; p < ln.p_in; ++p) {
                         const float2 t = __ldg(sp + p);
                         sum += t.x;
                         sq += t.y;
