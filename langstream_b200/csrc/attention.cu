@@ -464,6 +464,15 @@ int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_
         return attention_tc_launch(qkv, cu_seqlens, n_seq, T, H, heads, max_seqlen, ctx,
                                    (dev >= 0 && dev < 64) ? sms_cache[dev] : 148, stream);
     }
+    if (d == 64 && attention_tc64_supported(H, heads)) {  // tcgen05, any sequence length
+        static int sms_cache64[64] = {};
+        int dev = 0;
+        LSC_CUDA(cudaGetDevice(&dev));
+        if (dev >= 0 && dev < 64 && sms_cache64[dev] == 0)
+            LSC_CUDA(cudaDeviceGetAttribute(&sms_cache64[dev], cudaDevAttrMultiProcessorCount, dev));
+        return attention_tc64_launch(qkv, cu_seqlens, n_seq, T, H, heads, ctx, (dev >= 0 && dev < 64) ? sms_cache64[dev] : 148,
+                                     stream);
+    }
     if (d == 32) return launch_d<32>(qkv, cu_seqlens, n_seq, H, heads, max_seqlen, ctx, stream);
     if (d == 64) return launch_d<64>(qkv, cu_seqlens, n_seq, H, heads, max_seqlen, ctx, stream);
     return fail(LSC_E_UNSUPPORTED, "attention: head dimension must be 32 or 64");

@@ -158,6 +158,10 @@ int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream);
 int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                         int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
+// tcgen05 attention for d_head 64 and any sequence length (attention_tc64.cu).
+bool attention_tc64_supported(int H, int heads);
+int attention_tc64_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
+                          __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
 // Masked mean-pool over each sequence's tokens + L2 normalisation -> fp32 [n_seq,H].  With `stats`
 // (per-row partial sums, see LnArgs) x holds pre-LayerNorm rows and the final LayerNorm (gamma, beta)
 // is applied on the fly.
