@@ -30,6 +30,10 @@ def _reference(qkv, cu, H, heads):
     (768, 12, [512, 300, 64, 1, 257], 1.0),  # d_head 64, several key blocks with online rescaling
     (768, 12, [512, 511], 4.0),
     (128, 4, [40, 5], 1.0),
+    # d_head 64 on the tcgen05 kernel: more items than SMs, every residue of the 128-row / 64-key tiling, rounds
+    # with 1-4 active query tiles, sequences longer than 512 (two rounds of query tiles), empty sequences
+    (768, 12, [1, 63, 64, 65, 127, 128, 129, 191, 192, 193, 255, 256, 257, 383, 384, 385, 0, 511, 513, 640, 700], 1.0),
+    (256, 4, [33, 600, 2, 130], 3.0),
 ])
 def test_attention_matches_fp32_reference(native_lib, cuda_device, H, heads, lens, scale):
     import torch
