@@ -357,19 +357,37 @@ def run_cuda(args):
     h_cu = torch.from_numpy(cu).pin_memory()
     h_out = torch.empty(N_SEQ, spec.hidden).pin_memory()
     h_ids_np, h_cu_np, h_out_np = h_ids.numpy(), h_cu.numpy(), h_out.numpy()
+    # two batches in flight through lsc_encoder_submit / lsc_encoder_wait (the asynchronous form of the service
+    # contract): the upload of step i+1 and the download of step i-1 overlap the kernels of step i.  Every step
+    # uploads its ids from pinned host memory and its embeddings are in host memory when its wait returns.
+    h_out2 = torch.empty(N_SEQ, spec.hidden).pin_memory()
+    h_ids2, h_cu2 = h_ids.clone().pin_memory(), h_cu.clone().pin_memory()
+    bufs = [(h_ids_np, h_cu_np, h_out_np), (h_ids2.numpy(), h_cu2.numpy(), h_out2.numpy())]
     for _ in range(3):
         enc.embed(h_ids_np, h_cu_np, out=h_out_np)
+    barrier()
+    t0 = time.perf_counter()
+    pending = enc.submit(*bufs[0])
+    for i in range(1, args.steps):
+        nxt = enc.submit(*bufs[i & 1])
+        enc.wait(pending)  # step i-1 is complete in host memory
+        pending = nxt
+    enc.wait(pending)
+    e2e_s = time.perf_counter() - t0
+    e2e_ms = max_over_ranks(e2e_s * 1000.0)
+    # and the blocking call, one batch at a time
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         enc.embed(h_ids_np, h_cu_np, out=h_out_np)  # blocks until the embeddings are in host memory
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    e2e_ms = max_over_ranks(e2e_s * 1000.0)
+    blocking_ms = max_over_ranks((time.perf_counter() - t0) * 1000.0)
     e2e = {"value": world * N_SEQ * args.steps / (e2e_ms / 1000.0), "unit": "embeddings/s",
            "h2d_bytes_per_step": int(h_ids_np.nbytes + h_cu_np.nbytes),
            "d2h_bytes_per_step": int(h_out_np.nbytes),
-           "api": "lsc_encoder_embed (host token ids -> host fp32 embeddings)"}
+           "api": "lsc_encoder_submit / lsc_encoder_wait, two batches in flight (host token ids -> host fp32 embeddings)",
+           "blocking_call_value": world * N_SEQ * args.steps / (blocking_ms / 1000.0),
+           "blocking_call_api": "lsc_encoder_embed, one batch at a time"}
 
     # from texts: lsc_tokenizer_encode (native WordPiece, all host threads) + lsc_encoder_embed, per step 1024
     # synthetic texts of 126 pseudo-words (= 128 tokens with [CLS] / [SEP]); extra figure, not the headline

@@ -122,6 +122,22 @@ int lsc_encoder_embed_dev(lsc_encoder* enc, const int32_t* d_token_ids, const in
                           void* stream);
 
 /*
+ * Asynchronous form of lsc_encoder_embed - the shape of the reference's contract, which returns a
+ * CompletableFuture (EmbeddingsService.computeEmbeddings, EmbeddingsService.java:24-37).
+ * lsc_encoder_submit validates, enqueues upload, kernels and download and returns a ticket at once;
+ * lsc_encoder_wait(ticket) blocks until that batch's embeddings are in `out`.  Up to two submissions are in
+ * flight per handle (a third submit first waits for the oldest): the upload of batch i+1 and the download of
+ * batch i-1 run on their own streams beside the kernels of batch i, so a caller that keeps two batches in
+ * flight sees the device-resident rate.  token_ids, cu_seqlens and out must stay valid (and untouched) until
+ * the ticket has been waited for; pinned host memory is what makes the copies asynchronous.  Batches are
+ * processed in submission order.  A batch that needs more than one pass (> 262,144 tokens) is served
+ * synchronously inside submit.
+ */
+int lsc_encoder_submit(lsc_encoder* enc, const int32_t* token_ids, const int32_t* cu_seqlens, int32_t n_seq,
+                       float* out, int64_t* ticket);
+int lsc_encoder_wait(lsc_encoder* enc, int64_t ticket);
+
+/*
  * Measurement aid (no reference counterpart): when enabled, every kernel launch of this handle is
  * bracketed by CUDA events on its stream.  lsc_encoder_read_profile waits for them and returns the
  * milliseconds and launch counts accumulated since the previous read, per kernel class:

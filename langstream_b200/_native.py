@@ -56,6 +56,8 @@ SIGNATURES = {
     "lsc_encoder_create": (C.c_int, [C.POINTER(EncoderConfig), _vp, C.c_size_t, C.c_int, C.POINTER(_vp)]),
     "lsc_encoder_embed": (C.c_int, [_vp, _vp, _vp, _i32, _vp]),
     "lsc_encoder_embed_dev": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
+    "lsc_encoder_submit": (C.c_int, [_vp, _vp, _vp, _i32, _vp, C.POINTER(_i64)]),
+    "lsc_encoder_wait": (C.c_int, [_vp, _i64]),
     "lsc_encoder_set_profiling": (C.c_int, [_vp, C.c_int]),
     "lsc_encoder_read_profile": (C.c_int, [_vp, _vp, _vp, _i32]),
     "lsc_encoder_dim": (C.c_int, [_vp]),
@@ -173,6 +175,17 @@ class Encoder:
         return int(lib().lsc_encoder_launch_count(self._h))
 
     PROFILE_CLASSES = ("embed_ln", "gemm", "attention", "layernorm", "pool_l2", "ffn_fused")
+
+    def submit(self, token_ids, cu_seqlens, out) -> int:
+        """lsc_encoder_submit: enqueue a batch and return its ticket.  The three arrays (int32 ids, int32
+        cu_seqlens, float32 [n, hidden] out) must stay alive and untouched until wait(ticket)."""
+        n = int(len(cu_seqlens) - 1)
+        t = _i64(0)
+        check(lib().lsc_encoder_submit(self._h, _ptr(token_ids), _ptr(cu_seqlens), n, _ptr(out), C.byref(t)))
+        return int(t.value)
+
+    def wait(self, ticket: int) -> None:
+        check(lib().lsc_encoder_wait(self._h, int(ticket)))
 
     def set_profiling(self, enabled: bool):
         check(lib().lsc_encoder_set_profiling(self._h, int(enabled)))

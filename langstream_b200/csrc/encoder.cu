@@ -68,6 +68,21 @@ struct lsc_encoder {
     int32_t* d_ids = nullptr;
     int32_t* d_cu = nullptr;
     float* d_out = nullptr;
+    // asynchronous host-buffer path (lsc_encoder_submit / lsc_encoder_wait): two staging slots, copies on their
+    // own streams so that batch i+1's upload and batch i-1's download overlap batch i's kernels
+    struct AsyncSlot {
+        int32_t* d_ids = nullptr;
+        int32_t* d_cu = nullptr;
+        float* d_out = nullptr;
+        int64_t cap_tokens = 0, cap_seqs = 0;
+        std::vector<int32_t> cu_host;
+        cudaEvent_t ev_in = nullptr, ev_fwd = nullptr, ev_done = nullptr;
+        int64_t ticket = -1;   // ticket in flight in this slot (-1: free)
+        bool sync_done = false;  // the submission was served synchronously (multi-pass batch)
+    };
+    AsyncSlot slots[2];
+    cudaStream_t stream_in = nullptr, stream_out = nullptr;
+    int64_t next_ticket = 0;
     float* stats_x = nullptr;   // [cap_tokens][stats_p][2] partial row statistics of x / tmp (LN folding)
     float* stats_1 = nullptr;
     int stats_p = 0;    // partials per row of stats_1 (written by the attention-output GEMM)
@@ -317,6 +332,17 @@ void lsc_encoder_destroy(lsc_encoder* e) {
     if (e == nullptr) return;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->stream_out) cudaStreamSynchronize(e->stream_out);
+    for (auto& sl : e->slots) {
+        if (sl.d_ids) cudaFree(sl.d_ids);
+        if (sl.d_cu) cudaFree(sl.d_cu);
+        if (sl.d_out) cudaFree(sl.d_out);
+        if (sl.ev_in) cudaEventDestroy(sl.ev_in);
+        if (sl.ev_fwd) cudaEventDestroy(sl.ev_fwd);
+        if (sl.ev_done) cudaEventDestroy(sl.ev_done);
+    }
+    if (e->stream_in) cudaStreamDestroy(e->stream_in);
+    if (e->stream_out) cudaStreamDestroy(e->stream_out);
     for (void* p : e->owned) cudaFree(p);
     void* ws[] = {e->x, e->x1, e->tmp, e->qkv, e->ctx, e->ffn, e->d_ids, e->d_cu, e->d_out, e->stats_x, e->stats_1};
     for (void* p : ws)
@@ -482,25 +508,34 @@ int lsc_encoder_embed_dev(lsc_encoder* e, const int32_t* d_token_ids, const int3
                    static_cast<cudaStream_t>(stream));
 }
 
+// argument checks shared by the host-buffer entry points; *total receives the token count
+static int validate_batch(const char* who, lsc_encoder* e, const int32_t* token_ids, const int32_t* cu_seqlens,
+                          int32_t n_seq, const float* out, int64_t* total_out) {
+    if (cu_seqlens == nullptr || out == nullptr) return fail(LSC_E_INVALID, std::string(who) + ": null pointer");
+    if (cu_seqlens[0] != 0) return fail(LSC_E_INVALID, std::string(who) + ": cu_seqlens[0] must be 0");
+    for (int i = 0; i < n_seq; ++i) {
+        const int len = cu_seqlens[i + 1] - cu_seqlens[i];
+        if (len < 0) return fail(LSC_E_INVALID, std::string(who) + ": cu_seqlens must be non-decreasing");
+        if (len > e->cfg.max_position)
+            return fail(LSC_E_TOO_LONG, "Illegal input, maybe the number of tokens is too high");
+    }
+    const int64_t total = cu_seqlens[n_seq];
+    if (total > 0 && token_ids == nullptr) return fail(LSC_E_INVALID, std::string(who) + ": token_ids is null");
+    for (int64_t t = 0; t < total; ++t)
+        if (token_ids[t] < 0 || token_ids[t] >= e->cfg.vocab)
+            return fail(LSC_E_INVALID, std::string(who) + ": token id outside the vocabulary");
+    *total_out = total;
+    return LSC_OK;
+}
+
 int lsc_encoder_embed(lsc_encoder* e, const int32_t* token_ids, const int32_t* cu_seqlens, int32_t n_seq,
                       float* out) {
     if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed: encoder is null");
     if (n_seq < 0) return fail(LSC_E_INVALID, "lsc_encoder_embed: negative n_seq");
     if (n_seq == 0) return LSC_OK;
-    if (cu_seqlens == nullptr || out == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed: null pointer");
-    if (cu_seqlens[0] != 0) return fail(LSC_E_INVALID, "lsc_encoder_embed: cu_seqlens[0] must be 0");
+    int64_t total = 0;
+    LSC_TRY(validate_batch("lsc_encoder_embed", e, token_ids, cu_seqlens, n_seq, out, &total));
     const int H = e->cfg.hidden;
-    for (int i = 0; i < n_seq; ++i) {
-        const int len = cu_seqlens[i + 1] - cu_seqlens[i];
-        if (len < 0) return fail(LSC_E_INVALID, "lsc_encoder_embed: cu_seqlens must be non-decreasing");
-        if (len > e->cfg.max_position)
-            return fail(LSC_E_TOO_LONG, "Illegal input, maybe the number of tokens is too high");
-    }
-    const int64_t total = cu_seqlens[n_seq];
-    if (total > 0 && token_ids == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed: token_ids is null");
-    for (int64_t t = 0; t < total; ++t)
-        if (token_ids[t] < 0 || token_ids[t] >= e->cfg.vocab)
-            return fail(LSC_E_INVALID, "lsc_encoder_embed: token id outside the vocabulary");
 
     std::lock_guard<std::mutex> lock(e->mu);
     LSC_CUDA(cudaSetDevice(e->device));
@@ -530,6 +565,107 @@ int lsc_encoder_embed(lsc_encoder* e, const int32_t* token_ids, const int32_t* c
         LSC_CUDA(cudaStreamSynchronize(e->stream));  // cu_local and staging are reused by the next chunk
         s0 = s1;
     }
+    return LSC_OK;
+}
+
+int lsc_encoder_submit(lsc_encoder* e, const int32_t* token_ids, const int32_t* cu_seqlens, int32_t n_seq, float* out,
+                       int64_t* ticket) {
+    if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_submit: encoder is null");
+    if (ticket == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_submit: ticket is null");
+    if (n_seq < 0) return fail(LSC_E_INVALID, "lsc_encoder_submit: negative n_seq");
+    int64_t total = 0;
+    if (n_seq > 0) LSC_TRY(validate_batch("lsc_encoder_submit", e, token_ids, cu_seqlens, n_seq, out, &total));
+    std::lock_guard<std::mutex> lock(e->mu);
+    LSC_CUDA(cudaSetDevice(e->device));
+    const int64_t tk = e->next_ticket;
+    lsc_encoder::AsyncSlot& sl = e->slots[tk & 1];
+    if (sl.ticket >= 0) {  // two submissions in flight: the older one has to finish before its slot is reused
+        if (!sl.sync_done) LSC_CUDA(cudaEventSynchronize(sl.ev_done));
+        sl.ticket = -1;
+    }
+    if (e->stream_in == nullptr) {
+        LSC_CUDA(cudaStreamCreateWithFlags(&e->stream_in, cudaStreamNonBlocking));
+        LSC_CUDA(cudaStreamCreateWithFlags(&e->stream_out, cudaStreamNonBlocking));
+    }
+    if (sl.ev_in == nullptr) {
+        LSC_CUDA(cudaEventCreateWithFlags(&sl.ev_in, cudaEventDisableTiming));
+        LSC_CUDA(cudaEventCreateWithFlags(&sl.ev_fwd, cudaEventDisableTiming));
+        LSC_CUDA(cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
+    }
+    sl.sync_done = false;
+    if (n_seq == 0 || total > kChunkTokens) {
+        // empty, or more than one pass: served synchronously on the compute stream (ordered behind earlier tickets)
+        if (n_seq > 0) {
+            e->mu.unlock();
+            const int rc = lsc_encoder_embed(e, token_ids, cu_seqlens, n_seq, out);
+            e->mu.lock();
+            if (rc != LSC_OK) return rc;
+        }
+        sl.sync_done = true;
+    } else {
+        const int H = e->cfg.hidden;
+        if (total > sl.cap_tokens) {
+            if (sl.d_ids) cudaFree(sl.d_ids);
+            sl.d_ids = nullptr;
+            sl.cap_tokens = 0;
+            const int64_t cap = std::max<int64_t>(total, 4096);
+            LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&sl.d_ids), cap * sizeof(int32_t)));
+            sl.cap_tokens = cap;
+        }
+        if (n_seq > sl.cap_seqs) {
+            if (sl.d_cu) cudaFree(sl.d_cu);
+            if (sl.d_out) cudaFree(sl.d_out);
+            sl.d_cu = nullptr;
+            sl.d_out = nullptr;
+            sl.cap_seqs = 0;
+            const int64_t cap = std::max<int64_t>(n_seq, 64);
+            LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&sl.d_cu), (cap + 1) * sizeof(int32_t)));
+            LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&sl.d_out), cap * H * sizeof(float)));
+            sl.cap_seqs = cap;
+        }
+        int maxlen = 0;
+        for (int i = 0; i < n_seq; ++i) maxlen = std::max(maxlen, cu_seqlens[i + 1] - cu_seqlens[i]);
+        sl.cu_host.assign(cu_seqlens, cu_seqlens + n_seq + 1);  // stays alive until the copy has run
+        // upload on the input stream, kernels on the compute stream (shared workspace: batches are serialised
+        // there), download on the output stream
+        if (total > 0)
+            LSC_CUDA(cudaMemcpyAsync(sl.d_ids, token_ids, static_cast<size_t>(total) * sizeof(int32_t), cudaMemcpyHostToDevice,
+                                     e->stream_in));
+        LSC_CUDA(cudaMemcpyAsync(sl.d_cu, sl.cu_host.data(), static_cast<size_t>(n_seq + 1) * sizeof(int32_t),
+                                 cudaMemcpyHostToDevice, e->stream_in));
+        LSC_CUDA(cudaEventRecord(sl.ev_in, e->stream_in));
+        LSC_CUDA(cudaStreamWaitEvent(e->stream, sl.ev_in, 0));
+        LSC_TRY(forward(e, sl.d_ids, sl.d_cu, n_seq, static_cast<int>(total), maxlen, sl.d_out, e->stream));
+        LSC_CUDA(cudaEventRecord(sl.ev_fwd, e->stream));
+        LSC_CUDA(cudaStreamWaitEvent(e->stream_out, sl.ev_fwd, 0));
+        LSC_CUDA(cudaMemcpyAsync(out, sl.d_out, static_cast<size_t>(n_seq) * H * sizeof(float), cudaMemcpyDeviceToHost,
+                                 e->stream_out));
+        LSC_CUDA(cudaEventRecord(sl.ev_done, e->stream_out));
+    }
+    sl.ticket = tk;
+    e->next_ticket = tk + 1;
+    *ticket = tk;
+    return LSC_OK;
+}
+
+int lsc_encoder_wait(lsc_encoder* e, int64_t ticket) {
+    if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_wait: encoder is null");
+    cudaEvent_t ev = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(e->mu);
+        if (ticket < 0 || ticket >= e->next_ticket) return fail(LSC_E_INVALID, "lsc_encoder_wait: unknown ticket");
+        lsc_encoder::AsyncSlot& sl = e->slots[ticket & 1];
+        if (sl.ticket != ticket) return LSC_OK;  // already completed (its slot has been reused or released)
+        if (sl.sync_done) {
+            sl.ticket = -1;
+            return LSC_OK;
+        }
+        ev = sl.ev_done;
+    }
+    LSC_CUDA(cudaSetDevice(e->device));
+    LSC_CUDA(cudaEventSynchronize(ev));
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (e->slots[ticket & 1].ticket == ticket) e->slots[ticket & 1].ticket = -1;
     return LSC_OK;
 }
 

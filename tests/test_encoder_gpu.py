@@ -149,3 +149,38 @@ def test_device_api_matches_host_api(native_lib, cuda_device):
     assert np.array_equal(d_out.cpu().numpy(), host)
     assert enc.launch_count > 0
     enc.close()
+
+
+def test_submit_wait_pipeline_matches_blocking_call(native_lib, cuda_device):
+    """lsc_encoder_submit / lsc_encoder_wait: the same embeddings as lsc_encoder_embed, in submission order, with
+    two batches in flight, out-of-order waits, an empty batch and a repeated wait."""
+    import torch
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder, NativeError
+
+    spec = W.MINILM_L6
+    enc = Encoder(spec, W.random_init(spec, 0))
+    batches = []
+    for i, (n, L) in enumerate([(64, 128), (17, 40), (200, 64), (1, 1), (96, 128), (33, 90)]):
+        ids, cu = W.synthetic_token_ids(n, L, seed=100 + i, min_len=1)
+        h_ids, h_cu = torch.from_numpy(ids).pin_memory(), torch.from_numpy(cu).pin_memory()
+        h_out = torch.full((n, spec.hidden), float("nan")).pin_memory()
+        batches.append((h_ids.numpy(), h_cu.numpy(), h_out.numpy(), enc.embed(ids, cu).copy()))
+    tickets = [enc.submit(b[0], b[1], b[2]) for b in batches[:2]]
+    for i in range(2, len(batches)):            # keep two in flight
+        enc.wait(tickets[i - 2])
+        tickets.append(enc.submit(batches[i][0], batches[i][1], batches[i][2]))
+    enc.wait(tickets[-1])                       # newest first, then the older one, then again
+    enc.wait(tickets[-2])
+    enc.wait(tickets[-2])
+    assert tickets == list(range(len(batches)))
+    for _, _, out, ref in batches:
+        assert np.array_equal(out, ref)         # same kernels, same order of operations: identical bits
+    empty_out = np.zeros((0, spec.hidden), np.float32)
+    t = enc.submit(np.zeros(0, np.int32), np.zeros(1, np.int32), empty_out)
+    enc.wait(t)
+    with pytest.raises(NativeError):
+        enc.wait(10_000)
+    with pytest.raises(NativeError, match="vocabulary"):
+        enc.submit(np.array([spec.vocab], np.int32), np.array([0, 1], np.int32), np.zeros((1, spec.hidden), np.float32))
+    enc.close()
