@@ -406,15 +406,21 @@ def run_cuda(args):
         barrier()
         t0 = time.perf_counter()
         tok_s = 0.0
-        for _ in range(reps):
+        pending, keep = None, []
+        for r in range(reps):  # tokenise batch r while the GPU works on batch r-1 (submit / wait)
             a0 = time.perf_counter()
             t_ids, t_cu = tok.encode_packed(texts)
             tok_s += time.perf_counter() - a0
-            enc.embed(t_ids, t_cu, out=h_out_np)
-        torch.cuda.synchronize()
+            keep = keep[-1:] + [(t_ids, t_cu)]  # the arrays of the batches in flight stay referenced
+            t = enc.submit(t_ids, t_cu, bufs[r & 1][2])
+            if pending is not None:
+                enc.wait(pending)
+            pending = t
+        enc.wait(pending)
         text_ms = max_over_ranks((time.perf_counter() - t0) * 1000.0)
         text_e2e = {"value": world * N_SEQ * reps / (text_ms / 1000.0), "unit": "embeddings/s",
-                    "api": "lsc_tokenizer_encode + lsc_encoder_embed (host texts -> host fp32 embeddings), serial",
+                    "api": "lsc_tokenizer_encode + lsc_encoder_submit / lsc_encoder_wait (host texts -> host fp32 embeddings), "
+                           "tokenisation of batch i+1 overlapping the kernels of batch i",
                     "tokenizer_texts_per_s": N_SEQ * reps / tok_s, "tokenizer_threads": os.cpu_count()}
         tok.close()
     except Exception as e:  # noqa: BLE001 - an extra figure must not take the benchmark down
