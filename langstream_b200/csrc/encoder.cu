@@ -89,6 +89,18 @@ struct lsc_encoder {
     int stats_px = 0;   // partials per row of stats_x (4 when the fused feed-forward kernel writes it)
     std::atomic<int64_t> launches{0};
     Profiler prof;  // classes: 0 embed+LN, 1 GEMM, 2 attention, 3 LayerNorm, 4 pool
+    // All passes of a handle share the activation workspace, and the *_dev / submit calls return without
+    // synchronising: every pass records this event at its end and the next pass - on whatever stream - waits
+    // for it first, so passes enqueued on different streams are serialised on the GPU as well as on the host.
+    cudaEvent_t ev_last = nullptr;
+    bool ev_recorded = false;
+    // tensor maps of the activation buffers for a given token count (they change only with T or a re-allocation)
+    struct ActMaps {
+        int64_t T = -1;
+        CUtensorMap tm_x, tm_tmp, tm_ctx, tm_ffn, tc_qkv, tc_tmp, tc_x, tc_ffn;
+    };
+    ActMaps act_maps[4];
+    int act_next = 0;
 };
 
 namespace lsc {
@@ -185,6 +197,7 @@ int ensure_workspace(lsc_encoder* e, int64_t T) {
     if (e->stats_1) cudaFree(e->stats_1);
     e->stats_x = e->stats_1 = nullptr;
     e->cap_tokens = 0;
+    for (auto& m : e->act_maps) m.T = -1;  // they describe the buffers just freed
     const size_t sizes[6] = {H, H, H, 3 * H, H, F};
     for (int i = 0; i < 6; ++i) {
         void* p = nullptr;
@@ -245,21 +258,32 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
     const lsc_encoder_config& c = e->cfg;
     const int H = c.hidden, F = c.ffn;
     int64_t nlaunch = 0;
+    if (T > 0) LSC_TRY(ensure_workspace(e, T));
+    if (e->ev_recorded) LSC_CUDA(cudaStreamWaitEvent(st, e->ev_last, 0));
     if (T > 0) {
-        LSC_TRY(ensure_workspace(e, T));
         if (c.gemm_impl == 0) {
             // ---- product path: tcgen05 GEMMs, every LayerNorm folded into the neighbouring epilogues ----
             // x and tmp hold PRE-LayerNorm rows plus per-row partial statistics; a normalised activation is
             // never written to memory.
-            CUtensorMap tm_x, tm_tmp, tm_ctx, tm_ffn, tc_qkv, tc_tmp, tc_x, tc_ffn;
-            LSC_TRY(make_tmap_bf16_store32(&tc_qkv, e->qkv, T, 3 * H));
-            LSC_TRY(make_tmap_bf16_store32(&tc_tmp, e->tmp, T, H));
-            LSC_TRY(make_tmap_bf16_store32(&tc_x, e->x, T, H));
-            LSC_TRY(make_tmap_bf16_store32(&tc_ffn, e->ffn, T, F));
-            LSC_TRY(make_tmap_bf16_sw128(&tm_x, e->x, T, H, 128));
-            LSC_TRY(make_tmap_bf16_sw128(&tm_tmp, e->tmp, T, H, 128));
-            LSC_TRY(make_tmap_bf16_sw128(&tm_ctx, e->ctx, T, H, 128));
-            LSC_TRY(make_tmap_bf16_sw128(&tm_ffn, e->ffn, T, F, 128));
+            lsc_encoder::ActMaps* am = nullptr;
+            for (auto& m : e->act_maps)
+                if (m.T == T) am = &m;
+            if (am == nullptr) {
+                am = &e->act_maps[e->act_next];
+                e->act_next = (e->act_next + 1) % 4;
+                am->T = -1;
+                LSC_TRY(make_tmap_bf16_store32(&am->tc_qkv, e->qkv, T, 3 * H));
+                LSC_TRY(make_tmap_bf16_store32(&am->tc_tmp, e->tmp, T, H));
+                LSC_TRY(make_tmap_bf16_store32(&am->tc_x, e->x, T, H));
+                LSC_TRY(make_tmap_bf16_store32(&am->tc_ffn, e->ffn, T, F));
+                LSC_TRY(make_tmap_bf16_sw128(&am->tm_x, e->x, T, H, 128));
+                LSC_TRY(make_tmap_bf16_sw128(&am->tm_tmp, e->tmp, T, H, 128));
+                LSC_TRY(make_tmap_bf16_sw128(&am->tm_ctx, e->ctx, T, H, 128));
+                LSC_TRY(make_tmap_bf16_sw128(&am->tm_ffn, e->ffn, T, F, 128));
+                am->T = T;
+            }
+            const CUtensorMap &tm_x = am->tm_x, &tm_tmp = am->tm_tmp, &tm_ctx = am->tm_ctx, &tm_ffn = am->tm_ffn,
+                              &tc_qkv = am->tc_qkv, &tc_tmp = am->tc_tmp, &tc_x = am->tc_x, &tc_ffn = am->tc_ffn;
             const int P = e->stats_p, PX = e->stats_px;
             const float inv_h = 1.0f / static_cast<float>(H);
             LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word, e->d_pos,
@@ -314,6 +338,8 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
     } else {
         LSC_LAUNCH(4, pool_l2_launch(e->x, d_cu, n_seq, H, d_out, nullptr, 0, nullptr, nullptr, c.ln_eps, st));
     }
+    LSC_CUDA(cudaEventRecord(e->ev_last, st));
+    e->ev_recorded = true;
     e->launches += nlaunch;
     return LSC_OK;
 }
@@ -348,6 +374,7 @@ void lsc_encoder_destroy(lsc_encoder* e) {
     for (void* p : ws)
         if (p) cudaFree(p);
     if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->ev_last) cudaEventDestroy(e->ev_last);
     delete e;
 }
 
@@ -375,6 +402,7 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
     int rc = LSC_OK;
     auto body = [&]() -> int {
         LSC_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+        LSC_CUDA(cudaEventCreateWithFlags(&e->ev_last, cudaEventDisableTiming));
         const size_t H = cfg->hidden, F = cfg->ffn;
         const float* p = static_cast<const float*>(weights);
         LSC_TRY(upload_f32(e, &e->d_word, p, static_cast<size_t>(cfg->vocab) * H));
@@ -528,17 +556,9 @@ static int validate_batch(const char* who, lsc_encoder* e, const int32_t* token_
     return LSC_OK;
 }
 
-int lsc_encoder_embed(lsc_encoder* e, const int32_t* token_ids, const int32_t* cu_seqlens, int32_t n_seq,
-                      float* out) {
-    if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed: encoder is null");
-    if (n_seq < 0) return fail(LSC_E_INVALID, "lsc_encoder_embed: negative n_seq");
-    if (n_seq == 0) return LSC_OK;
-    int64_t total = 0;
-    LSC_TRY(validate_batch("lsc_encoder_embed", e, token_ids, cu_seqlens, n_seq, out, &total));
+// The blocking host-buffer pass; the caller holds e->mu and has made the device current.
+static int embed_locked(lsc_encoder* e, const int32_t* token_ids, const int32_t* cu_seqlens, int32_t n_seq, float* out) {
     const int H = e->cfg.hidden;
-
-    std::lock_guard<std::mutex> lock(e->mu);
-    LSC_CUDA(cudaSetDevice(e->device));
     // Chunk the batch so one pass holds at most kChunkTokens tokens.
     std::vector<int32_t> cu_local;
     int s0 = 0;
@@ -568,6 +588,18 @@ int lsc_encoder_embed(lsc_encoder* e, const int32_t* token_ids, const int32_t* c
     return LSC_OK;
 }
 
+int lsc_encoder_embed(lsc_encoder* e, const int32_t* token_ids, const int32_t* cu_seqlens, int32_t n_seq,
+                      float* out) {
+    if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_embed: encoder is null");
+    if (n_seq < 0) return fail(LSC_E_INVALID, "lsc_encoder_embed: negative n_seq");
+    if (n_seq == 0) return LSC_OK;
+    int64_t total = 0;
+    LSC_TRY(validate_batch("lsc_encoder_embed", e, token_ids, cu_seqlens, n_seq, out, &total));
+    std::lock_guard<std::mutex> lock(e->mu);
+    LSC_CUDA(cudaSetDevice(e->device));
+    return embed_locked(e, token_ids, cu_seqlens, n_seq, out);
+}
+
 int lsc_encoder_submit(lsc_encoder* e, const int32_t* token_ids, const int32_t* cu_seqlens, int32_t n_seq, float* out,
                        int64_t* ticket) {
     if (e == nullptr) return fail(LSC_E_INVALID, "lsc_encoder_submit: encoder is null");
@@ -595,12 +627,8 @@ int lsc_encoder_submit(lsc_encoder* e, const int32_t* token_ids, const int32_t* 
     sl.sync_done = false;
     if (n_seq == 0 || total > kChunkTokens) {
         // empty, or more than one pass: served synchronously on the compute stream (ordered behind earlier tickets)
-        if (n_seq > 0) {
-            e->mu.unlock();
-            const int rc = lsc_encoder_embed(e, token_ids, cu_seqlens, n_seq, out);
-            e->mu.lock();
-            if (rc != LSC_OK) return rc;
-        }
+        // (the handle stays locked throughout: the ticket and its slot cannot be handed out twice)
+        if (n_seq > 0) LSC_TRY(embed_locked(e, token_ids, cu_seqlens, n_seq, out));
         sl.sync_done = true;
     } else {
         const int H = e->cfg.hidden;

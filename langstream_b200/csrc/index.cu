@@ -46,6 +46,11 @@ struct lsc_index {
     int64_t* d_slots = nullptr;        // upsert target slots
     int64_t cap_slots = 0;
     cudaStream_t stream = nullptr;
+    // The query / candidate scratch and the slab are shared by every call on the handle, and the *_dev calls
+    // return without synchronising: each pass records this event at its end and the next pass - on whatever
+    // stream it runs - waits for it first, so passes enqueued on different streams never overlap on the GPU.
+    cudaEvent_t ev_last = nullptr;
+    bool ev_recorded = false;
     std::mutex mu;
     std::atomic<int64_t> launches{0};
     Profiler prof;  // classes: 0 normalise rows/queries, 1 scan, 2 merge
@@ -53,6 +58,17 @@ struct lsc_index {
 
 namespace lsc {
 namespace {
+
+int order_after_previous(lsc_index* ix, cudaStream_t st) {
+    if (ix->ev_recorded) LSC_CUDA(cudaStreamWaitEvent(st, ix->ev_last, 0));
+    return LSC_OK;
+}
+
+int mark_pass_end(lsc_index* ix, cudaStream_t st) {
+    LSC_CUDA(cudaEventRecord(ix->ev_last, st));
+    ix->ev_recorded = true;
+    return LSC_OK;
+}
 
 int grow_rows(lsc_index* ix, int64_t need) {
     if (need <= ix->capacity) return LSC_OK;
@@ -136,6 +152,7 @@ int search_dev(lsc_index* ix, const float* d_queries, int B, int k, int64_t* d_o
         return LSC_OK;
     }
     LSC_TRY(ensure_query_buffers(ix, B, k));
+    LSC_TRY(order_after_previous(ix, st));
     const int qblk = B > TK_QROWS ? 2 * TK_QROWS : TK_QROWS;
     const int bpad = (B + qblk - 1) / qblk * qblk;
     LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st));
@@ -166,6 +183,7 @@ int search_dev(lsc_index* ix, const float* d_queries, int B, int k, int64_t* d_o
     }
     LSC_LAUNCH(2, topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, d_out_ids,
                                       d_out_scores, st));
+    LSC_TRY(mark_pass_end(ix, st));
     ix->launches += nlaunch;
     return LSC_OK;
 }
@@ -194,11 +212,13 @@ int upsert_dev(lsc_index* ix, const int64_t* ids, const float* d_vecs, int n, cu
     }
     LSC_TRY(grow_rows(ix, new_n));
     LSC_TRY(grow_buf(&ix->d_slots, &ix->cap_slots, n, 1024));
+    LSC_TRY(order_after_previous(ix, st));
     LSC_CUDA(cudaMemcpyAsync(ix->d_slots, slots.data(), static_cast<size_t>(n) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
     if (!new_ids.empty())
         LSC_CUDA(cudaMemcpyAsync(ix->d_ids + ix->n, new_ids.data(), new_ids.size() * sizeof(int64_t), cudaMemcpyHostToDevice, st));
     int64_t nlaunch = 0;
     LSC_LAUNCH(0, normalize_rows_launch(d_vecs, n, n, ix->dim, ix->d_slots, ix->d_rows, st));
+    LSC_TRY(mark_pass_end(ix, st));
     LSC_CUDA(cudaStreamSynchronize(st));  // host vectors `slots` / `new_ids` go out of scope
     for (int64_t id : new_ids) {
         ix->slot_of[id] = static_cast<int64_t>(ix->ids.size());
@@ -223,6 +243,7 @@ void lsc_index_destroy(lsc_index* ix) {
     for (void* p : bufs)
         if (p) cudaFree(p);
     if (ix->stream) cudaStreamDestroy(ix->stream);
+    if (ix->ev_last) cudaEventDestroy(ix->ev_last);
     delete ix;
 }
 
@@ -247,6 +268,10 @@ int lsc_index_create(int32_t dim, int64_t capacity, int device, lsc_index** out)
     int rc = LSC_OK;
     cudaError_t ce = cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking);
     if (ce != cudaSuccess) rc = fail_cuda(ce, "cudaStreamCreateWithFlags", __FILE__, __LINE__);
+    if (rc == LSC_OK) {
+        ce = cudaEventCreateWithFlags(&ix->ev_last, cudaEventDisableTiming);
+        if (ce != cudaSuccess) rc = fail_cuda(ce, "cudaEventCreateWithFlags", __FILE__, __LINE__);
+    }
     if (rc == LSC_OK) rc = grow_rows(ix, std::max<int64_t>(capacity, 1));
     if (rc != LSC_OK) {
         std::string msg = lsc_last_error();
@@ -312,23 +337,52 @@ int lsc_index_delete(lsc_index* ix, const int64_t* ids, int32_t n) {
     if (ids == nullptr) return fail(LSC_E_INVALID, "lsc_index_delete: null pointer");
     std::lock_guard<std::mutex> lock(ix->mu);
     LSC_CUDA(cudaSetDevice(ix->device));
-    LSC_CUDA(cudaDeviceSynchronize());
-    const size_t row_bytes = static_cast<size_t>(ix->dim) * sizeof(__nv_bfloat16);
+    // Host side: replay "move the last row into the freed slot" for every id and keep, per slot that ends up
+    // holding a different row, the ORIGINAL slot of that row.  A row is only ever taken from the current end of
+    // the slab, so every source lies at or past the final size and every destination in front of it: the moves
+    // are independent and one gather kernel applies them all (one upload, one launch, one wait per call
+    // instead of a device-wide synchronise and two blocking copies per deleted row).
+    std::unordered_map<int64_t, int64_t> origin;  // slot -> original slot of the row now in it
+    bool any = false;
     for (int i = 0; i < n; ++i) {
         auto it = ix->slot_of.find(ids[i]);
         if (it == ix->slot_of.end()) continue;
+        any = true;
         const int64_t slot = it->second;
         const int64_t last = ix->n - 1;
         ix->slot_of.erase(it);
+        auto lo = origin.find(last);
+        const int64_t last_origin = lo != origin.end() ? lo->second : last;
+        if (lo != origin.end()) origin.erase(lo);
         if (slot != last) {
             const int64_t moved = ix->ids[last];
-            LSC_CUDA(cudaMemcpy(ix->d_rows + slot * ix->dim, ix->d_rows + last * ix->dim, row_bytes, cudaMemcpyDeviceToDevice));
-            LSC_CUDA(cudaMemcpy(ix->d_ids + slot, &moved, sizeof(int64_t), cudaMemcpyHostToDevice));
+            origin[slot] = last_origin;
             ix->ids[slot] = moved;
             ix->slot_of[moved] = slot;
+        } else {
+            origin.erase(slot);
         }
         ix->ids.pop_back();
         ix->n = last;
+    }
+    if (!any) return LSC_OK;
+    std::vector<int64_t> moves;
+    moves.reserve(origin.size() * 2);
+    for (const auto& kv : origin) {
+        if (kv.first >= ix->n) continue;  // the slot itself was dropped later on
+        moves.push_back(kv.first);
+        moves.push_back(kv.second);
+    }
+    const int m = static_cast<int>(moves.size() / 2);
+    if (m > 0) {
+        LSC_TRY(grow_buf(&ix->d_slots, &ix->cap_slots, 2 * static_cast<int64_t>(m), 1024));
+        LSC_TRY(order_after_previous(ix, ix->stream));
+        LSC_CUDA(cudaMemcpyAsync(ix->d_slots, moves.data(), moves.size() * sizeof(int64_t), cudaMemcpyHostToDevice, ix->stream));
+        const int rc = move_rows_launch(ix->d_rows, ix->d_ids, ix->dim, ix->d_slots, m, ix->stream);
+        if (rc < 0) return rc;
+        ix->launches += rc;
+        LSC_TRY(mark_pass_end(ix, ix->stream));
+        LSC_CUDA(cudaStreamSynchronize(ix->stream));  // `moves` goes out of scope
     }
     return LSC_OK;
 }
@@ -379,11 +433,13 @@ int lsc_index_scores_naive_dev(lsc_index* ix, const float* d_queries, int32_t B,
     LSC_CUDA(cudaSetDevice(ix->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     LSC_TRY(ensure_query_buffers(ix, B, 1));
+    LSC_TRY(order_after_previous(ix, st));
     const int bpad = (B + TK_QROWS - 1) / TK_QROWS * TK_QROWS;
     int rc = normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st);
     if (rc < 0) return rc;
     rc = scores_naive_launch(ix->d_rows, ix->n, ix->dim, ix->d_qbf, B, d_scores, st);
-    return rc < 0 ? rc : LSC_OK;
+    if (rc < 0) return rc;
+    return mark_pass_end(ix, st);
 }
 
 int lsc_topk_merge_dev(const int64_t* d_ids, const float* d_scores, int32_t parts, int32_t B, int32_t k,

@@ -14,6 +14,10 @@
 // One CTA does the whole selection: the pairwise cosine matrix (n <= 128 documents: 64 KB of shared memory)
 // is computed once, then one iteration per picked document with BM25 re-evaluated over the documents still
 // remaining (N, avgdl and the document frequencies change as documents leave the pool, as in the reference).
+#include <algorithm>
+#include <cstring>
+#include <mutex>
+
 #include "common.h"
 
 namespace lsc {
@@ -154,6 +158,16 @@ int launch(const float* d_vecs, int n, int dim, const int32_t* d_tf, const int32
     return LSC_OK;
 }
 
+constexpr int kMaxDevices = 64;
+struct HostStaging {
+    std::mutex mu;
+    unsigned char* d = nullptr;  // device block
+    unsigned char* h = nullptr;  // pinned host twin
+    size_t cap = 0;
+    cudaStream_t stream = nullptr;
+};
+HostStaging g_staging[kMaxDevices];
+
 }  // namespace
 }  // namespace lsc
 
@@ -185,28 +199,43 @@ extern "C" int lsc_rerank_mmr(const float* doc_vecs, int32_t n_docs, int32_t dim
     const size_t nt = static_cast<size_t>(n_docs) * (n_terms > 0 ? n_terms : 1) * sizeof(int32_t);
     const size_t nl = static_cast<size_t>(n_docs) * sizeof(int32_t);
     const size_t no = static_cast<size_t>(n_docs + 1) * sizeof(int32_t);
-    unsigned char* d = nullptr;  // one allocation: vectors | term frequencies | lengths | order + count
+    // one block: vectors | term frequencies | lengths | order + count
     const size_t o_t = (nv + 255) & ~static_cast<size_t>(255), o_l = (o_t + nt + 255) & ~static_cast<size_t>(255),
                  o_o = (o_l + nl + 255) & ~static_cast<size_t>(255);
-    LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d), o_o + no));
-    int rc = LSC_OK;
-    auto body = [&]() -> int {
-        LSC_CUDA(cudaMemcpy(d, doc_vecs, nv, cudaMemcpyHostToDevice));
-        if (n_terms > 0) LSC_CUDA(cudaMemcpy(d + o_t, term_freq, nt, cudaMemcpyHostToDevice));
-        LSC_CUDA(cudaMemcpy(d + o_l, doc_len, nl, cudaMemcpyHostToDevice));
-        int32_t* d_order = reinterpret_cast<int32_t*>(d + o_o);
-        LSC_TRY(launch(reinterpret_cast<const float*>(d), n_docs, dim, reinterpret_cast<const int32_t*>(d + o_t),
-                       reinterpret_cast<const int32_t*>(d + o_l), n_terms, max_docs, lambda, k1, b, d_order,
-                       d_order + n_docs, nullptr));
-        std::vector<int32_t> host(static_cast<size_t>(n_docs) + 1);
-        LSC_CUDA(cudaMemcpy(host.data(), d_order, no, cudaMemcpyDeviceToHost));
-        const int32_t count = host[n_docs];
-        if (count < 0) return fail(LSC_E_INVALID, "rerank: no document could be selected (all scores are NaN)");
-        for (int32_t i = 0; i < count; ++i) out_order[i] = host[i];
-        *out_count = count;
-        return LSC_OK;
-    };
-    rc = body();
-    cudaFree(d);
-    return rc;
+    const size_t total = o_o + no;
+    int dev = 0;
+    LSC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(LSC_E_UNSUPPORTED, "lsc_rerank_mmr: device ordinal too large");
+    // Per-device staging kept between calls (a device block, its pinned host twin and a stream): at <= 128
+    // documents the kernel takes microseconds, so a cudaMalloc / cudaFree pair and blocking copies on the
+    // default stream per call were most of the call.  Calls on one device are serialised by the mutex.
+    HostStaging& hs = g_staging[dev];
+    std::lock_guard<std::mutex> lock(hs.mu);
+    if (hs.stream == nullptr) LSC_CUDA(cudaStreamCreateWithFlags(&hs.stream, cudaStreamNonBlocking));
+    if (total > hs.cap) {
+        if (hs.d) cudaFree(hs.d);
+        if (hs.h) cudaFreeHost(hs.h);
+        hs.d = hs.h = nullptr;
+        hs.cap = 0;
+        const size_t cap = std::max<size_t>(total, 1 << 20);
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&hs.d), cap));
+        LSC_CUDA(cudaMallocHost(reinterpret_cast<void**>(&hs.h), cap));
+        hs.cap = cap;
+    }
+    memcpy(hs.h, doc_vecs, nv);
+    if (n_terms > 0) memcpy(hs.h + o_t, term_freq, nt);
+    memcpy(hs.h + o_l, doc_len, nl);
+    LSC_CUDA(cudaMemcpyAsync(hs.d, hs.h, o_o, cudaMemcpyHostToDevice, hs.stream));  // one upload
+    int32_t* d_order = reinterpret_cast<int32_t*>(hs.d + o_o);
+    LSC_TRY(launch(reinterpret_cast<const float*>(hs.d), n_docs, dim, reinterpret_cast<const int32_t*>(hs.d + o_t),
+                   reinterpret_cast<const int32_t*>(hs.d + o_l), n_terms, max_docs, lambda, k1, b, d_order,
+                   d_order + n_docs, hs.stream));
+    LSC_CUDA(cudaMemcpyAsync(hs.h + o_o, d_order, no, cudaMemcpyDeviceToHost, hs.stream));
+    LSC_CUDA(cudaStreamSynchronize(hs.stream));
+    const int32_t* host = reinterpret_cast<const int32_t*>(hs.h + o_o);
+    const int32_t count = host[n_docs];
+    if (count < 0) return fail(LSC_E_INVALID, "rerank: no document could be selected (all scores are NaN)");
+    for (int32_t i = 0; i < count; ++i) out_order[i] = host[i];
+    *out_count = count;
+    return LSC_OK;
 }

@@ -283,7 +283,7 @@ __device__ __forceinline__ Head shfl_head(const Head& h, int o) {
 // LAYOUT 0: scan scratch  [qblock][parts][128][k], idx = int32 storage slot, ids mapped through
 //           `slot_ids`; ties by slot.
 // LAYOUT 1: shard lists   [parts][B][k], idx = int64 id; ties by part (shards hold ascending
-//           contiguous row ranges) then by position.
+//           contiguous row ranges) then by position inside the part's list.
 template <int LAYOUT>
 __global__ void __launch_bounds__(256)
 topk_merge_kernel(const float* __restrict__ sc, const void* __restrict__ ix, int parts, int B, int k,
@@ -312,7 +312,10 @@ topk_merge_kernel(const float* __restrict__ sc, const void* __restrict__ ix, int
             else id = static_cast<const int64_t*>(ix)[base + at];
             if (id >= 0) {
                 h.s = sc[base + at];
-                h.tie = LAYOUT == 0 ? id : static_cast<long long>(at);
+                // LAYOUT 1: shard first, then position inside the shard's list = the global storage order
+                // among equal scores (shards hold ascending row ranges), so duplicates come back in the same
+                // order as from one unsharded index
+                h.tie = LAYOUT == 0 ? id : ((static_cast<long long>(p) << 32) | static_cast<long long>(at));
             }
         }
         return h;
@@ -423,6 +426,21 @@ scores_naive_kernel(const __nv_bfloat16* __restrict__ rows, long long n, int dim
     }
 }
 
+// Delete support: row (and id) moves[2j+1] -> slot moves[2j], one warp per move.  Sources lie past the new end
+// of the slab and destinations in front of it, so no move reads what another one writes.
+__global__ void __launch_bounds__(256)
+move_rows_kernel(__nv_bfloat16* __restrict__ rows, int64_t* __restrict__ ids, int dim,
+                 const int64_t* __restrict__ moves, int m) {
+    const int lane = threadIdx.x & 31;
+    const int j = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (j >= m) return;
+    const int64_t dst = moves[2 * j], src = moves[2 * j + 1];
+    const uint4* s = reinterpret_cast<const uint4*>(rows + static_cast<size_t>(src) * dim);
+    uint4* d = reinterpret_cast<uint4*>(rows + static_cast<size_t>(dst) * dim);
+    for (int c = lane; c < dim / 8; c += 32) d[c] = s[c];
+    if (lane == 0) ids[dst] = ids[src];
+}
+
 __global__ void fill_empty_kernel(int64_t* ids, float* scores, size_t n) {
     const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) {
@@ -506,6 +524,14 @@ int scores_naive_launch(const __nv_bfloat16* rows, int64_t n, int dim, const __n
     const int wpb = 8;
     const int64_t grid = (n + wpb - 1) / wpb;
     scores_naive_kernel<<<static_cast<unsigned>(grid), 256, 0, stream>>>(rows, n, dim, q, B, out);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+int move_rows_launch(__nv_bfloat16* rows, int64_t* ids, int dim, const int64_t* moves, int m, cudaStream_t stream) {
+    if (m <= 0) return 0;
+    const int wpb = 8;
+    move_rows_kernel<<<(m + wpb - 1) / wpb, 256, 0, stream>>>(rows, ids, dim, moves, m);
     LSC_CUDA(cudaGetLastError());
     return 1;
 }

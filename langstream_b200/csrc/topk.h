@@ -44,6 +44,10 @@ int normalize_rows_launch(const float* src, int n, int n_pad, int dim, const int
 int scores_naive_launch(const __nv_bfloat16* rows, int64_t n, int dim, const __nv_bfloat16* q, int B,
                         float* out, cudaStream_t stream);
 
+// rows[moves[2j]] = rows[moves[2j+1]] (and the ids likewise) for j < m: the batched form of "move the last
+// row into the freed slot"; sources and destinations must not overlap.
+int move_rows_launch(__nv_bfloat16* rows, int64_t* ids, int dim, const int64_t* moves, int m, cudaStream_t stream);
+
 int fill_empty_launch(int64_t* ids, float* scores, size_t n, cudaStream_t stream);
 
 }  // namespace lsc

@@ -7,9 +7,9 @@
 // because both synchronise the whole device and stall every stream that is running.
 // The regular entry point, lsc_index_search_dev, grows its query and candidate buffers with
 // cudaMalloc the first time a larger batch arrives.  This variant runs the same kernels
-// (normalise queries -> topk_scan_kernel -> topk_merge_kernel) but takes their scratch memory from a
-// fixed array that is part of the library image, so it never calls cudaMalloc, cudaFree or any
-// allocating library routine.  Caller-visible limits follow from the array's size: one query block
+// (normalise queries -> the scan: topk_scan_rows_kernel for k <= 16, topk_scan_kernel above that ->
+// topk_merge_kernel) but takes their scratch memory from a fixed array that is part of the library
+// image, so it never calls cudaMalloc, cudaFree or any allocating library routine.  Caller-visible limits follow from the array's size: one query block
 // (B <= 128), k <= 32, dim <= 512, at most 160 SMs.
 //
 // Things a caller must know:

@@ -11,6 +11,34 @@ COS_MIN = 0.999
 MAX_ABS = 2e-3
 
 
+def _margins(got, want):
+    """(cos_min, max_abs) of a batch, the two quantities BASELINE.json's tolerance is stated in."""
+    num = (got * want).sum(1)
+    den = np.linalg.norm(got, axis=1) * np.linalg.norm(want, axis=1)
+    ok = den > 0
+    cos_min = float((num[ok] / den[ok]).min()) if ok.any() else 1.0
+    return cos_min, float(np.abs(got - want).max())
+
+
+def _report(name, got, want):
+    """Print the parity margin of a headline configuration and append it to gpurun_out/parity_margins.jsonl (the
+    figures quoted in DESIGN.md / profiles/ come from there)."""
+    import json
+
+    cos_min, max_abs = _margins(got, want)
+    rec = {"case": name, "rows": int(got.shape[0]), "cos_min": cos_min, "max_abs": max_abs,
+           "cos_budget": COS_MIN, "max_abs_budget": MAX_ABS}
+    print("PARITY", json.dumps(rec))
+    out = Path(__file__).resolve().parents[1] / "gpurun_out"
+    try:
+        out.mkdir(exist_ok=True)
+        with open(out / "parity_margins.jsonl", "a") as f:
+            f.write(json.dumps(rec) + "\n")
+    except OSError:
+        pass
+    return cos_min, max_abs
+
+
 def _check(got, want):
     assert got.shape == want.shape
     assert np.isfinite(got).all()
@@ -183,4 +211,145 @@ def test_submit_wait_pipeline_matches_blocking_call(native_lib, cuda_device):
         enc.wait(10_000)
     with pytest.raises(NativeError, match="vocabulary"):
         enc.submit(np.array([spec.vocab], np.int32), np.array([0, 1], np.int32), np.zeros((1, spec.hidden), np.float32))
+    enc.close()
+
+
+@pytest.mark.parametrize("ragged", [False, True])
+def test_headline_config_all_1024_rows(native_lib, cuda_device, ragged):
+    """BASELINE configs[1] at its full size: 1024 sequences of 128 tokens, fixed length
+    and UniformInt[16,128] packed, EVERY row against the HuggingFace fp32 oracle run one text per forward like the
+    reference (AbstractHuggingFaceEmbeddingService.java:191-206), on the weights bench.py uses (seed 0)."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+    from oracle.encoder_oracle import HFOracle
+
+    spec = W.MINILM_L6
+    blob = W.random_init(spec, seed=0)
+    ids, cu = W.synthetic_token_ids(1024, 128, seed=1234, min_len=16 if ragged else None)
+    want = HFOracle(spec, blob).embed_one_by_one(ids, cu)
+    enc = Encoder(spec, blob)
+    got = enc.embed(ids, cu)
+    enc.close()
+    _report("minilm_1024x128_" + ("ragged16-128" if ragged else "fixed"), got, want)
+    _check(got, want)
+
+
+def test_headline_config_perturbed_weights_1024_rows(native_lib, cuda_device):
+    """Same size with randomised biases / LayerNorm parameters (HF's default init leaves them at 0 / 1, which
+    would hide an error in the LayerNorm folding)."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+    from oracle.encoder_oracle import HFOracle
+
+    spec = W.MINILM_L6
+    blob = W.random_init(spec, seed=3, perturb=True)
+    ids, cu = W.synthetic_token_ids(1024, 128, seed=4321, min_len=16)
+    want = HFOracle(spec, blob).embed_one_by_one(ids, cu)
+    enc = Encoder(spec, blob)
+    got = enc.embed(ids, cu)
+    enc.close()
+    _report("minilm_1024x128_ragged_perturbed", got, want)
+    _check(got, want)
+
+
+def test_base_shape_64_sequences(native_lib, cuda_device):
+    """SURVEY.md 8(d) config 3's parity subset: 12L/768-d, 64 sequences - 16 of exactly 512 tokens, 48 drawn from
+    UniformInt[64,512] - against the fp32 oracle."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+    from oracle.encoder_oracle import HFOracle
+
+    spec = W.BERT_BASE
+    blob = W.random_init(spec, seed=0)
+    ids_a, cu_a = W.synthetic_token_ids(16, 512, seed=99)
+    ids_b, cu_b = W.synthetic_token_ids(48, 512, seed=98, min_len=64)
+    ids = np.concatenate([ids_a, ids_b])
+    cu = np.concatenate([cu_a, cu_a[-1] + cu_b[1:]]).astype(np.int32)
+    want = HFOracle(spec, blob).embed_batched(ids, cu, batch=4)
+    enc = Encoder(spec, blob)
+    got = enc.embed(ids, cu)
+    enc.close()
+    _report("base_64seq_512tok", got, want)
+    _check(got, want)
+
+
+def test_two_threads_submitting_keep_their_tickets_apart(native_lib, cuda_device):
+    """The handle promises thread safety: two threads submit at the same time, one of them a batch of more than
+    262,144 tokens (served in several passes inside submit).  Every ticket is distinct and every batch comes back
+    as the blocking call computes it."""
+    import threading
+
+    import torch
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+
+    spec = W.MINILM_L6
+    enc = Encoder(spec, W.random_init(spec, 0))
+    shapes = {0: [(2100, 128), (40, 64), (64, 128)], 1: [(48, 100), (300, 128), (7, 30), (128, 128)]}
+    work = {}
+    for t, lst in shapes.items():
+        work[t] = []
+        for i, (n, L) in enumerate(lst):
+            ids, cu = W.synthetic_token_ids(n, L, seed=500 + 10 * t + i, min_len=L if n > 1000 else 1)
+            ref = enc.embed(ids, cu).copy()
+            h_ids, h_cu = torch.from_numpy(ids).pin_memory(), torch.from_numpy(cu).pin_memory()
+            h_out = torch.full((n, spec.hidden), float("nan")).pin_memory()
+            work[t].append((h_ids, h_cu, h_out, ref))
+    assert int(work[0][0][1][-1]) > 262_144
+    tickets, errors = {0: [], 1: []}, []
+    start = threading.Barrier(2)
+
+    def run(t):
+        try:
+            start.wait()
+            for rep in range(3):
+                for h_ids, h_cu, h_out, _ in work[t]:
+                    tk = enc.submit(h_ids.numpy(), h_cu.numpy(), h_out.numpy())
+                    tickets[t].append(tk)
+                    enc.wait(tk)
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=run, args=(t,)) for t in (0, 1)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    every = tickets[0] + tickets[1]
+    assert len(set(every)) == len(every) == 3 * (len(shapes[0]) + len(shapes[1]))
+    for t in (0, 1):
+        for _, _, h_out, ref in work[t]:
+            assert np.array_equal(h_out.numpy(), ref)
+    enc.close()
+
+
+def test_passes_on_different_streams_do_not_overlap(native_lib, cuda_device):
+    """All passes of a handle share one activation workspace; lsc_encoder_embed_dev on two caller streams (and the
+    handle's own stream through the host call) must still give each batch its own result."""
+    import torch
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+
+    spec = W.MINILM_L6
+    enc = Encoder(spec, W.random_init(spec, 0))
+    batches = []
+    for i in range(4):
+        ids, cu = W.synthetic_token_ids(256, 128, seed=900 + i, min_len=8)
+        batches.append((ids, cu, enc.embed(ids, cu).copy()))
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = []
+    dev = [(torch.from_numpy(i).to(cuda_device), torch.from_numpy(c).to(cuda_device)) for i, c, _ in batches]
+    torch.cuda.synchronize()
+    for rep in range(3):
+        outs = []
+        for j, ((ids, cu, _), (d_ids, d_cu)) in enumerate(zip(batches, dev)):
+            d_out = torch.empty(256, spec.hidden, device=cuda_device)
+            enc.embed_dev(d_ids, d_cu, 256, int(cu[-1]), int(np.diff(cu).max()), d_out, streams[j & 1].cuda_stream)
+            outs.append(d_out)
+        host = enc.embed(batches[0][0], batches[0][1])  # the handle's own stream, behind the four passes
+        torch.cuda.synchronize()
+        assert np.array_equal(host, batches[0][2])
+        for d_out, (_, _, ref) in zip(outs, batches):
+            assert np.array_equal(d_out.cpu().numpy(), ref)
     enc.close()

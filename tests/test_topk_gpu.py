@@ -248,3 +248,177 @@ def test_bad_arguments_raise(native_lib, cuda_device):
     with pytest.raises(NativeError):
         ix.search(np.zeros((1, 64), np.float32), 129)
     ix.close()
+
+
+def test_batched_delete_matches_a_host_model(native_lib, cuda_device):
+    """lsc_index_delete applies a whole batch with one gather kernel; the surviving table must be what deleting
+    one id at a time gives (JdbcWriter.java:139-179 deletes per record): same size, and a search over it
+    returns exactly the oracle's answer over the surviving rows - including chains where the row moved into a
+    freed slot is itself deleted, or moved again, later in the same call."""
+    from langstream_b200._native import Index
+    from oracle import topk_oracle
+
+    dim, n = 128, 6000
+    rng = np.random.default_rng(5)
+    rows = _quantised(n, dim, 11)
+    ids = np.arange(n, dtype=np.int64) * 7 + 1
+    ix = Index(dim, capacity=n)
+    ix.upsert(ids, rows)
+    alive = dict(zip(ids.tolist(), range(n)))
+    for batch in (np.concatenate([ids[-40:], ids[:25], [999_999_999]]),      # the tail itself + the head + unknown id
+                  rng.choice(ids[25:-40], 1500, replace=False),             # a large random batch
+                  np.concatenate([ids[3000:3010], ids[3000:3010]])):        # ids repeated inside one call
+        ix.delete(batch)
+        for i in batch.tolist():
+            alive.pop(int(i), None)
+        assert len(ix) == len(alive)
+        keep = np.fromiter(alive.values(), dtype=np.int64)
+        q = _quantised(9, dim, 100 + len(alive))
+        got_ids, got_sc = ix.search(q, 10)
+        full = topk_oracle.scores_numpy(rows, q)
+        masked = np.full_like(full, -np.inf)
+        masked[:, keep] = full[:, keep]
+        # map returned ids back to original row numbers; the order among exact ties follows storage slots, which
+        # deletes permute, so ties are exempt exactly as the parity rule says
+        got_rows = np.where(got_ids >= 0, (got_ids - 1) // 7, -1)
+        assert all(int(i) in alive for i in got_ids.reshape(-1) if i >= 0)
+        topk_oracle.assert_topk_matches(got_rows, got_sc, masked, 10, tol=TOL)
+    # re-insert some deleted ids: they append at the end and are found again
+    back = ids[:25]
+    ix.upsert(back, rows[:25])
+    got_ids, got_sc = ix.search(rows[3], 1)
+    assert got_ids[0, 0] == ids[3] and abs(got_sc[0, 0] - 1.0) < 1e-2
+    ix.close()
+
+
+def test_merge_orders_duplicate_rows_like_one_index(native_lib, cuda_device):
+    """Crawled corpora hold duplicate chunks: equal scores across shards must come back in global storage order
+    (shard first, then position), exactly as the unsharded index orders them - also at the k boundary."""
+    import torch
+    from langstream_b200._native import Index, topk_merge_dev
+
+    dim, B, k, n = 64, 5, 10, 3000
+    base = _quantised(40, dim, 21)
+    rng = np.random.default_rng(22)
+    rows = base[rng.integers(0, 40, n)]          # every row is one of 40 vectors: ~75 copies of each
+    q = base[:B]
+    whole = Index(dim)
+    whole.upsert(np.arange(n), rows)
+    want_ids, want_sc = whole.search(q, k)
+    cuts = [0, 700, 1500, 2300, n]
+    parts = []
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        p = Index(dim)
+        p.upsert(np.arange(a, b), rows[a:b])
+        parts.append(p)
+    dq = torch.from_numpy(q).to(cuda_device)
+    st = torch.cuda.current_stream().cuda_stream
+    ids = torch.empty(len(parts), B, k, dtype=torch.int64, device=cuda_device)
+    sc = torch.empty(len(parts), B, k, dtype=torch.float32, device=cuda_device)
+    for p in range(len(parts)):
+        parts[p].search_dev(dq, B, k, ids[p], sc[p], st)
+    out_ids = torch.empty(B, k, dtype=torch.int64, device=cuda_device)
+    out_sc = torch.empty(B, k, dtype=torch.float32, device=cuda_device)
+    topk_merge_dev(ids, sc, len(parts), B, k, out_ids, out_sc, st)
+    torch.cuda.synchronize()
+    assert (out_ids.cpu().numpy() == want_ids).all()
+    assert np.array_equal(out_sc.cpu().numpy(), want_sc)
+    for p in parts + [whole]:
+        p.close()
+
+
+def test_searches_on_different_streams_do_not_overlap(native_lib, cuda_device):
+    """The index handle's query / candidate scratch is shared by all calls: lsc_index_search_dev on two caller
+    streams and the host call on the handle's own stream still each get their own answer."""
+    import torch
+    from langstream_b200._native import Index
+
+    dim, n, k = 384, 300_000, 10
+    g = torch.Generator(device=cuda_device).manual_seed(4)
+    rows = torch.randn(n, dim, generator=g, device=cuda_device)
+    ix = Index(dim, capacity=n)
+    ix.upsert_dev(np.arange(n, dtype=np.int64), rows, n, torch.cuda.current_stream().cuda_stream)
+    qs = [torch.randn(B, dim, generator=g, device=cuda_device) for B in (64, 3, 128, 17)]
+    want = [ix.search(q.cpu().numpy(), k) for q in qs]
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    torch.cuda.synchronize()
+    for rep in range(3):
+        outs = []
+        for j, q in enumerate(qs):
+            B = q.shape[0]
+            o_ids = torch.empty(B, k, dtype=torch.int64, device=cuda_device)
+            o_sc = torch.empty(B, k, dtype=torch.float32, device=cuda_device)
+            ix.search_dev(q, B, k, o_ids, o_sc, streams[j & 1].cuda_stream)
+            outs.append((o_ids, o_sc))
+        h_ids, h_sc = ix.search(qs[0].cpu().numpy(), k)
+        torch.cuda.synchronize()
+        assert (h_ids == want[0][0]).all()
+        for (o_ids, o_sc), (w_ids, w_sc) in zip(outs, want):
+            assert (o_ids.cpu().numpy() == w_ids).all() and np.array_equal(o_sc.cpu().numpy(), w_sc)
+    ix.close()
+
+
+@pytest.fixture(scope="module")
+def corpus_10m(native_lib, cuda_device):
+    """BASELINE configs[3]'s corpus on one GPU: 10M x 384, randn seed 42 per 1M-row chunk (bench.py's generator)."""
+    import torch
+    from langstream_b200._native import Index
+
+    n, dim, chunk = 10_000_000, 384, 1 << 20
+    ix = Index(dim, capacity=n)
+    st = torch.cuda.current_stream().cuda_stream
+    for o in range(0, n, chunk):
+        m = min(chunk, n - o)
+        g = torch.Generator(device=cuda_device).manual_seed(42 + o // chunk)
+        vec = torch.randn(m, dim, generator=g, device=cuda_device)
+        ix.upsert_dev(np.arange(o, o + m, dtype=np.int64), vec, m, st)
+    del vec
+    torch.cuda.empty_cache()
+    yield ix
+    ix.close()
+    torch.cuda.empty_cache()
+
+
+@pytest.mark.parametrize("B", [1, 64, 1024])
+def test_config4_full_size_10m(corpus_10m, cuda_device, B):
+    """BASELINE configs[3] / SURVEY.md 8(d) config 4 at its own size: 10M x 384, k = 10, B = 1 / 64 / 1024 (the
+    last one is the only check that runs topk_scan_rows_kernel<2>, the CTA-pair scan, over a full-length corpus).
+    Checker: lsc_index_scores_naive_dev (exact fp32 dot products on CUDA cores over the same bf16 operands) in
+    chunks of 16 queries + a plain top-k of those scores.  Rule: ids identical except ties within 1e-5."""
+    import json
+    import torch
+
+    ix, n, dim, k = corpus_10m, 10_000_000, 384, 10
+    st = torch.cuda.current_stream().cuda_stream
+    q = torch.randn(B, dim, generator=torch.Generator(device=cuda_device).manual_seed(43), device=cuda_device)
+    out_ids = torch.empty(B, k, dtype=torch.int64, device=cuda_device)
+    out_sc = torch.empty(B, k, dtype=torch.float32, device=cuda_device)
+    ix.search_dev(q, B, k, out_ids, out_sc, st)
+    torch.cuda.synchronize()
+    full = torch.empty(16, n, dtype=torch.float32, device=cuda_device)
+    mismatches, worst_score, worst_rank = 0, 0.0, 0.0
+    for b0 in range(0, B, 16):
+        nb = min(16, B - b0)
+        ix.scores_naive_dev(q[b0:b0 + nb].contiguous(), nb, full, st)
+        view = full.view(-1)[: nb * n].view(nb, n)
+        ref_sc, ref_ids = torch.topk(view, k, dim=1)
+        got_ids, got_sc = out_ids[b0:b0 + nb], out_sc[b0:b0 + nb]
+        true_sc = torch.gather(view, 1, got_ids)               # ids are row numbers here
+        worst_score = max(worst_score, (true_sc - got_sc).abs().max().item())
+        worst_rank = max(worst_rank, (true_sc - ref_sc).abs().max().item())
+        mismatches += int((got_ids != ref_ids).sum().item())
+        srt = torch.sort(got_ids, dim=1).values
+        assert (srt[:, 1:] != srt[:, :-1]).all(), "duplicate ids in a result list"
+        assert (got_sc[:, 1:] <= got_sc[:, :-1]).all(), "result list not sorted best first"
+    rec = {"case": f"topk_10Mx384_B{B}_k10", "queries": B, "id_mismatches_all_within_tie_tol": mismatches,
+           "max_abs_score_err": worst_score, "max_abs_rank_score_gap": worst_rank, "tol": TOL}
+    print("PARITY", json.dumps(rec))
+    out = Path(__file__).resolve().parents[1] / "gpurun_out"
+    try:
+        out.mkdir(exist_ok=True)
+        with open(out / "parity_margins.jsonl", "a") as f:
+            f.write(json.dumps(rec) + "\n")
+    except OSError:
+        pass
+    assert worst_score <= TOL, f"returned scores off by {worst_score}"
+    assert worst_rank <= TOL, f"a returned row is not within the tie tolerance of the oracle's row at its rank ({worst_rank})"
