@@ -43,6 +43,8 @@ extern "C" {
 
 typedef struct lsc_encoder lsc_encoder;
 typedef struct lsc_index lsc_index;
+typedef struct lsc_exchange lsc_exchange;
+typedef struct lsc_sharded_index lsc_sharded_index;
 
 /* ---- library ---------------------------------------------------------------------------- */
 
@@ -246,6 +248,68 @@ int lsc_topk_merge_dev(const int64_t* d_ids, const float* d_scores, int32_t part
 int lsc_topk_search_static_dev(const void* d_rows_bf16, const int64_t* d_row_ids, int64_t n_rows,
                                int32_t dim, const float* d_queries, int32_t B, int32_t k,
                                int64_t* d_out_ids, float* d_out_scores, void* stream);
+
+/* ---- row-sharded corpus: one shard per GPU ------------------------------------------------------ */
+
+/*
+ * No counterpart in the single-node reference (HerdDB answers `ORDER BY cosine_similarity(...) LIMIT k` inside one
+ * JVM, AI/ai/langstream/ai/agents/datasource/impl/JdbcDataSourceProvider.java:103-124); this is the multi-GPU
+ * form of the same query: the table's rows are spread over the GPUs, every GPU scans its shard and the per-shard
+ * top-k lists are merged.
+ *
+ * lsc_exchange = one GPU's end of the step in between: a receive buffer other GPUs of the NVLink domain store
+ * their (score, id) records into.  The scan kernel of lsc_index_search_sharded_dev writes its shard's lists
+ * straight into every peer's buffer (peer-to-peer stores), raises a flag per query, and merges the peers' lists
+ * as their flags arrive - one kernel launch per pass over the corpus, no collective call.  world <= 8,
+ * max_queries = largest slice of a batch exchanged at once (larger batches are cut into slices).
+ *   - GPUs driven by ONE process: create one endpoint per GPU, then lsc_exchange_connect_local (or simply use
+ *     lsc_sharded_index_*, which does all of this).
+ *   - one process per GPU (one agent pod / torchrun rank per GPU): every rank creates its endpoint, publishes
+ *     the LSC_EXCHANGE_HANDLE_BYTES from lsc_exchange_ipc_handle to the others over any channel they share and
+ *     calls lsc_exchange_connect_ipc with all ranks' handles in rank order (its own slot is ignored).
+ */
+#define LSC_EXCHANGE_HANDLE_BYTES 64
+int lsc_exchange_create(int device, int32_t rank, int32_t world, int32_t max_queries, lsc_exchange** out);
+int lsc_exchange_ipc_handle(lsc_exchange* x, void* handle_out);
+int lsc_exchange_connect_ipc(lsc_exchange* x, const void* all_handles);
+int lsc_exchange_connect_local(lsc_exchange** endpoints, int32_t world);
+void lsc_exchange_destroy(lsc_exchange* x);
+
+/*
+ * Search this GPU's shard AND merge with the other shards: every rank of the group calls it with the same
+ * queries (device fp32 B x dim), B and k (<= 32), in the same order of calls; every rank receives the same
+ * merged [B][k] ids / scores.  Equal scores come back in (rank, position inside the rank's list) order, which is
+ * the storage order of one unsharded index when rank r holds the r-th contiguous range of rows.  Enqueued on
+ * `stream`; does not synchronise.  A rank that never makes the matching call leaves its peers waiting: after 30 s
+ * they give up and the next lsc_index_check / host-buffer search on that handle reports it.
+ */
+int lsc_index_search_sharded_dev(lsc_index* idx, lsc_exchange* x, const float* d_queries, int32_t B, int32_t k,
+                                 int64_t* d_out_ids, float* d_out_scores, void* stream);
+/* Synchronises `stream` and reports (once) whether a wait inside an earlier search on this handle gave up. */
+int lsc_index_check(lsc_index* idx, void* stream);
+
+/*
+ * The whole sharded table behind one handle, for a host that drives several GPUs from one process - the shape a
+ * Java datasource needs: QueryStepDataSource.fetchData is called from one JVM thread
+ * (AI/com/datastax/oss/streaming/ai/datasource/QueryStepDataSource.java:22-37).  The library keeps one worker
+ * thread, stream, lsc_index shard and lsc_exchange endpoint per device; calls are forwarded to all of them and
+ * return when every shard is done.  New ids are placed on the shard with the fewest rows; an existing id is
+ * replaced where it lives.  Same semantics otherwise as lsc_index_upsert / _delete / _search (host buffers,
+ * blocking); k <= 32.  `devices` may name the same GPU more than once (tests on a single GPU).
+ * Replaces: the JDBC datasource + writer pair (JdbcDataSourceProvider.java:103-124,
+ * VEC/jdbc/JdbcWriter.java:139-179) for a table that does not fit, or should not be scanned by, one GPU.
+ */
+int lsc_sharded_index_create(int32_t dim, int64_t capacity_per_shard, const int* devices, int32_t ndev,
+                             lsc_sharded_index** out);
+int lsc_sharded_index_upsert(lsc_sharded_index* s, const int64_t* ids, const float* vecs, int32_t n);
+int lsc_sharded_index_delete(lsc_sharded_index* s, const int64_t* ids, int32_t n);
+int64_t lsc_sharded_index_size(const lsc_sharded_index* s);
+int lsc_sharded_index_search(lsc_sharded_index* s, const float* queries, int32_t B, int32_t k, int64_t* out_ids,
+                             float* out_scores);
+int32_t lsc_sharded_index_shards(const lsc_sharded_index* s);
+/* The shard living on the i-th device of the handle (borrowed: do not destroy), e.g. for lsc_index_upsert_dev. */
+lsc_index* lsc_sharded_index_shard(lsc_sharded_index* s, int32_t i);
+void lsc_sharded_index_destroy(lsc_sharded_index* s);
 
 /* Same measurement aid as lsc_encoder_set_profiling; classes: 0 normalise (queries / upserted rows),
  * 1 scan, 2 merge. */

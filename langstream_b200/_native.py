@@ -72,6 +72,21 @@ SIGNATURES = {
     "lsc_index_search_dev": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "lsc_index_scores_naive_dev": (C.c_int, [_vp, _vp, _i32, _vp, _vp]),
     "lsc_topk_merge_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "lsc_exchange_create": (C.c_int, [C.c_int, _i32, _i32, _i32, C.POINTER(_vp)]),
+    "lsc_exchange_ipc_handle": (C.c_int, [_vp, _vp]),
+    "lsc_exchange_connect_ipc": (C.c_int, [_vp, _vp]),
+    "lsc_exchange_connect_local": (C.c_int, [C.POINTER(_vp), _i32]),
+    "lsc_exchange_destroy": (None, [_vp]),
+    "lsc_index_search_sharded_dev": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp]),
+    "lsc_index_check": (C.c_int, [_vp, _vp]),
+    "lsc_sharded_index_create": (C.c_int, [_i32, _i64, C.POINTER(C.c_int), _i32, C.POINTER(_vp)]),
+    "lsc_sharded_index_upsert": (C.c_int, [_vp, _vp, _vp, _i32]),
+    "lsc_sharded_index_delete": (C.c_int, [_vp, _vp, _i32]),
+    "lsc_sharded_index_size": (_i64, [_vp]),
+    "lsc_sharded_index_search": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _vp]),
+    "lsc_sharded_index_shards": (_i32, [_vp]),
+    "lsc_sharded_index_shard": (_vp, [_vp, _i32]),
+    "lsc_sharded_index_destroy": (None, [_vp]),
     "lsc_topk_search_static_dev": (C.c_int, [_vp, _vp, _i64, _i32, _vp, _i32, _i32, _vp, _vp, _vp]),
     "lsc_index_set_profiling": (C.c_int, [_vp, C.c_int]),
     "lsc_index_read_profile": (C.c_int, [_vp, _vp, _vp, _i32]),
@@ -261,6 +276,16 @@ class Index:
     def search_dev(self, d_queries, B, k, d_out_ids, d_out_scores, stream=0):
         check(lib().lsc_index_search_dev(self._h, _ptr(d_queries), B, k, _ptr(d_out_ids), _ptr(d_out_scores), stream))
 
+    def search_sharded_dev(self, exchange, d_queries, B, k, d_out_ids, d_out_scores, stream=0):
+        """This shard's part of a search over a row-sharded table; every rank of `exchange`'s group makes the same
+        call and every rank receives the merged [B, k] result (lsc_index_search_sharded_dev)."""
+        check(lib().lsc_index_search_sharded_dev(self._h, exchange._h, _ptr(d_queries), B, k, _ptr(d_out_ids),
+                                                 _ptr(d_out_scores), stream))
+
+    def check(self, stream=0):
+        """Synchronise `stream` and raise if a wait inside an earlier search gave up (lsc_index_check)."""
+        check(lib().lsc_index_check(self._h, stream))
+
     def scores_naive_dev(self, d_queries, B, d_scores, stream=0):
         check(lib().lsc_index_scores_naive_dev(self._h, _ptr(d_queries), B, _ptr(d_scores), stream))
 
@@ -281,14 +306,109 @@ class Index:
         return {c: (float(ms[i]), int(cnt[i])) for i, c in enumerate(self.PROFILE_CLASSES)}
 
     def close(self):
-        if self._h:
+        if self._h and getattr(self, "_owned", True):
             lib().lsc_index_destroy(self._h)
-            self._h = None
+        self._h = None
 
     def __del__(self):
         try:
             self.close()
         except Exception:
+            pass
+
+
+class Exchange:
+    """One GPU's end of the sharded search's candidate exchange (lsc_exchange)."""
+
+    HANDLE_BYTES = 64
+
+    def __init__(self, device: int, rank: int, world: int, max_queries: int = 1024):
+        h = _vp()
+        check(lib().lsc_exchange_create(device, rank, world, max_queries, C.byref(h)))
+        self._h = h
+        self.rank, self.world, self.device = rank, world, device
+
+    def ipc_handle(self) -> bytes:
+        buf = C.create_string_buffer(self.HANDLE_BYTES)
+        check(lib().lsc_exchange_ipc_handle(self._h, buf))
+        return buf.raw
+
+    def connect_ipc(self, handles) -> None:
+        """handles: every rank's ipc_handle() bytes, in rank order."""
+        blob = b"".join(handles)
+        if len(blob) != self.world * self.HANDLE_BYTES:
+            raise ValueError("one 64-byte handle per rank is needed")
+        check(lib().lsc_exchange_connect_ipc(self._h, blob))
+
+    @staticmethod
+    def connect_local(endpoints) -> None:
+        arr = (_vp * len(endpoints))(*[e._h for e in endpoints])
+        check(lib().lsc_exchange_connect_local(arr, len(endpoints)))
+
+    def close(self):
+        if self._h:
+            lib().lsc_exchange_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+
+class ShardedIndex:
+    """A table spread over several GPUs behind one handle and one host thread (lsc_sharded_index)."""
+
+    def __init__(self, dim: int, devices, capacity_per_shard: int = 0):
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        h = _vp()
+        check(lib().lsc_sharded_index_create(dim, capacity_per_shard, devs, len(devices), C.byref(h)))
+        self._h = h
+        self.dim = dim
+        self.devices = list(devices)
+
+    def __len__(self) -> int:
+        return int(lib().lsc_sharded_index_size(self._h))
+
+    def upsert(self, ids, vecs):
+        ids = _np.ascontiguousarray(ids, _np.int64)
+        vecs = _np.ascontiguousarray(vecs, _np.float32).reshape(ids.size, -1)
+        if vecs.shape[1] != self.dim:
+            raise ValueError(f"vectors have dimension {vecs.shape[1]}, index has {self.dim}")
+        check(lib().lsc_sharded_index_upsert(self._h, _ptr(ids), _ptr(vecs), int(ids.size)))
+
+    def delete(self, ids):
+        ids = _np.ascontiguousarray(ids, _np.int64)
+        check(lib().lsc_sharded_index_delete(self._h, _ptr(ids), int(ids.size)))
+
+    def search(self, queries, k: int):
+        q = _np.ascontiguousarray(queries, _np.float32).reshape(-1, self.dim)
+        B = q.shape[0]
+        ids = _np.empty((B, k), _np.int64)
+        scores = _np.empty((B, k), _np.float32)
+        check(lib().lsc_sharded_index_search(self._h, _ptr(q), B, k, _ptr(ids), _ptr(scores)))
+        return ids, scores
+
+    def shard(self, i: int) -> "Index":
+        """The i-th shard as a borrowed Index (closing it does not destroy the shard)."""
+        h = lib().lsc_sharded_index_shard(self._h, i)
+        if not h:
+            raise IndexError(i)
+        ix = Index.__new__(Index)
+        ix._h, ix.dim, ix.device = _vp(h), self.dim, self.devices[i]
+        ix._owned = False
+        return ix
+
+    def close(self):
+        if self._h:
+            lib().lsc_sharded_index_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
             pass
 
 

@@ -9,12 +9,14 @@
 #include <algorithm>
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
 #include <vector>
 
 #include "common.h"
+#include "exchange.h"
 #include "topk.h"
 
 using namespace lsc;
@@ -40,6 +42,16 @@ struct lsc_index {
     CUtensorMap tmapQ;
     float* d_cand_scores = nullptr;
     int32_t* d_cand_idx = nullptr;
+    // state of the fused scan (topk_fuse.cuh): per-query shared thresholds [cap_q], one arrival counter per
+    // scan launch of a batch [cap_q / 128], and a status word that a wait which gave up sets
+    int32_t* d_gthr = nullptr;
+    unsigned* d_done = nullptr;
+    int32_t* d_status = nullptr;
+    bool shares_gpu = false;  // this shard runs beside other shards on the same GPU (SM budget set): plain launches
+    // shard-local [B][k] results in front of the stand-alone exchange (query-major scan, 16 < k <= 32)
+    int64_t* d_loc_ids = nullptr;
+    float* d_loc_scores = nullptr;
+    int64_t cap_loc = 0;
     int64_t* d_out_ids = nullptr;      // staging for host results
     float* d_out_scores = nullptr;
     int64_t cap_out = 0;
@@ -120,6 +132,12 @@ int ensure_query_buffers(lsc_index* ix, int B, int k) {
         ix->d_qbf = nullptr;
         ix->cap_q = 0;
         LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_qbf), static_cast<size_t>(bpad) * ix->dim * sizeof(__nv_bfloat16)));
+        if (ix->d_gthr) cudaFree(ix->d_gthr);
+        if (ix->d_done) cudaFree(ix->d_done);
+        ix->d_gthr = nullptr;
+        ix->d_done = nullptr;
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_gthr), static_cast<size_t>(bpad) * sizeof(int32_t)));
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_done), static_cast<size_t>(bpad / TK_QROWS) * sizeof(unsigned)));
         ix->cap_q = bpad;
         LSC_TRY(make_tmap_bf16_sw128(&ix->tmapQ, ix->d_qbf, static_cast<uint64_t>(bpad), ix->dim, TK_QROWS));
     }
@@ -142,11 +160,13 @@ int ensure_query_buffers(lsc_index* ix, int B, int k) {
         nlaunch += _n;                \
     } while (0)
 
-// queries (device fp32 [B,dim]) -> top-k ids/scores (device), all on `st`.
-int search_dev(lsc_index* ix, const float* d_queries, int B, int k, int64_t* d_out_ids, float* d_out_scores,
-               cudaStream_t st) {
+// queries (device fp32 [B,dim]) -> top-k ids/scores (device), all on `st`.  With an exchange endpoint `xg` the
+// shard's lists are exchanged with the peer GPUs and the outputs hold the merged result over all shards.
+int search_dev(lsc_index* ix, lsc_exchange* xg, const float* d_queries, int B, int k, int64_t* d_out_ids,
+               float* d_out_scores, cudaStream_t st) {
     int64_t nlaunch = 0;
-    if (ix->n == 0) {
+    const bool sharded = xg != nullptr && xg->world > 1;
+    if (ix->n == 0 && !sharded) {
         LSC_LAUNCH(2, fill_empty_launch(d_out_ids, d_out_scores, static_cast<size_t>(B) * k, st));
         ix->launches += nlaunch;
         return LSC_OK;
@@ -155,37 +175,85 @@ int search_dev(lsc_index* ix, const float* d_queries, int B, int k, int64_t* d_o
     LSC_TRY(order_after_previous(ix, st));
     const int qblk = B > TK_QROWS ? 2 * TK_QROWS : TK_QROWS;
     const int bpad = (B + qblk - 1) / qblk * qblk;
-    LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st));
+    LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st, ix->d_gthr, bpad, ix->d_done,
+                                        bpad / TK_QROWS));
+    TopkFuse fuse;
+    fuse.status = ix->d_status;
+    fuse.slot_ids = ix->d_ids;
+    fuse.out_ids = d_out_ids;
+    fuse.out_scores = d_out_scores;
+    fuse.cooperative = ix->shares_gpu ? 0 : 1;
+    if (sharded) exchange_fill(xg, &fuse, ++xg->epoch);
     const int n_rows = static_cast<int>(ix->n);
-    const bool rows_kernel = topk_scan_rows_supported(ix->dim, k);
-    const bool pair = rows_kernel && B > TK_QROWS && topk_scan_rows_pair_supported(ix->dim, k, ix->num_sms);
-    const int grid = pair ? topk_scan_rows_pair_grid(n_rows, ix->num_sms)
-                          : (rows_kernel ? topk_scan_rows_grid(n_rows, ix->num_sms) : topk_scan_grid(n_rows, ix->num_sms));
-    if (pair) {
-        // 256 queries per pass over the corpus (two query blocks of the candidate scratch per launch)
-        for (int q0 = 0; q0 < B; q0 += 2 * TK_QROWS) {
-            const int nq = std::min(2 * TK_QROWS, B - q0);
+    const bool rows_kernel = n_rows > 0 && topk_scan_rows_supported(ix->dim, k);
+    if (rows_kernel) {
+        // row-major scan: thresholds shared between the CTAs, and the merge of the per-CTA lists (plus the
+        // exchange with the peers) inside the scan launch - one launch per pass over the corpus
+        static const bool unfused = getenv("LSC_TOPK_UNFUSED") != nullptr;  // debug: separate merge launch
+        static const bool no_gthr = getenv("LSC_TOPK_NO_SHARED_THRESHOLDS") != nullptr;  // debug
+        const bool pair = B > TK_QROWS && topk_scan_rows_pair_supported(ix->dim, k, ix->num_sms);
+        const int grid = pair ? topk_scan_rows_pair_grid(n_rows, ix->num_sms) : topk_scan_rows_grid(n_rows, ix->num_sms);
+        const bool fused = !unfused || sharded;
+        fuse.gthr = no_gthr ? nullptr : ix->d_gthr;
+        const int step = pair ? 2 * TK_QROWS : TK_QROWS;
+        int pass = 0;
+        for (int q0 = 0; q0 < B; q0 += step, ++pass) {
+            const int nq = std::min(step, B - q0);
             const size_t off = static_cast<size_t>(q0 / TK_QROWS) * grid * TK_QROWS * k;
-            LSC_LAUNCH(1, topk_scan_rows_pair_launch(ix->tmapQ, ix->tmapC128, q0, nq, n_rows, ix->dim, k, grid,
-                                                     ix->d_cand_scores + off, ix->d_cand_idx + off, st));
-        }
-    } else {
-        for (int qb = 0; qb * TK_QROWS < B; ++qb) {
-            const int nq = std::min(TK_QROWS, B - qb * TK_QROWS);
-            const size_t off = static_cast<size_t>(qb) * grid * TK_QROWS * k;
-            if (rows_kernel)
-                LSC_LAUNCH(1, topk_scan_rows_launch(ix->tmapQ, ix->tmapC128, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
-                                                    ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+            fuse.done = fused ? ix->d_done + pass : nullptr;
+            if (pair)
+                LSC_LAUNCH(1, topk_scan_rows_pair_launch(ix->tmapQ, ix->tmapC128, q0, nq, n_rows, ix->dim, k, grid,
+                                                         ix->d_cand_scores + off, ix->d_cand_idx + off, fuse, st));
             else
+                LSC_LAUNCH(1, topk_scan_rows_launch(ix->tmapQ, ix->tmapC128, q0, nq, n_rows, ix->dim, k, grid,
+                                                    ix->d_cand_scores + off, ix->d_cand_idx + off, fuse, st));
+        }
+        if (!fused)
+            LSC_LAUNCH(2, topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, d_out_ids,
+                                                 d_out_scores, st));
+    } else {
+        // query-major scan (k > 16), or an empty shard: shard-local lists first, then the exchange on its own
+        int64_t* loc_ids = d_out_ids;
+        float* loc_scores = d_out_scores;
+        if (sharded) {
+            const int64_t nout = static_cast<int64_t>(B) * k;
+            if (nout > ix->cap_loc) {
+                int64_t c1 = ix->cap_loc, c2 = ix->cap_loc;
+                LSC_TRY(grow_buf(&ix->d_loc_ids, &c1, nout, 4096));
+                LSC_TRY(grow_buf(&ix->d_loc_scores, &c2, nout, 4096));
+                ix->cap_loc = std::min(c1, c2);
+            }
+            loc_ids = ix->d_loc_ids;
+            loc_scores = ix->d_loc_scores;
+        }
+        if (n_rows == 0) {
+            LSC_LAUNCH(2, fill_empty_launch(loc_ids, loc_scores, static_cast<size_t>(B) * k, st));
+        } else {
+            const int grid = topk_scan_grid(n_rows, ix->num_sms);
+            for (int qb = 0; qb * TK_QROWS < B; ++qb) {
+                const int nq = std::min(TK_QROWS, B - qb * TK_QROWS);
+                const size_t off = static_cast<size_t>(qb) * grid * TK_QROWS * k;
                 LSC_LAUNCH(1, topk_scan_launch(ix->tmapQ, ix->tmapC, qb * TK_QROWS, nq, n_rows, ix->dim, k, grid,
                                                ix->d_cand_scores + off, ix->d_cand_idx + off, st));
+            }
+            LSC_LAUNCH(2, topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, loc_ids, loc_scores, st));
         }
+        if (sharded) LSC_LAUNCH(2, topk_exchange_launch(loc_ids, loc_scores, B, k, fuse, st));
     }
-    LSC_LAUNCH(2, topk_merge_scan_launch(ix->d_cand_scores, ix->d_cand_idx, grid, B, k, ix->d_ids, d_out_ids,
-                                      d_out_scores, st));
     LSC_TRY(mark_pass_end(ix, st));
     ix->launches += nlaunch;
     return LSC_OK;
+}
+
+// A wait inside the fused scan gave up (topk_fuse.cuh): surface it where the host synchronises anyway.
+int check_status(lsc_index* ix, cudaStream_t st) {
+    int32_t h = 0;
+    LSC_CUDA(cudaMemcpyAsync(&h, ix->d_status, sizeof(h), cudaMemcpyDeviceToHost, st));
+    LSC_CUDA(cudaStreamSynchronize(st));
+    if (h == 0) return LSC_OK;
+    cudaMemsetAsync(ix->d_status, 0, sizeof(int32_t), st);
+    return fail(LSC_E_CUDA, h == 2 ? "top-k: a peer GPU's candidates did not arrive within 30 s (is every rank calling the search?)"
+                                   : "top-k: the scan's CTAs did not all arrive (grid barrier timed out)");
 }
 
 int upsert_dev(lsc_index* ix, const int64_t* ids, const float* d_vecs, int n, cudaStream_t st) {
@@ -232,6 +300,18 @@ int upsert_dev(lsc_index* ix, const int64_t* ids, const float* d_vecs, int n, cu
 }  // namespace
 }  // namespace lsc
 
+namespace lsc {
+// Shards that share one GPU (sharded_index.cu) split its SMs: their fused scans wait for each other's candidates
+// and therefore have to be resident side by side.
+void index_set_sm_budget(lsc_index* ix, int sms) {
+    std::lock_guard<std::mutex> lock(ix->mu);
+    ix->num_sms = sms;
+    ix->shares_gpu = true;
+    ix->cap_cand = 0;  // the candidate scratch is sized by the grid; let it be re-derived
+}
+int index_sm_count(const lsc_index* ix) { return ix->num_sms; }
+}  // namespace lsc
+
 extern "C" {
 
 void lsc_index_destroy(lsc_index* ix) {
@@ -239,7 +319,8 @@ void lsc_index_destroy(lsc_index* ix) {
     cudaSetDevice(ix->device);
     cudaDeviceSynchronize();
     void* bufs[] = {ix->d_rows, ix->d_ids, ix->d_q32, ix->d_qbf, ix->d_cand_scores, ix->d_cand_idx,
-                    ix->d_out_ids, ix->d_out_scores, ix->d_slots};
+                    ix->d_out_ids, ix->d_out_scores, ix->d_slots, ix->d_gthr, ix->d_done, ix->d_status,
+                    ix->d_loc_ids, ix->d_loc_scores};
     for (void* p : bufs)
         if (p) cudaFree(p);
     if (ix->stream) cudaStreamDestroy(ix->stream);
@@ -264,6 +345,15 @@ int lsc_index_create(int32_t dim, int64_t capacity, int device, lsc_index** out)
     lsc_index* ix = new lsc_index();
     ix->device = device;
     ix->num_sms = prop.multiProcessorCount;
+    // LSC_TOPK_MAX_CTAS (testing aid): cap the scan's grid, so that several shards / processes sharing one GPU can
+    // run their fused scans - which wait for each other's candidates - side by side
+    if (const char* cap = getenv("LSC_TOPK_MAX_CTAS")) {
+        const int c = atoi(cap) & ~1;
+        if (c >= 2 && c < ix->num_sms) {
+            ix->num_sms = c;
+            ix->shares_gpu = true;
+        }
+    }
     ix->dim = dim;
     int rc = LSC_OK;
     cudaError_t ce = cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking);
@@ -271,6 +361,11 @@ int lsc_index_create(int32_t dim, int64_t capacity, int device, lsc_index** out)
     if (rc == LSC_OK) {
         ce = cudaEventCreateWithFlags(&ix->ev_last, cudaEventDisableTiming);
         if (ce != cudaSuccess) rc = fail_cuda(ce, "cudaEventCreateWithFlags", __FILE__, __LINE__);
+    }
+    if (rc == LSC_OK) {
+        ce = cudaMalloc(reinterpret_cast<void**>(&ix->d_status), sizeof(int32_t));
+        if (ce == cudaSuccess) ce = cudaMemset(ix->d_status, 0, sizeof(int32_t));
+        if (ce != cudaSuccess) rc = fail_cuda(ce, "cudaMalloc(status)", __FILE__, __LINE__);
     }
     if (rc == LSC_OK) rc = grow_rows(ix, std::max<int64_t>(capacity, 1));
     if (rc != LSC_OK) {
@@ -397,7 +492,35 @@ int lsc_index_search_dev(lsc_index* ix, const float* d_queries, int32_t B, int32
         return fail(LSC_E_INVALID, "lsc_index_search_dev: null pointer");
     std::lock_guard<std::mutex> lock(ix->mu);
     LSC_CUDA(cudaSetDevice(ix->device));
-    return search_dev(ix, d_queries, B, k, d_out_ids, d_out_scores, static_cast<cudaStream_t>(stream));
+    return search_dev(ix, nullptr, d_queries, B, k, d_out_ids, d_out_scores, static_cast<cudaStream_t>(stream));
+}
+
+int lsc_index_search_sharded_dev(lsc_index* ix, lsc_exchange* xg, const float* d_queries, int32_t B, int32_t k,
+                                 int64_t* d_out_ids, float* d_out_scores, void* stream) {
+    if (ix == nullptr || xg == nullptr) return fail(LSC_E_INVALID, "lsc_index_search_sharded_dev: null handle");
+    if (B < 0) return fail(LSC_E_INVALID, "lsc_index_search_sharded_dev: negative B");
+    if (k < 1 || k > TKX_MAX_XK) return fail(LSC_E_UNSUPPORTED, "lsc_index_search_sharded_dev: k must be in [1,32]");
+    if (B == 0) return LSC_OK;
+    if (d_queries == nullptr || d_out_ids == nullptr || d_out_scores == nullptr)
+        return fail(LSC_E_INVALID, "lsc_index_search_sharded_dev: null pointer");
+    if (!xg->connected) return fail(LSC_E_INVALID, "lsc_index_search_sharded_dev: the exchange endpoint is not connected to its peers");
+    if (xg->device != ix->device) return fail(LSC_E_INVALID, "lsc_index_search_sharded_dev: index and exchange endpoint live on different GPUs");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    // slices of at most xB queries: the receive buffers hold one slice (every rank cuts the batch alike)
+    for (int b0 = 0; b0 < B; b0 += xg->xB) {
+        const int nb = std::min<int>(xg->xB, B - b0);
+        LSC_TRY(search_dev(ix, xg, d_queries + static_cast<size_t>(b0) * ix->dim, nb, k, d_out_ids + static_cast<size_t>(b0) * k,
+                           d_out_scores + static_cast<size_t>(b0) * k, static_cast<cudaStream_t>(stream)));
+    }
+    return LSC_OK;
+}
+
+int lsc_index_check(lsc_index* ix, void* stream) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_check: index is null");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    return check_status(ix, static_cast<cudaStream_t>(stream));
 }
 
 int lsc_index_search(lsc_index* ix, const float* queries, int32_t B, int32_t k, int64_t* out_ids,
@@ -419,11 +542,10 @@ int lsc_index_search(lsc_index* ix, const float* queries, int32_t B, int32_t k, 
         ix->cap_out = std::min(c1, c2);
     }
     LSC_CUDA(cudaMemcpyAsync(ix->d_q32, queries, static_cast<size_t>(B) * ix->dim * sizeof(float), cudaMemcpyHostToDevice, ix->stream));
-    LSC_TRY(search_dev(ix, ix->d_q32, B, k, ix->d_out_ids, ix->d_out_scores, ix->stream));
+    LSC_TRY(search_dev(ix, nullptr, ix->d_q32, B, k, ix->d_out_ids, ix->d_out_scores, ix->stream));
     LSC_CUDA(cudaMemcpyAsync(out_ids, ix->d_out_ids, static_cast<size_t>(nout) * sizeof(int64_t), cudaMemcpyDeviceToHost, ix->stream));
     LSC_CUDA(cudaMemcpyAsync(out_scores, ix->d_out_scores, static_cast<size_t>(nout) * sizeof(float), cudaMemcpyDeviceToHost, ix->stream));
-    LSC_CUDA(cudaStreamSynchronize(ix->stream));
-    return LSC_OK;
+    return check_status(ix, ix->stream);
 }
 
 int lsc_index_scores_naive_dev(lsc_index* ix, const float* d_queries, int32_t B, float* d_scores, void* stream) {

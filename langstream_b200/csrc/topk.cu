@@ -376,9 +376,13 @@ __device__ __forceinline__ float warp_sum(float v) {
 // rows in [n, n_pad) are written as zeros (query padding).  A zero vector stays zero.
 __global__ void __launch_bounds__(256)
 normalize_rows_kernel(const float* __restrict__ src, int n, int n_pad, int dim,
-                      const int64_t* __restrict__ dst_rows, __nv_bfloat16* __restrict__ dst) {
+                      const int64_t* __restrict__ dst_rows, __nv_bfloat16* __restrict__ dst,
+                      int32_t* __restrict__ gthr, int n_gthr, unsigned* __restrict__ done, int n_done) {
     const int lane = threadIdx.x & 31;
     const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    // state of the fused scan that follows in the stream (topk_fuse.cuh)
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_gthr; i += gridDim.x * blockDim.x) gthr[i] = TKX_KEY_NEG_INF;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_done; i += gridDim.x * blockDim.x) done[i] = 0u;
     if (r >= n_pad) return;
     long long out_row = r;
     if (dst_rows != nullptr) {
@@ -439,6 +443,20 @@ move_rows_kernel(__nv_bfloat16* __restrict__ rows, int64_t* __restrict__ ids, in
     uint4* d = reinterpret_cast<uint4*>(rows + static_cast<size_t>(dst) * dim);
     for (int c = lane; c < dim / 8; c += 32) d[c] = s[c];
     if (lane == 0) ids[dst] = ids[src];
+}
+
+// Exchange + final merge for shard results that already lie in memory as [B][k] lists: one CTA per query.
+__global__ void __launch_bounds__(TKX_THREADS)
+topk_exchange_kernel(const int64_t* __restrict__ local_ids, const float* __restrict__ local_scores, int k,
+                     const __grid_constant__ TopkFuse fuse) {
+    __shared__ TopkTailSmem sm;
+    const int q = blockIdx.x;
+    if (threadIdx.x < k) {
+        sm.res_s[threadIdx.x] = local_scores[static_cast<size_t>(q) * k + threadIdx.x];
+        sm.res_i[threadIdx.x] = local_ids[static_cast<size_t>(q) * k + threadIdx.x];
+    }
+    tail_bar();
+    tail_exchange(fuse, q, k, sm);
 }
 
 __global__ void fill_empty_kernel(int64_t* ids, float* scores, size_t n) {
@@ -510,10 +528,12 @@ int topk_merge_shards_launch(const float* scores, const int64_t* ids, int parts,
 }
 
 int normalize_rows_launch(const float* src, int n, int n_pad, int dim, const int64_t* dst_rows,
-                          __nv_bfloat16* dst, cudaStream_t stream) {
+                          __nv_bfloat16* dst, cudaStream_t stream, int32_t* gthr, int n_gthr, unsigned* done,
+                          int n_done) {
     if (n_pad <= 0) return 0;
     const int wpb = 8;
-    normalize_rows_kernel<<<(n_pad + wpb - 1) / wpb, 256, 0, stream>>>(src, n, n_pad, dim, dst_rows, dst);
+    normalize_rows_kernel<<<(n_pad + wpb - 1) / wpb, 256, 0, stream>>>(src, n, n_pad, dim, dst_rows, dst, gthr, n_gthr,
+                                                                      done, n_done);
     LSC_CUDA(cudaGetLastError());
     return 1;
 }
@@ -532,6 +552,16 @@ int move_rows_launch(__nv_bfloat16* rows, int64_t* ids, int dim, const int64_t* 
     if (m <= 0) return 0;
     const int wpb = 8;
     move_rows_kernel<<<(m + wpb - 1) / wpb, 256, 0, stream>>>(rows, ids, dim, moves, m);
+    LSC_CUDA(cudaGetLastError());
+    return 1;
+}
+
+int topk_exchange_launch(const int64_t* local_ids, const float* local_scores, int B, int k, const TopkFuse& fuse,
+                         cudaStream_t stream) {
+    if (B <= 0) return 0;
+    if (k > TKX_MAX_XK || k > fuse.xk || fuse.world > TKX_MAX_WORLD || fuse.world < 2)
+        return fail(LSC_E_UNSUPPORTED, "top-k exchange: k <= 32 and 2..8 shards");
+    topk_exchange_kernel<<<B, TKX_THREADS, 0, stream>>>(local_ids, local_scores, k, fuse);
     LSC_CUDA(cudaGetLastError());
     return 1;
 }

@@ -123,7 +123,8 @@ extern "C" int lsc_topk_search_static_dev(const void* d_rows_bf16, const int64_t
     const int grid = rows_kernel ? topk_scan_rows_grid(n, s->num_sms) : topk_scan_grid(n, s->num_sms);
     int rc = normalize_rows_launch(d_queries, B, TK_QROWS, dim, nullptr, d_q, st);  // rewrites all 128 rows
     if (rc < 0) return rc;
-    rc = rows_kernel ? topk_scan_rows_launch(tmapQ, tmapC, 0, B, n, dim, k, grid, d_cand_scores, d_cand_idx, st)
+    const TopkFuse plain;  // the scan only writes its scratch; the merge below is a launch of its own
+    rc = rows_kernel ? topk_scan_rows_launch(tmapQ, tmapC, 0, B, n, dim, k, grid, d_cand_scores, d_cand_idx, plain, st)
                      : topk_scan_launch(tmapQ, tmapC, 0, B, n, dim, k, grid, d_cand_scores, d_cand_idx, st);
     if (rc < 0) return rc;
     rc = topk_merge_scan_launch(d_cand_scores, d_cand_idx, grid, B, k, d_row_ids, d_out_ids, d_out_scores, st);

@@ -30,6 +30,7 @@
 #include "common.h"
 #include "ptx.cuh"
 #include "topk.h"
+#include "topk_fuse.cuh"
 
 namespace lsc {
 
@@ -51,8 +52,10 @@ constexpr int TR_TRIG = 16;                            // compact a query once i
 // descending sort); rows are unique, so the positions are a permutation.  Lane t holds candidate t and, for
 // t < k, list entry t; the others' values are broadcast reads from shared memory, all independent.
 // ls / li / bs / bi / thr are 32-bit shared-window addresses; the caller owns the query.
+// gthr_q (may be null): the query's threshold shared between the CTAs of the grid - a raised local k-th best
+// score is published there with one atomic max (see topk_fuse.cuh).
 __device__ __forceinline__ void compact_query(uint32_t ls, uint32_t li, uint32_t bs, uint32_t bi, uint32_t thr,
-                                              int k, int n) {
+                                              int k, int n, int32_t* gthr_q) {
     const int lane = threadIdx.x & 31;
     const bool hc = lane < n, hl = lane < k;
     const float cs = hc ? lds_f32(bs + 4 * lane) : -INFINITY;
@@ -76,12 +79,18 @@ __device__ __forceinline__ void compact_query(uint32_t ls, uint32_t li, uint32_t
     if (hc && cpos < k) {
         sts_f32(ls + 4 * cpos, cs);
         sts_s32(li + 4 * cpos, cr);
-        if (cpos == k - 1) sts_f32(thr, cs);
+        if (cpos == k - 1) {
+            sts_f32(thr, cs);
+            if (gthr_q != nullptr) atomicMax(gthr_q, score_key(cs));
+        }
     }
     if (hl && epos < k) {
         sts_f32(ls + 4 * epos, es);
         sts_s32(li + 4 * epos, er);
-        if (epos == k - 1) sts_f32(thr, er >= 0 ? es : -INFINITY);
+        if (epos == k - 1) {
+            sts_f32(thr, er >= 0 ? es : -INFINITY);
+            if (gthr_q != nullptr && er >= 0) atomicMax(gthr_q, score_key(es));
+        }
     }
     __syncwarp();
 }
@@ -95,7 +104,8 @@ template <int PAIR>
 __global__ void __launch_bounds__(TR_THREADS, 1)
 topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constant__ CUtensorMap tmapC,
                       int q_row0, int nq, int n_rows, int dim, int k, int stages, uint32_t idesc,
-                      float* __restrict__ cand_scores, int32_t* __restrict__ cand_idx) {
+                      float* __restrict__ cand_scores, int32_t* __restrict__ cand_idx,
+                      const __grid_constant__ TopkFuse fuse) {
     extern __shared__ uint8_t smem_raw[];
     // aligned by pointer arithmetic on the shared array (an integer round trip would turn every access
     // through it into a generic-address one)
@@ -253,6 +263,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
         const int nchunks = (nq + 31) / 32;
         const bool scans = cg * CPW < nchunks;
         const int myq = lane * TR_SEL_WARPS + sw;  // lanes 0 .. NQ / 16 - 1: the queries this warp compacts
+        int32_t* const gthr = fuse.gthr != nullptr ? fuse.gthr + q_row0 : nullptr;
         const uint32_t lead_tempty = PAIR == 2 ? mapa_u32(bar_tempty, 0) : bar_tempty;
         int acc = 0;
         uint32_t acc_phase = 0;
@@ -264,6 +275,10 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
 #pragma unroll
             for (int cc = 0; cc < CPW; ++cc) pend[cc] = 0u;
             bool released = !scans;
+            // the other CTAs' k-th best score for this warp's queries: asked for now, used after the tile's
+            // compaction (the L2 round trip hides behind the append phase)
+            int32_t gkey = TKX_KEY_NEG_INF;
+            if (gthr != nullptr && lane < NQ / TR_SEL_WARPS && myq < nq) gkey = ld_relaxed_gpu_s32(gthr + myq);
             if (scans) {
                 mbar_wait(bar_tfull + 8 * acc, acc_phase);
                 tc_fence_after();
@@ -337,8 +352,15 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                     int n = __shfl_sync(0xffffffffu, n_my, l);
                     n = n < BUF ? n : BUF;
                     compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * BUF, buf_i + 4 * q * BUF,
-                                  thrs + 4 * q, k, n);
+                                  thrs + 4 * q, k, n, gthr != nullptr ? gthr + q : nullptr);
                     if (lane == 0) sts_s32(cnt + 4 * q, 0);
+                }
+                if (gkey > TKX_KEY_NEG_INF) {
+                    // k rows score >= key_score(gkey) somewhere in the grid: nothing strictly below it can make the
+                    // top k.  One ulp under it, so that rows EQUAL to it still get through (ties go by row number,
+                    // which only the merge can settle).
+                    const float g = key_score(gkey - 1);
+                    if (g > lds_f32(thrs + 4 * myq)) sts_f32(thrs + 4 * myq, g);
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
                 if (!again) break;  // CTA-uniform
@@ -358,7 +380,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                 int n = __shfl_sync(0xffffffffu, n_my, l);
                 n = n < BUF ? n : BUF;
                 compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * BUF, buf_i + 4 * q * BUF,
-                              thrs + 4 * q, k, n);
+                              thrs + 4 * q, k, n, nullptr);
             }
         }
         asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
@@ -378,6 +400,16 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     if (warp == 1) {
         tc_fence_after();
         if (PAIR == 2) tmem_dealloc_pair(tmem_base, 512); else tmem_dealloc(tmem_base, 256);
+    }
+    // merge of the per-CTA lists (and, for a sharded corpus, the exchange with the peer GPUs) in this launch
+    if (fuse.done != nullptr) {
+        const unsigned parts = gridDim.x;
+        // scratch of the tail: the candidate buffers (16 KB, dead since the lists were written out)
+        static_assert(sizeof(TopkTailSmem) <= 4 * TK_QROWS * 16, "tail scratch must fit the candidate buffers");
+        TopkTailSmem& tail_sm = *reinterpret_cast<TopkTailSmem*>(after_ring + 8 * NQ * k);
+        topk_fused_tail(fuse, cand_scores, cand_idx, q_row0, nq, k, tail_sm, [parts, k](int p, int q) {
+            return ((static_cast<size_t>(q >> 7) * parts + p) * TK_QROWS + static_cast<size_t>(q & 127)) * k;
+        });
     }
 }
 
@@ -419,7 +451,9 @@ int topk_scan_rows_pair_grid(int n_rows, int num_sms) {
 
 template <int PAIR>
 static int rows_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows, int dim,
-                       int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream) {
+                       int k, int grid, float* cand_scores, int32_t* cand_idx, const TopkFuse& fuse, cudaStream_t stream) {
+    if (fuse.done != nullptr && (grid > TKX_THREADS || k > TKX_MAX_K))
+        return fail(LSC_E_UNSUPPORTED, "top-k (row-major): fused merge needs grid <= 256 and k <= 16");
     const int fixed = rows_fixed_bytes(dim, k, PAIR);
     int stages = (227 * 1024 - fixed) / TR_STAGE_BYTES;
     if (stages > TR_MAX_STAGES) stages = TR_MAX_STAGES;
@@ -442,32 +476,41 @@ static int rows_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, in
     lc.blockDim = dim3(TR_THREADS);
     lc.dynamicSmemBytes = smem;
     lc.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = PAIR;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    // The fused tail waits for every CTA of the grid: a cooperative launch makes them all resident at once, also
+    // when another handle's scan runs on the same GPU.  Shards that share one GPU on purpose (sharded_index.cu,
+    // LSC_TOPK_MAX_CTAS) split the SMs between their grids instead and launch plainly, because their scans wait
+    // for EACH OTHER's candidates and must run side by side.
+    attr[1].id = cudaLaunchAttributeCooperative;
+    attr[1].val.cooperative = 1;
     lc.attrs = attr;
-    lc.numAttrs = 1;
-    LSC_CUDA(cudaLaunchKernelEx(&lc, kern, tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, stages, idesc, cand_scores, cand_idx));
+    lc.numAttrs = (fuse.done != nullptr && fuse.cooperative != 0) ? 2 : 1;
+    LSC_CUDA(cudaLaunchKernelEx(&lc, kern, tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, stages, idesc, cand_scores, cand_idx,
+                                fuse));
     LSC_CUDA(cudaGetLastError());
     return 1;
 }
 
 // tmapC here must have a box of 128 rows x 64 columns (the query-major kernel uses 256-row boxes).
 int topk_scan_rows_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows,
-                          int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream) {
+                          int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, const TopkFuse& fuse,
+                          cudaStream_t stream) {
     if (!topk_scan_rows_supported(dim, k)) return fail(LSC_E_UNSUPPORTED, "top-k (row-major): unsupported dim / k");
-    return rows_launch<1>(tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, grid, cand_scores, cand_idx, stream);
+    return rows_launch<1>(tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, grid, cand_scores, cand_idx, fuse, stream);
 }
 
 // Up to 256 queries [q_row0, q_row0 + nq) per pass on CTA pairs; the query matrix behind tmapQ must have rows up
 // to q_row0 + 256 (zeros past the batch) or end before them (TMA fills with zeros).  Candidates are written as
 // two query blocks: cand + (qb * grid + cta) * 128 * k for qb = 0, 1.
 int topk_scan_rows_pair_launch(const CUtensorMap& tmapQ, const CUtensorMap& tmapC128, int q_row0, int nq, int n_rows,
-                               int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, cudaStream_t stream) {
+                               int dim, int k, int grid, float* cand_scores, int32_t* cand_idx, const TopkFuse& fuse,
+                               cudaStream_t stream) {
     if (grid < 2 || grid % 2 != 0) return fail(LSC_E_INVALID, "top-k (row-major, pairs): grid must be even");
-    return rows_launch<2>(tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, grid, cand_scores, cand_idx, stream);
+    return rows_launch<2>(tmapQ, tmapC128, q_row0, nq, n_rows, dim, k, grid, cand_scores, cand_idx, fuse, stream);
 }
 
 }  // namespace lsc
