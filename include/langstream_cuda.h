@@ -285,6 +285,13 @@ void lsc_exchange_destroy(lsc_exchange* x);
  */
 int lsc_index_search_sharded_dev(lsc_index* idx, lsc_exchange* x, const float* d_queries, int32_t B, int32_t k,
                                  int64_t* d_out_ids, float* d_out_scores, void* stream);
+/*
+ * Allocate now whatever scratch a later search of up to B queries and up to k results needs, so that the search
+ * itself makes no allocation (a growing buffer costs a device-wide synchronisation, which a latency-bound caller
+ * wants at start-up, and which - between shards that share ONE GPU - would stall the shard whose peers already
+ * wait for it).  No reference counterpart (HerdDB sizes its own buffers).
+ */
+int lsc_index_reserve(lsc_index* idx, int32_t B, int32_t k);
 /* Synchronises `stream` and reports (once) whether a wait inside an earlier search on this handle gave up. */
 int lsc_index_check(lsc_index* idx, void* stream);
 

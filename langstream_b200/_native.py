@@ -79,6 +79,7 @@ SIGNATURES = {
     "lsc_exchange_destroy": (None, [_vp]),
     "lsc_index_search_sharded_dev": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "lsc_index_check": (C.c_int, [_vp, _vp]),
+    "lsc_index_reserve": (C.c_int, [_vp, _i32, _i32]),
     "lsc_sharded_index_create": (C.c_int, [_i32, _i64, C.POINTER(C.c_int), _i32, C.POINTER(_vp)]),
     "lsc_sharded_index_upsert": (C.c_int, [_vp, _vp, _vp, _i32]),
     "lsc_sharded_index_delete": (C.c_int, [_vp, _vp, _i32]),
@@ -281,6 +282,10 @@ class Index:
         call and every rank receives the merged [B, k] result (lsc_index_search_sharded_dev)."""
         check(lib().lsc_index_search_sharded_dev(self._h, exchange._h, _ptr(d_queries), B, k, _ptr(d_out_ids),
                                                  _ptr(d_out_scores), stream))
+
+    def reserve(self, B: int, k: int):
+        """Allocate the scratch of a later search of up to B queries / k results now (lsc_index_reserve)."""
+        check(lib().lsc_index_reserve(self._h, int(B), int(k)))
 
     def check(self, stream=0):
         """Synchronise `stream` and raise if a wait inside an earlier search gave up (lsc_index_check)."""

@@ -15,6 +15,7 @@
 
 #include "common.h"
 #include "exchange.h"
+#include "topk.h"
 
 using namespace lsc;
 
@@ -52,6 +53,7 @@ int lsc_exchange_create(int device, int32_t rank, int32_t world, int32_t max_que
     LSC_CUDA(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail(LSC_E_INVALID, "lsc_exchange_create: no such device");
     LSC_CUDA(cudaSetDevice(device));
+    LSC_TRY(topk_preload_kernels());  // nothing may be left to load once a peer's scan waits for this GPU
     lsc_exchange* x = new lsc_exchange();
     x->device = device;
     x->rank = rank;

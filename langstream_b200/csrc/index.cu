@@ -516,6 +516,28 @@ int lsc_index_search_sharded_dev(lsc_index* ix, lsc_exchange* xg, const float* d
     return LSC_OK;
 }
 
+int lsc_index_reserve(lsc_index* ix, int32_t B, int32_t k) {
+    if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_reserve: index is null");
+    if (B < 1 || k < 1 || k > TK_KMAX) return fail(LSC_E_INVALID, "lsc_index_reserve: B >= 1 and k in [1,128]");
+    std::lock_guard<std::mutex> lock(ix->mu);
+    LSC_CUDA(cudaSetDevice(ix->device));
+    LSC_TRY(ensure_query_buffers(ix, B, k));
+    const int64_t nout = static_cast<int64_t>(B) * k;
+    if (nout > ix->cap_loc) {
+        int64_t c1 = ix->cap_loc, c2 = ix->cap_loc;
+        LSC_TRY(grow_buf(&ix->d_loc_ids, &c1, nout, 4096));
+        LSC_TRY(grow_buf(&ix->d_loc_scores, &c2, nout, 4096));
+        ix->cap_loc = std::min(c1, c2);
+    }
+    if (nout > ix->cap_out) {
+        int64_t c1 = ix->cap_out, c2 = ix->cap_out;
+        LSC_TRY(grow_buf(&ix->d_out_ids, &c1, nout, 4096));
+        LSC_TRY(grow_buf(&ix->d_out_scores, &c2, nout, 4096));
+        ix->cap_out = std::min(c1, c2);
+    }
+    return grow_buf(&ix->d_q32, &ix->cap_q32, static_cast<int64_t>(B) * ix->dim, 1 << 16);
+}
+
 int lsc_index_check(lsc_index* ix, void* stream) {
     if (ix == nullptr) return fail(LSC_E_INVALID, "lsc_index_check: index is null");
     std::lock_guard<std::mutex> lock(ix->mu);

@@ -284,7 +284,9 @@ int lsc_sharded_index_search(lsc_sharded_index* s, const float* queries, int32_t
     std::lock_guard<std::mutex> lock(s->mu);
     const int dim = s->dim;
     const int64_t nout = static_cast<int64_t>(B) * k;
-    return s->on_all([&](int sh) -> int {
+    // Phase 1: every shard sizes its buffers.  Allocation synchronises the device; it must be over on ALL shards
+    // before the first scan starts, because a running scan waits for its peers (shards may share a GPU).
+    LSC_TRY(s->on_all([&](int sh) -> int {
         Worker* w = s->workers[sh];
         LSC_CUDA(cudaSetDevice(w->device));
         LSC_TRY(grow(&w->d_q, &w->cap_q, static_cast<int64_t>(B) * dim, 1 << 16));
@@ -294,6 +296,12 @@ int lsc_sharded_index_search(lsc_sharded_index* s, const float* queries, int32_t
             LSC_TRY(grow(&w->d_scores, &c2, nout, 4096));
             w->cap_out = std::min(c1, c2);
         }
+        return lsc_index_reserve(s->shards[sh], std::min<int32_t>(B, s->xs[sh]->xB), k);
+    }));
+    // Phase 2: upload, scan + exchange + merge (one fused launch per pass), read back.
+    return s->on_all([&](int sh) -> int {
+        Worker* w = s->workers[sh];
+        LSC_CUDA(cudaSetDevice(w->device));
         LSC_CUDA(cudaMemcpyAsync(w->d_q, queries, static_cast<size_t>(B) * dim * sizeof(float), cudaMemcpyHostToDevice, w->stream));
         if (s->ndev == 1)
             LSC_TRY(lsc_index_search_dev(s->shards[sh], w->d_q, B, k, w->d_ids, w->d_scores, w->stream));

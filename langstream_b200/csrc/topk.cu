@@ -472,7 +472,13 @@ int scan_inst(const CUtensorMap& tmapQ, const CUtensorMap& tmapC, int q_row0, in
               int dim, int k, int stages, size_t smem, int grid, float* cand_scores, int32_t* cand_idx,
               cudaStream_t stream) {
     auto kern = topk_scan_kernel<KCAP, EW>;
-    LSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    static bool configured[64] = {};  // once per device: not on the launch path of a search whose peers may wait
+    int dev = 0;
+    LSC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+        LSC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
     kern<<<grid, 64 + EW * 32, smem, stream>>>(tmapQ, tmapC, q_row0, nq, n_rows, dim, k, stages, cand_scores,
                                              cand_idx);
     LSC_CUDA(cudaGetLastError());
@@ -480,6 +486,26 @@ int scan_inst(const CUtensorMap& tmapQ, const CUtensorMap& tmapC, int q_row0, in
 }
 
 }  // namespace
+
+// Load every kernel a sharded search can launch into the current device's context NOW.  The CUDA runtime loads a
+// kernel lazily at its first launch, and that load can wait for the kernels already running on the device - one
+// of which may be a peer shard's scan or exchange kernel that waits for this very launch.
+int topk_preload_kernels() {
+    cudaFuncAttributes a;
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_exchange_kernel));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_merge_kernel<0>));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_merge_kernel<1>));
+    LSC_CUDA(cudaFuncGetAttributes(&a, normalize_rows_kernel));
+    LSC_CUDA(cudaFuncGetAttributes(&a, fill_empty_kernel));
+    LSC_CUDA(cudaFuncGetAttributes(&a, move_rows_kernel));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_scan_kernel<16, 8>));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_scan_kernel<32, 8>));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_scan_kernel<128, 8>));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_scan_kernel<16, 16>));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_scan_kernel<32, 16>));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_scan_kernel<128, 16>));
+    return topk_rows_preload_kernels();
+}
 
 int topk_scan_grid(int n_rows, int num_sms) {
     const int tiles = (n_rows + TK_BN - 1) / TK_BN;

@@ -61,6 +61,10 @@ int scores_naive_launch(const __nv_bfloat16* rows, int64_t n, int dim, const __n
 // row into the freed slot"; sources and destinations must not overlap.
 int move_rows_launch(__nv_bfloat16* rows, int64_t* ids, int dim, const int64_t* moves, int m, cudaStream_t stream);
 
+// Force-load the top-k kernels into the current device's context (see topk.cu).
+int topk_preload_kernels();
+int topk_rows_preload_kernels();
+
 int fill_empty_launch(int64_t* ids, float* scores, size_t n, cudaStream_t stream);
 
 }  // namespace lsc

@@ -422,6 +422,13 @@ static int rows_fixed_bytes(int dim, int k, int pair) {
     return (dim / TR_BK) * TR_QBLK_BYTES + nq * k * 8 + nq * buf * 8 + nq * 8 + 256 + 1024;
 }
 
+int topk_rows_preload_kernels() {
+    cudaFuncAttributes a;
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_scan_rows_kernel<1>));
+    LSC_CUDA(cudaFuncGetAttributes(&a, topk_scan_rows_kernel<2>));
+    return LSC_OK;
+}
+
 int topk_scan_rows_grid(int n_rows, int num_sms) {
     const int tiles = (n_rows + TR_BM - 1) / TR_BM;
     return tiles < num_sms ? tiles : num_sms;

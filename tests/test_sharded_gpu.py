@@ -114,6 +114,7 @@ def test_sharded_duplicates_keep_storage_order(native_lib, cuda_device):
     cuts = [0, 900, 2100, 3000, n]
     for r in range(world):
         shards[r].upsert(np.arange(cuts[r], cuts[r + 1]), rows[cuts[r]:cuts[r + 1]])
+        shards[r].reserve(B, k)  # no allocation (= device-wide synchronise) once a peer's scan is waiting
     dq = torch.from_numpy(q).to(cuda_device)
     streams = [torch.cuda.Stream() for _ in range(world)]
     outs = [(torch.empty(B, k, dtype=torch.int64, device=cuda_device), torch.empty(B, k, dtype=torch.float32, device=cuda_device))
