@@ -153,6 +153,8 @@ def run_reference(args):
     from langstream_b200 import weights as W
     from oracle.encoder_oracle import HFOracle
 
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the reference arm is one process and gets the whole host
+    torch.set_num_threads(os.cpu_count() or 1)
     spec = W.MINILM_L6
     sample = 32  # sequences per step: BASELINE configs[0] (batch 32 x 128 on CPU)
     oracle = HFOracle(spec, W.random_init(spec, seed=0))
@@ -181,6 +183,239 @@ def run_reference(args):
     }
     emit(line)
     return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# top-k half of the metric
+# ---------------------------------------------------------------------------------------------
+def topk_cpu_baseline(max_seconds: float = 12.0):
+    """BASELINE.md 3, rows B4 and B5, on the box's host cores.
+    B4: fp32 `queries @ corpus.T` + top-k over a 1M x 384 slice (L2-normalised, bf16-rounded, widened) for
+        B = 1 / 64 / 1024, QPS at 1M rows and EXTRAPOLATED x10 (a scan is linear in the rows) to 10M.
+    B5: the scalar per-row cosine of ReRankAgent.cosineSimilarity (ReRankAgent.java:254-273,361-372) + stable
+        top-10 on 10k rows, one thread: a per-row cost figure, not extrapolated."""
+    import torch
+    from oracle import topk_oracle
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    n, dim = 1_000_000, TOPK_DIM
+    g = torch.Generator().manual_seed(42)
+    corpus = torch.nn.functional.normalize(torch.randn(n, dim, generator=g), dim=1).bfloat16().float()
+    out = {"kind": "port", "cores": torch.get_num_threads(), "rows": n,
+           "what": "B4: torch CPU fp32 queries @ corpus.T + topk on a 1M-row slice, x10-extrapolated to 10M rows; "
+                   "B5: scalar ReRankAgent-form cosine + stable top-10 on 10k rows (1 thread)", "batches": {}}
+    budget = max_seconds / 3.0
+    for B in (1, 64, 1024):
+        q = torch.nn.functional.normalize(torch.randn(B, dim, generator=torch.Generator().manual_seed(43)), dim=1).bfloat16().float()
+        torch.topk(q @ corpus.T, TOPK_K, dim=1)
+        done, t0 = 0, time.perf_counter()
+        while True:
+            torch.topk(q @ corpus.T, TOPK_K, dim=1)
+            done += 1
+            el = time.perf_counter() - t0
+            if el >= budget or done >= 50:
+                break
+        qps_1m = B * done / el
+        out["batches"][str(B)] = {"qps_at_1M_rows": qps_1m, "qps_at_10M_rows_extrapolated": qps_1m / 10.0,
+                                  "sample": f"{done} batches in {el:.2f} s"}
+    rows10k = corpus[:10_000].numpy()
+    q1 = corpus[123:124].numpy()
+    topk_oracle.search_scalar(rows10k[:100], q1, TOPK_K)
+    t0 = time.perf_counter()
+    reps = 0
+    while time.perf_counter() - t0 < 1.0:
+        topk_oracle.search_scalar(rows10k, q1, TOPK_K)
+        reps += 1
+    el = time.perf_counter() - t0
+    out["scalar_form"] = {"rows": 10_000, "ns_per_row": 1e9 * el / (reps * 10_000), "queries_per_s_at_10k_rows": reps / el,
+                          "cores": 1}
+    return out
+
+
+def run_topk(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks, pk, peak_tf):
+    """Top-10 queries/s over a 10M x 384 bf16 corpus row-sharded over the ranks, B = 1 / 64 / 1024.
+
+    One step = one query batch answered on every rank: N = 1: lsc_index_search_dev (normalise + ONE fused scan launch per
+    pass); N > 1: lsc_index_search_sharded_dev - the same launch also stores the shard's candidates into every
+    peer's receive buffer over NVLink and merges the peers' (lsc_exchange over CUDA IPC handles, exchanged once
+    through torch.distributed).  `nccl_allgather_qps` times the unfused form (search, one NCCL all-gather per
+    array, merge launch) beside it.  `e2e` starts from pinned HOST queries and ends with the merged ids / scores
+    in host memory every step.  `parity` compares the timed result with exact fp32 scores of every shard row
+    (lsc_index_scores_naive_dev, CUDA cores) - ids identical except ties within 1e-5."""
+    import torch
+    import torch.distributed as dist
+    from langstream_b200._native import Exchange, Index, topk_merge_dev
+
+    rows_total = args.topk_rows
+    lo = rows_total * rank // world
+    hi = rows_total * (rank + 1) // world
+    n_local = hi - lo
+    ix = Index(TOPK_DIM, capacity=n_local, device=local_rank)
+    chunk = 1 << 20
+    for o in range(0, n_local, chunk):
+        m = min(chunk, n_local - o)
+        g = torch.Generator(device=dev).manual_seed(42 + (lo + o) // chunk)
+        vec = torch.randn(m, TOPK_DIM, generator=g, device=dev)
+        ix.upsert_dev(np.arange(lo + o, lo + o + m, dtype=np.int64), vec, m, stream)
+    del vec
+    xg, exchange_kind = None, "none (one GPU)"
+    if world > 1:
+        try:
+            xg = Exchange(local_rank, rank, world, 1024)
+            handles = [None] * world
+            dist.all_gather_object(handles, xg.ipc_handle())
+            xg.connect_ipc(handles)
+            exchange_kind = "fused into the scan launch: peer-to-peer stores + per-query flags (lsc_exchange, CUDA IPC)"
+        except Exception as e:  # noqa: BLE001 - no P2P between these GPUs: the NCCL form is the product path then
+            xg, exchange_kind = None, f"NCCL all-gather + merge launch (peer mapping failed: {e})"
+        ok = torch.tensor([1 if xg is not None else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            xg = None
+    ix.reserve(1024, TOPK_K)
+    topk = {"corpus": f"{rows_total} x {TOPK_DIM} bf16, seed 42, row-sharded over {world} GPU(s)", "k": TOPK_K,
+            "exchange": exchange_kind, "batches": {}}
+    steps_topk = max(3, min(args.steps, 20))
+    topk_traffic = None
+    try:
+        topk_traffic = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())["topk_scan_kernel"]["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for B in (1, 64, 1024):
+        g = torch.Generator(device=dev).manual_seed(43)
+        q = torch.randn(B, TOPK_DIM, generator=g, device=dev)
+        fin_ids = torch.empty(B, TOPK_K, dtype=torch.int64, device=dev)
+        fin_sc = torch.empty(B, TOPK_K, dtype=torch.float32, device=dev)
+        loc_ids = torch.empty(B, TOPK_K, dtype=torch.int64, device=dev)
+        loc_sc = torch.empty(B, TOPK_K, dtype=torch.float32, device=dev)
+        all_ids = torch.empty(world, B, TOPK_K, dtype=torch.int64, device=dev)
+        all_sc = torch.empty(world, B, TOPK_K, dtype=torch.float32, device=dev)
+
+        def q_step():
+            if world == 1:
+                ix.search_dev(q, B, TOPK_K, fin_ids, fin_sc, stream)
+            elif xg is not None:
+                ix.search_sharded_dev(xg, q, B, TOPK_K, fin_ids, fin_sc, stream)
+            else:
+                q_step_nccl()
+
+        def q_step_nccl():
+            ix.search_dev(q, B, TOPK_K, loc_ids, loc_sc, stream)
+            dist.all_gather_into_tensor(all_ids, loc_ids)
+            dist.all_gather_into_tensor(all_sc, loc_sc)
+            topk_merge_dev(all_ids, all_sc, world, B, TOPK_K, fin_ids, fin_sc, stream)
+
+        def timed(fn, n):
+            barrier()
+            ev0.record()
+            for _ in range(n):
+                fn()
+            ev1.record()
+            barrier()
+            return max_over_ranks(ev0.elapsed_time(ev1))
+
+        for _ in range(3):
+            q_step()
+        ms_q = timed(q_step, steps_topk)            # the QPS: nothing but the search in the timed region
+        ix.set_profiling(True)                      # same steps again with every launch bracketed by events
+        timed(q_step, steps_topk)
+        pr = ix.read_profile()
+        ix.set_profiling(False)
+        ix.check(stream)
+        scan_ms, scan_launches = pr["scan"]
+        per_launch_ms = scan_ms / max(scan_launches, 1)
+        bytes_per_launch = n_local * TOPK_DIM * 2
+        gbs = bytes_per_launch / (per_launch_ms / 1000.0) / 1e9 if per_launch_ms > 0 else 0.0
+        entry = {"qps": B * steps_topk / (ms_q / 1000.0), "ms_per_batch": ms_q / steps_topk,
+                 "scan_launches_per_batch": scan_launches / steps_topk, "scan_ms_per_launch": per_launch_ms,
+                 "scan_launch_covers": "scan + merge of the per-CTA lists" + (" + peer exchange + final merge" if xg is not None else "")}
+        if B <= 128:
+            entry["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                                 "frac": gbs / pk["hbm_gbs"], "bytes_per_launch": bytes_per_launch,
+                                 "traffic": topk_traffic if (world == 1 and rows_total == TOPK_ROWS) else None}
+        else:
+            tf = 2.0 * B * n_local * TOPK_DIM * steps_topk / (scan_ms / 1000.0) / 1e12 if scan_ms > 0 else 0.0
+            entry["roofline"] = {"bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s",
+                                 "frac": tf / peak_tf,
+                                 "hbm_frac": (bytes_per_launch / (per_launch_ms / 1000.0) / 1e9 / pk["hbm_gbs"]) if per_launch_ms > 0 else None}
+        if world > 1 and xg is not None:
+            for _ in range(2):
+                q_step_nccl()
+            ms_n = timed(q_step_nccl, steps_topk)
+            entry["nccl_allgather_qps"] = B * steps_topk / (ms_n / 1000.0)
+
+        # ---- parity of the timed result (every rank checks its shard exactly; merged over ranks with torch) ----
+        q_step()
+        torch.cuda.synchronize()
+        got_ids, got_sc = fin_ids.clone(), fin_sc.clone()
+        ref_sc = torch.empty(B, TOPK_K, dtype=torch.float32, device=dev)
+        ref_id = torch.empty(B, TOPK_K, dtype=torch.int64, device=dev)
+        full = torch.empty(16 * n_local, dtype=torch.float32, device=dev)
+        for b0 in range(0, B, 16):
+            nb = min(16, B - b0)
+            ix.scores_naive_dev(q[b0:b0 + nb].contiguous(), nb, full, stream)
+            s, i = torch.topk(full[: nb * n_local].view(nb, n_local), TOPK_K, dim=1)
+            ref_sc[b0:b0 + nb], ref_id[b0:b0 + nb] = s, i + lo
+        del full
+        if world > 1:
+            g_sc = torch.empty(world, B, TOPK_K, dtype=torch.float32, device=dev)
+            g_id = torch.empty(world, B, TOPK_K, dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(g_sc, ref_sc)
+            dist.all_gather_into_tensor(g_id, ref_id)
+            cat_sc = g_sc.permute(1, 0, 2).reshape(B, world * TOPK_K)
+            cat_id = g_id.permute(1, 0, 2).reshape(B, world * TOPK_K)
+            ref_sc, pos = torch.topk(cat_sc, TOPK_K, dim=1)
+            ref_id = torch.gather(cat_id, 1, pos)
+        # rank by rank: the returned row's score must equal the exact k-th score within the tie tolerance
+        rank_gap = float((got_sc - ref_sc).abs().max().item())
+        differ = got_ids != ref_id
+        beyond_tol = int((differ & ((got_sc - ref_sc).abs() > 1e-5)).sum().item())
+        entry["parity"] = {"topk_mismatch": beyond_tol, "ids_differing_within_tie_tol": int(differ.sum().item()) - beyond_tol,
+                           "max_abs_score_gap": rank_gap, "tol": 1e-5, "queries_checked": B,
+                           "checker": "exact fp32 dot products of every shard row (CUDA cores) + top-k, merged over ranks"}
+
+        # ---- e2e: pinned host queries in, merged ids + scores in host memory out, every step ----
+        h_q = q.cpu().pin_memory()
+        h_ids = torch.empty(B, TOPK_K, dtype=torch.int64).pin_memory()
+        h_sc = torch.empty(B, TOPK_K, dtype=torch.float32).pin_memory()
+        if world == 1:
+            hq_np, hi_np, hs_np = h_q.numpy(), h_ids.numpy(), h_sc.numpy()
+            from langstream_b200._native import lib as _lib, check as _check, _ptr
+
+            def e2e_step():  # the host-buffer C-ABI call a datasource makes
+                _check(_lib().lsc_index_search(ix._h, _ptr(hq_np), B, TOPK_K, _ptr(hi_np), _ptr(hs_np)))
+            api = "lsc_index_search (host queries -> host ids + scores)"
+        else:
+            def e2e_step():
+                q.copy_(h_q, non_blocking=True)
+                q_step()
+                h_ids.copy_(fin_ids, non_blocking=True)
+                h_sc.copy_(fin_sc, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+            api = ("pinned host queries -> lsc_index_search_sharded_dev on every rank -> merged ids + scores copied to "
+                   "host memory, synchronised every step")
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps_topk):
+            e2e_step()
+        torch.cuda.synchronize()
+        e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1000.0)
+        entry["e2e"] = {"value": B * steps_topk / (e2e_ms / 1000.0), "unit": "queries/s", "api": api,
+                        "h2d_bytes_per_step": int(B * TOPK_DIM * 4), "d2h_bytes_per_step": int(B * TOPK_K * 12)}
+        topk["batches"][str(B)] = entry
+    topk["gpu_launches_per_batch"] = {"1": 2, "64": 2, "1024": 5}  # normalise + one fused scan per 256-query pass
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            topk["cpu_baseline"] = topk_cpu_baseline()
+        except Exception as e:  # noqa: BLE001
+            topk["cpu_baseline"] = {"error": str(e)}
+    ix.close()
+    if xg is not None:
+        xg.close()
+    return topk
 
 
 # ---------------------------------------------------------------------------------------------
@@ -248,6 +483,27 @@ def run_cuda(args):
     clocks = sampler.stop()
     launches = enc.launch_count - launches0
     value = world * N_SEQ * args.steps / (ms_total / 1000.0)
+
+    # parity of what the timed steps produced: the first sequences of this rank's batch against the fp32 oracle
+    # (one text per forward, as the reference runs them); worst margin over the ranks
+    parity = {"tolerance": {"cos_min": 0.999, "max_abs": 2e-3}}
+    try:
+        from oracle.encoder_oracle import HFOracle
+        torch.set_num_threads(max(1, (os.cpu_count() or 1) // world))
+        n_chk = 16
+        want = HFOracle(spec, blob).embed_one_by_one(ids[: cu[n_chk]], cu[: n_chk + 1])
+        got = d_out[:n_chk].cpu().numpy()
+        cosv = (got * want).sum(1) / (np.linalg.norm(got, axis=1) * np.linalg.norm(want, axis=1))
+        cos_min, max_abs = float(cosv.min()), float(np.abs(got - want).max())
+        if world > 1:
+            t = torch.tensor([-cos_min, max_abs], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            cos_min, max_abs = -float(t[0].item()), float(t[1].item())
+        parity.update({"cos_min": cos_min, "max_abs": max_abs, "rows_checked_per_gpu": n_chk,
+                       "oracle": "HuggingFace BertModel fp32 on torch CPU (parity unpinned against the reference's own "
+                                 "tests: its one golden vector needs e5-small weights)"})
+    except Exception as e:  # noqa: BLE001
+        parity["error"] = str(e)
 
     # ---- same K steps again with every launch bracketed by CUDA events on the launching stream:
     #      per-kernel durations for the roofline (the events add a few microseconds per launch, which is
@@ -323,33 +579,53 @@ def run_cuda(args):
               "lengths": "UniformInt[16,128] packed", "tokens_per_step": Tv}
 
     # config 3 of SURVEY.md 8(d), as an extra figure (not the headline): the base shape (12 layers, H = 768,
-    # 12 heads of 64, FFN 3072) at 512 tokens per sequence; one pass = 512 sequences (262,144 tokens, the
-    # pass size the host API cuts larger batches into), so 4096 x 512 is eight such passes per GPU.
+    # 12 heads of 64, FFN 3072), 4096 sequences x 512 tokens SPLIT over the N GPUs (strong scaling: contiguous
+    # slices of the sequence list, no collective), fixed length and UniformInt[64,512] packed; each GPU runs its
+    # slice in passes of at most 262,144 tokens (the pass size the host API cuts batches into).
     base = None
     if not args.no_base:
         bspec = W.BERT_BASE
         benc = Encoder(bspec, W.random_init(bspec, 0), device=local_rank)
-        b_n, b_s = 512, 512
-        b_ids, b_cu = W.synthetic_token_ids(b_n, b_s, seed=99 + rank)
-        db_ids, db_cu = torch.from_numpy(b_ids).to(dev), torch.from_numpy(b_cu).to(dev)
-        db_out = torch.empty(b_n, bspec.hidden, device=dev)
-        for _ in range(2):
-            benc.embed_dev(db_ids, db_cu, b_n, int(b_cu[-1]), b_s, db_out, stream)
-        barrier()
-        reps = 3
-        ev0.record()
-        for _ in range(reps):
-            benc.embed_dev(db_ids, db_cu, b_n, int(b_cu[-1]), b_s, db_out, stream)
-        ev1.record()
-        barrier()
-        ms_base = max_over_ranks(ev0.elapsed_time(ev1))
-        b_total, _ = flops_per_sequence(bspec, b_s)
-        base = {"value": world * b_n * reps / (ms_base / 1000.0), "unit": "embeddings/s",
-                "workload": "base shape 12L/768/12h/3072, 512 sequences x 512 tokens per pass",
-                "ms_per_pass": ms_base / reps,
-                "whole_pass_tflops": b_total * b_n * reps / (ms_base / 1000.0) / 1e12}
+        b_total_seqs, b_s = 4096, 512
+        s_lo, s_hi = b_total_seqs * rank // world, b_total_seqs * (rank + 1) // world
+        base = {"workload": f"base shape 12L/768/12h/3072, {b_total_seqs} sequences x {b_s} tokens split over {world} GPU(s), "
+                            "passes of <= 262,144 tokens", "scaling": "strong"}
+        for label, min_len in (("fixed_512", None), ("ragged_64_512", 64)):
+            a_ids, a_cu = W.synthetic_token_ids(b_total_seqs, b_s, seed=99, min_len=min_len)
+            a_cu = a_cu.astype(np.int64)
+            passes, p0 = [], s_lo
+            while p0 < s_hi:  # whole sequences, <= 262,144 tokens per pass
+                p1 = p0 + 1
+                while p1 < s_hi and a_cu[p1 + 1] - a_cu[p0] <= (1 << 18):
+                    p1 += 1
+                ids_p = torch.from_numpy(a_ids[a_cu[p0]:a_cu[p1]].copy()).to(dev)
+                cu_p = torch.from_numpy((a_cu[p0:p1 + 1] - a_cu[p0]).astype(np.int32)).to(dev)
+                out_p = torch.empty(p1 - p0, bspec.hidden, device=dev)
+                passes.append((ids_p, cu_p, p1 - p0, int(a_cu[p1] - a_cu[p0]), int(np.diff(a_cu[p0:p1 + 1]).max()), out_p))
+                p0 = p1
+
+            def base_step():
+                for ids_p, cu_p, n_p, t_p, m_p, out_p in passes:
+                    benc.embed_dev(ids_p, cu_p, n_p, t_p, m_p, out_p, stream)
+
+            base_step()
+            barrier()
+            reps = 2
+            ev0.record()
+            for _ in range(reps):
+                base_step()
+            ev1.record()
+            barrier()
+            ms_base = max_over_ranks(ev0.elapsed_time(ev1))
+            lens = np.diff(a_cu)
+            flop = float(sum(bspec.layers * (24 * bspec.hidden ** 2 * int(l) + 4 * bspec.hidden * int(l) ** 2) for l in lens))
+            base[label] = {"value": b_total_seqs * reps / (ms_base / 1000.0), "unit": "embeddings/s",
+                           "ms_per_4096_sequences": ms_base / reps, "passes_per_gpu": len(passes),
+                           "tokens_total": int(a_cu[-1]),
+                           "whole_job_tflops": flop * reps / (ms_base / 1000.0) / 1e12,
+                           "frac_of_sustained_peak_per_gpu": flop * reps / (ms_base / 1000.0) / 1e12 / world / peak_tf}
+            del passes
         benc.close()
-        del db_ids, db_cu, db_out
         torch.cuda.empty_cache()
 
     # e2e: the C-ABI host-buffer call, pinned host memory, copies inside the timed region
@@ -395,8 +671,9 @@ def run_cuda(args):
     try:
         from langstream_b200._native import WordPieceTokenizer
         words = [f"w{i}" for i in range(spec.vocab - 5)]
+        tok_threads = max(1, (os.cpu_count() or 1) // world)  # the ranks of one box share its host cores
         tok = WordPieceTokenizer("\n".join(["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words) + "\n",
-                                 max_length=SEQ_LEN, n_threads=0)
+                                 max_length=SEQ_LEN, n_threads=tok_threads)
         trng = np.random.default_rng(77 + rank)
         texts = [" ".join(words[j] for j in trng.integers(0, len(words), SEQ_LEN - 2)) for _ in range(N_SEQ)]
         t_ids, t_cu = tok.encode_packed(texts)
@@ -421,7 +698,7 @@ def run_cuda(args):
         text_e2e = {"value": world * N_SEQ * reps / (text_ms / 1000.0), "unit": "embeddings/s",
                     "api": "lsc_tokenizer_encode + lsc_encoder_submit / lsc_encoder_wait (host texts -> host fp32 embeddings), "
                            "tokenisation of batch i+1 overlapping the kernels of batch i",
-                    "tokenizer_texts_per_s": N_SEQ * reps / tok_s, "tokenizer_threads": os.cpu_count()}
+                    "tokenizer_texts_per_s": N_SEQ * reps / tok_s, "tokenizer_threads": tok_threads}
         tok.close()
     except Exception as e:  # noqa: BLE001 - an extra figure must not take the benchmark down
         text_e2e = {"error": str(e)}
@@ -429,71 +706,7 @@ def run_cuda(args):
     # ---- top-k over a 10M x 384 corpus, row-sharded across ranks -------------------------------
     topk = None
     if not args.no_topk:
-        rows_total = args.topk_rows
-        lo = rows_total * rank // world
-        hi = rows_total * (rank + 1) // world
-        n_local = hi - lo
-        ix = Index(TOPK_DIM, capacity=n_local, device=local_rank)
-        chunk = 1 << 20
-        for o in range(0, n_local, chunk):
-            m = min(chunk, n_local - o)
-            g = torch.Generator(device=dev).manual_seed(42 + (lo + o) // chunk)
-            vec = torch.randn(m, TOPK_DIM, generator=g, device=dev)
-            ix.upsert_dev(np.arange(lo + o, lo + o + m, dtype=np.int64), vec, m, stream)
-        del vec
-        topk = {"corpus": f"{rows_total} x {TOPK_DIM} bf16, seed 42, row-sharded over {world} GPU(s)", "k": TOPK_K,
-                "batches": {}}
-        steps_topk = max(3, min(args.steps, 20))
-        topk_traffic = None
-        try:
-            topk_traffic = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())["topk_scan_kernel"]["dram_bytes_per_launch"]
-        except Exception:
-            pass
-        for B in (1, 64, 1024):
-            g = torch.Generator(device=dev).manual_seed(43)
-            q = torch.randn(B, TOPK_DIM, generator=g, device=dev)
-            loc_ids = torch.empty(B, TOPK_K, dtype=torch.int64, device=dev)
-            loc_sc = torch.empty(B, TOPK_K, dtype=torch.float32, device=dev)
-            all_ids = torch.empty(world, B, TOPK_K, dtype=torch.int64, device=dev)
-            all_sc = torch.empty(world, B, TOPK_K, dtype=torch.float32, device=dev)
-            fin_ids = torch.empty(B, TOPK_K, dtype=torch.int64, device=dev)
-            fin_sc = torch.empty(B, TOPK_K, dtype=torch.float32, device=dev)
-
-            def q_step():
-                ix.search_dev(q, B, TOPK_K, loc_ids, loc_sc, stream)
-                if world > 1:
-                    dist.all_gather_into_tensor(all_ids, loc_ids)
-                    dist.all_gather_into_tensor(all_sc, loc_sc)
-                    topk_merge_dev(all_ids, all_sc, world, B, TOPK_K, fin_ids, fin_sc, stream)
-
-            for _ in range(3):
-                q_step()
-            barrier()
-            ix.set_profiling(True)
-            ev0.record()
-            for _ in range(steps_topk):
-                q_step()
-            ev1.record()
-            barrier()
-            ms_q = max_over_ranks(ev0.elapsed_time(ev1))
-            pr = ix.read_profile()
-            ix.set_profiling(False)
-            scan_ms, scan_launches = pr["scan"]
-            per_launch_ms = scan_ms / max(scan_launches, 1)
-            bytes_per_launch = n_local * TOPK_DIM * 2
-            gbs = bytes_per_launch / (per_launch_ms / 1000.0) / 1e9 if per_launch_ms > 0 else 0.0
-            entry = {"qps": B * steps_topk / (ms_q / 1000.0), "ms_per_batch": ms_q / steps_topk,
-                     "scan_launches_per_batch": scan_launches / steps_topk, "scan_ms_per_launch": per_launch_ms}
-            if B <= 128:
-                entry["roofline"] = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                                     "frac": gbs / pk["hbm_gbs"], "bytes_per_launch": bytes_per_launch,
-                                     "traffic": topk_traffic if (world == 1 and rows_total == TOPK_ROWS) else None}
-            else:
-                tf = 2.0 * B * n_local * TOPK_DIM * steps_topk / (scan_ms / 1000.0) / 1e12 if scan_ms > 0 else 0.0
-                entry["roofline"] = {"bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s",
-                                     "frac": tf / peak_tf}
-            topk["batches"][str(B)] = entry
-        ix.close()
+        topk = run_topk(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks, pk, peak_tf)
 
     # ---- CPU baseline (rank 0, N=1 only): reference-shaped oracle on a bounded sample ------------
     cpu_baseline = None
@@ -513,8 +726,8 @@ def run_cuda(args):
                                    f"{N_SEQ} x {SEQ_LEN} synthetic tokens per GPU per step, packed",
                        "parallelism": f"dp{world} (one replica per GPU, no collective)",
                        "l2": "per-step working set ~1.1 GB of activations >> 126 MB L2; no explicit flush"},
-            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
-            "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "base_512": base, "text_e2e": text_e2e, "topk": topk,
+            "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "parity": parity,
+            "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "base_4096x512": base, "text_e2e": text_e2e, "topk": topk,
         }
         emit(line)
     enc.close()

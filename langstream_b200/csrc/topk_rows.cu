@@ -129,7 +129,8 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     const uint32_t buf_i = buf_s + 4 * NQ * BUF;
     const uint32_t thrs = buf_i + 4 * NQ * BUF;
     const uint32_t cnt = thrs + 4 * NQ;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * NQ * k + 8 * NQ * BUF + 8 * NQ);
+    const uint32_t gthr_s = cnt + 4 * NQ;  // shared-memory copy of the grid-wide thresholds (refreshed asynchronously)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * NQ * k + 8 * NQ * BUF + 12 * NQ);
     const uint32_t bar_full = smem_u32(bars);
     const uint32_t bar_empty = bar_full + 8 * TR_MAX_STAGES;
     const uint32_t bar_tfull = bar_empty + 8 * TR_MAX_STAGES;
@@ -172,6 +173,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     for (int i = threadIdx.x; i < NQ; i += TR_THREADS) {
         sts_f32(thrs + 4 * i, -INFINITY);
         sts_s32(cnt + 4 * i, 0);
+        sts_s32(gthr_s + 4 * i, TKX_KEY_NEG_INF);
     }
     if (threadIdx.x == 0) sts_s32(again_epoch, -1);
     tc_fence_before();
@@ -275,10 +277,17 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
 #pragma unroll
             for (int cc = 0; cc < CPW; ++cc) pend[cc] = 0u;
             bool released = !scans;
-            // the other CTAs' k-th best score for this warp's queries: asked for now, used after the tile's
-            // compaction (the L2 round trip hides behind the append phase)
-            int32_t gkey = TKX_KEY_NEG_INF;
-            if (gthr != nullptr && lane < NQ / TR_SEL_WARPS && myq < nq) gkey = ld_relaxed_gpu_s32(gthr + myq);
+            // The other CTAs' k-th best scores: every warp copies its slice of the grid-wide thresholds into
+            // shared memory with cp.async (L2 -> shared, no register in between, nobody waits for it) and the
+            // compaction phase reads whatever copy has landed.  A register load here costs an L2 round trip per
+            // tile on the selection warps' critical path (measured: 2x the scan time at 64 queries); a stale
+            // threshold only admits a few more candidates.
+            if (gthr != nullptr && lane < NQ / (TR_SEL_WARPS * 4)) {
+                const int i4 = (sw * (NQ / TR_SEL_WARPS) + lane * 4);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n\tcp.async.commit_group;" ::"r"(gthr_s + 4 * i4),
+                             "l"(gthr + i4)
+                             : "memory");
+            }
             if (scans) {
                 mbar_wait(bar_tfull + 8 * acc, acc_phase);
                 tc_fence_after();
@@ -316,6 +325,8 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                         any &= any - 1;
                         const uint32_t sc = tmem_ld_32x1(tcol + j);  // this lane's score against query c*32+j
                         tmem_ld_wait();
+                        // (a warp-aggregated slot reservation - one atomic per warp and query - was tried: it costs
+                        // more on the common single-hit iteration than it saves on the first, crowded tiles)
                         if ((m >> j) & 1u) {
                             const int q = c * 32 + j;
                             const int pos = atoms_add_s32(cnt + 4 * q, 1);
@@ -355,6 +366,8 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                                   thrs + 4 * q, k, n, gthr != nullptr ? gthr + q : nullptr);
                     if (lane == 0) sts_s32(cnt + 4 * q, 0);
                 }
+                const int32_t gkey = (gthr != nullptr && lane < NQ / TR_SEL_WARPS && myq < nq) ? lds_s32(gthr_s + 4 * myq)
+                                                                                                : TKX_KEY_NEG_INF;
                 if (gkey > TKX_KEY_NEG_INF) {
                     // k rows score >= key_score(gkey) somewhere in the grid: nothing strictly below it can make the
                     // top k.  One ulp under it, so that rows EQUAL to it still get through (ties go by row number,
@@ -419,7 +432,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
 // barriers, alignment slack
 static int rows_fixed_bytes(int dim, int k, int pair) {
     const int nq = TK_QROWS * pair, buf = pair == 2 ? 16 : TR_BUF;
-    return (dim / TR_BK) * TR_QBLK_BYTES + nq * k * 8 + nq * buf * 8 + nq * 8 + 256 + 1024;
+    return (dim / TR_BK) * TR_QBLK_BYTES + nq * k * 8 + nq * buf * 8 + nq * 12 + 256 + 1024;
 }
 
 int topk_rows_preload_kernels() {
