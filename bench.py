@@ -406,7 +406,7 @@ def run_topk(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks
         entry["e2e"] = {"value": B * steps_topk / (e2e_ms / 1000.0), "unit": "queries/s", "api": api,
                         "h2d_bytes_per_step": int(B * TOPK_DIM * 4), "d2h_bytes_per_step": int(B * TOPK_K * 12)}
         topk["batches"][str(B)] = entry
-    topk["gpu_launches_per_batch"] = {"1": 2, "64": 2, "1024": 5}  # normalise + one fused scan per 256-query pass
+    topk["gpu_launches_per_batch"] = {"1": 2, "64": 2, "1024": 6}  # normalise + fused scan; B > 256: normalise + 4 scans + merge
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             topk["cpu_baseline"] = topk_cpu_baseline()

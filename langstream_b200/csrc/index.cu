@@ -136,7 +136,7 @@ int ensure_query_buffers(lsc_index* ix, int B, int k) {
         if (ix->d_done) cudaFree(ix->d_done);
         ix->d_gthr = nullptr;
         ix->d_done = nullptr;
-        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_gthr), static_cast<size_t>(bpad) * sizeof(int32_t)));
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_gthr), 5 * static_cast<size_t>(bpad) * sizeof(int32_t)));
         LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_done), static_cast<size_t>(bpad / TK_QROWS) * sizeof(unsigned)));
         ix->cap_q = bpad;
         LSC_TRY(make_tmap_bf16_sw128(&ix->tmapQ, ix->d_qbf, static_cast<uint64_t>(bpad), ix->dim, TK_QROWS));
@@ -184,7 +184,7 @@ int search_dev(lsc_index* ix, lsc_exchange* xg, const float* d_queries, int B, i
     LSC_TRY(order_after_previous(ix, st));
     const int qblk = B > TK_QROWS ? 2 * TK_QROWS : TK_QROWS;
     const int bpad = (B + qblk - 1) / qblk * qblk;
-    LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st, ix->d_gthr, bpad, ix->d_done,
+    LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st, ix->d_gthr, 5 * bpad, ix->d_done,
                                         bpad / TK_QROWS));
     TopkFuse fuse;
     fuse.status = ix->d_status;
@@ -203,6 +203,7 @@ int search_dev(lsc_index* ix, lsc_exchange* xg, const float* d_queries, int B, i
         const bool pair = B > TK_QROWS && topk_scan_rows_pair_supported(ix->dim, k, ix->num_sms);
         const int grid = pair ? topk_scan_rows_pair_grid(n_rows, ix->num_sms) : topk_scan_rows_grid(n_rows, ix->num_sms);
         fuse.gthr = no_gthr ? nullptr : ix->d_gthr;
+        fuse.gstride = bpad;
         const int step = pair ? 2 * TK_QROWS : TK_QROWS;
         // One pass over the corpus: the merge (and the peer exchange) rides in the scan launch.  Several passes
         // (B > 256): each launch only scans, and ONE merge launch (+ one exchange launch) serves all queries -

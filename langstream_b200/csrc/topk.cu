@@ -447,16 +447,17 @@ move_rows_kernel(__nv_bfloat16* __restrict__ rows, int64_t* __restrict__ ids, in
 
 // Exchange + final merge for shard results that already lie in memory as [B][k] lists: one CTA per query.
 __global__ void __launch_bounds__(TKX_THREADS)
-topk_exchange_kernel(const int64_t* __restrict__ local_ids, const float* __restrict__ local_scores, int k,
+topk_exchange_kernel(const int64_t* __restrict__ local_ids, const float* __restrict__ local_scores, int B, int k,
                      const __grid_constant__ TopkFuse fuse) {
     __shared__ TopkTailSmem sm;
-    const int q = blockIdx.x;
-    if (threadIdx.x < k) {
-        sm.res_s[threadIdx.x] = local_scores[static_cast<size_t>(q) * k + threadIdx.x];
-        sm.res_i[threadIdx.x] = local_ids[static_cast<size_t>(q) * k + threadIdx.x];
+    for (int q = blockIdx.x; q < B; q += gridDim.x) {
+        if (threadIdx.x < k) {
+            sm.res_s[threadIdx.x] = local_scores[static_cast<size_t>(q) * k + threadIdx.x];
+            sm.res_i[threadIdx.x] = local_ids[static_cast<size_t>(q) * k + threadIdx.x];
+        }
+        tail_bar();
+        tail_exchange(fuse, q, k, sm);
     }
-    tail_bar();
-    tail_exchange(fuse, q, k, sm);
 }
 
 __global__ void fill_empty_kernel(int64_t* ids, float* scores, size_t n) {
@@ -582,12 +583,15 @@ int move_rows_launch(__nv_bfloat16* rows, int64_t* ids, int dim, const int64_t* 
     return 1;
 }
 
+// One CTA per query, unless the shard shares its GPU with other shards (fuse.cooperative == 0): their waiting
+// exchange CTAs must leave room for the scans they wait for, so a small grid walks the queries instead.
 int topk_exchange_launch(const int64_t* local_ids, const float* local_scores, int B, int k, const TopkFuse& fuse,
                          cudaStream_t stream) {
     if (B <= 0) return 0;
     if (k > TKX_MAX_XK || k > fuse.xk || fuse.world > TKX_MAX_WORLD || fuse.world < 2)
         return fail(LSC_E_UNSUPPORTED, "top-k exchange: k <= 32 and 2..8 shards");
-    topk_exchange_kernel<<<B, TKX_THREADS, 0, stream>>>(local_ids, local_scores, k, fuse);
+    const int grid = fuse.cooperative != 0 ? B : (B < 32 ? B : 32);
+    topk_exchange_kernel<<<grid, TKX_THREADS, 0, stream>>>(local_ids, local_scores, B, k, fuse);
     LSC_CUDA(cudaGetLastError());
     return 1;
 }

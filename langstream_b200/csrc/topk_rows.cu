@@ -129,8 +129,9 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     const uint32_t buf_i = buf_s + 4 * NQ * BUF;
     const uint32_t thrs = buf_i + 4 * NQ * BUF;
     const uint32_t cnt = thrs + 4 * NQ;
-    const uint32_t gthr_s = cnt + 4 * NQ;  // shared-memory copy of the grid-wide thresholds (refreshed asynchronously)
-    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * NQ * k + 8 * NQ * BUF + 12 * NQ);
+    const uint32_t gthr_s = cnt + 4 * NQ;  // shared-memory copy of the 5 grid-wide threshold arrays (refreshed asynchronously)
+    const uint32_t samp = buf_s;           // sampling pass only: per query, min over the 4 row quadrants of their best score
+    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * NQ * k + 8 * NQ * BUF + 28 * NQ);
     const uint32_t bar_full = smem_u32(bars);
     const uint32_t bar_empty = bar_full + 8 * TR_MAX_STAGES;
     const uint32_t bar_tfull = bar_empty + 8 * TR_MAX_STAGES;
@@ -173,7 +174,9 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     for (int i = threadIdx.x; i < NQ; i += TR_THREADS) {
         sts_f32(thrs + 4 * i, -INFINITY);
         sts_s32(cnt + 4 * i, 0);
-        sts_s32(gthr_s + 4 * i, TKX_KEY_NEG_INF);
+        sts_s32(samp + 4 * i, 0x7fffffff);
+#pragma unroll
+        for (int a = 0; a < 5; ++a) sts_s32(gthr_s + 4 * (a * NQ + i), TKX_KEY_NEG_INF);
     }
     if (threadIdx.x == 0) sts_s32(again_epoch, -1);
     tc_fence_before();
@@ -184,6 +187,16 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     // a tile = 128 * PAIR corpus rows, one per CTA (pair); this CTA's rows are its rank's half
     const int num_tiles = (n_rows + TR_BM * PAIR - 1) / (TR_BM * PAIR);
     const int tile0 = blockIdx.x / PAIR, tile_step = gridDim.x / PAIR;
+    // Tiles of this CTA (pair): tile0, tile0 + step, ...  With SAMPLING the first tile is visited twice: first
+    // only looked at - every CTA publishes, per query, a score that four of the tile's rows reach, and the
+    // minimum of four such scores from four CTAs is a threshold that 16 >= k rows of the corpus reach - and at
+    // the very end scanned like any other tile.  Without it every CTA starts from -inf and spends its first
+    // tiles inserting rows that cannot make the top k (the fixed cost that dominated short scans: 148 CTAs x k
+    // candidates per query); with it the first collecting tile already rejects all but a fraction of a percent.
+    const int n_my = tile0 < num_tiles ? (num_tiles - 1 - tile0) / tile_step + 1 : 0;
+    const bool sampling = fuse.gthr != nullptr && gridDim.x >= 4 && n_my >= 2;
+    const int n_it = n_my + (sampling ? 1 : 0);
+    auto tile_of = [=](int it) { return (sampling && it == n_it - 1) ? tile0 : tile0 + it * tile_step; };
 
     if (warp == 0) {
         if (elect_one()) {
@@ -202,7 +215,8 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
             const uint64_t pol = policy_evict_first();
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+            for (int it = 0; it < n_it; ++it) {
+                const int tile = tile_of(it);
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                     if (PAIR == 2) {
@@ -230,7 +244,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+            for (int it = 0; it < n_it; ++it) {
                 mbar_wait(bar_tempty + 8 * acc, acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * ACC;
@@ -270,9 +284,59 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
         int acc = 0;
         uint32_t acc_phase = 0;
         int epoch = 0;
-        for (int tile = tile0; tile < num_tiles; tile += tile_step) {
+        for (int it = 0; it < n_it; ++it) {
+            const int tile = tile_of(it);
             const int32_t row = (tile * PAIR + static_cast<int>(cta_rank)) * TR_BM + quad * 32 + lane;
             const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC;
+            if (sampling && it == 0) {
+                // ---- sampling pass over the first tile: nothing is collected ----
+                if (scans) {
+                    mbar_wait(bar_tfull + 8 * acc, acc_phase);
+                    tc_fence_after();
+#pragma unroll
+                    for (int cc = 0; cc < CPW; ++cc) {
+                        const int c = cg * CPW + cc;
+                        if (c >= nchunks) continue;
+                        uint32_t v[32];
+                        tmem_ld_32x32(tbase + c * 32, v);
+                        tmem_ld_wait();
+                        int32_t best = TKX_KEY_NEG_INF;  // lane j keeps the best score of this warp's 32 rows for query c*32+j
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int32_t key = row < n_rows ? score_key(__uint_as_float(v[j])) : TKX_KEY_NEG_INF;
+                            const int32_t r = __reduce_max_sync(0xffffffffu, key);
+                            if (lane == j) best = r;
+                        }
+                        if (c * 32 + lane < nq)
+                            asm volatile("red.shared.min.s32 [%0], %1;" ::"r"(samp + 4 * (c * 32 + lane)), "r"(best) : "memory");
+                    }
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (PAIR == 2) mbar_arrive_cluster(lead_tempty + 8 * acc); else mbar_arrive(bar_tempty + 8 * acc);
+                    }
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
+                if (lane < NQ / TR_SEL_WARPS && myq < nq) {
+                    // four rows of this CTA (one per quadrant) reach `mine` for query myq
+                    const int32_t mine = lds_s32(samp + 4 * myq);
+                    int32_t* const g0 = gthr + myq;
+                    if (mine > TKX_KEY_NEG_INF && mine != 0x7fffffff) atomicMax(g0 + (1 + (blockIdx.x & 3)) * fuse.gstride, mine);
+                    // the other CTAs are at the same point: give their values a moment to arrive (bounded), so
+                    // that the first collecting tile starts from a real threshold
+                    int32_t t_key = TKX_KEY_NEG_INF;
+                    for (int tries = 0; tries < 48 && t_key == TKX_KEY_NEG_INF; ++tries) {
+                        const int32_t s0 = ld_relaxed_gpu_s32(g0 + 1 * fuse.gstride), s1 = ld_relaxed_gpu_s32(g0 + 2 * fuse.gstride),
+                                      s2 = ld_relaxed_gpu_s32(g0 + 3 * fuse.gstride), s3 = ld_relaxed_gpu_s32(g0 + 4 * fuse.gstride);
+                        t_key = max(ld_relaxed_gpu_s32(g0), min(min(s0, s1), min(s2, s3)));
+                    }
+                    if (t_key > TKX_KEY_NEG_INF) sts_f32(thrs + 4 * myq, key_score(t_key - 1));
+                }
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+                continue;
+            }
             uint32_t pend[CPW];  // (row, query) pairs whose append found the buffer full
 #pragma unroll
             for (int cc = 0; cc < CPW; ++cc) pend[cc] = 0u;
@@ -282,10 +346,12 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
             // compaction phase reads whatever copy has landed.  A register load here costs an L2 round trip per
             // tile on the selection warps' critical path (measured: 2x the scan time at 64 queries); a stale
             // threshold only admits a few more candidates.
-            if (gthr != nullptr && lane < NQ / (TR_SEL_WARPS * 4)) {
-                const int i4 = (sw * (NQ / TR_SEL_WARPS) + lane * 4);
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n\tcp.async.commit_group;" ::"r"(gthr_s + 4 * i4),
-                             "l"(gthr + i4)
+            if (gthr != nullptr && lane < 5 * (NQ / (TR_SEL_WARPS * 4))) {
+                constexpr int LPA = NQ / (TR_SEL_WARPS * 4);  // lanes per array: 16-byte pieces of this warp's slice
+                const int a = lane / LPA;
+                const int i4 = sw * (NQ / TR_SEL_WARPS) + (lane % LPA) * 4;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n\tcp.async.commit_group;" ::"r"(gthr_s + 4 * (a * NQ + i4)),
+                             "l"(gthr + a * fuse.gstride + i4)
                              : "memory");
             }
             if (scans) {
@@ -366,8 +432,12 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                                   thrs + 4 * q, k, n, gthr != nullptr ? gthr + q : nullptr);
                     if (lane == 0) sts_s32(cnt + 4 * q, 0);
                 }
-                const int32_t gkey = (gthr != nullptr && lane < NQ / TR_SEL_WARPS && myq < nq) ? lds_s32(gthr_s + 4 * myq)
-                                                                                                : TKX_KEY_NEG_INF;
+                int32_t gkey = TKX_KEY_NEG_INF;
+                if (gthr != nullptr && lane < NQ / TR_SEL_WARPS && myq < nq) {
+                    const uint32_t gp = gthr_s + 4 * myq;
+                    gkey = max(lds_s32(gp), min(min(lds_s32(gp + 4 * NQ), lds_s32(gp + 8 * NQ)),
+                                                min(lds_s32(gp + 12 * NQ), lds_s32(gp + 16 * NQ))));
+                }
                 if (gkey > TKX_KEY_NEG_INF) {
                     // k rows score >= key_score(gkey) somewhere in the grid: nothing strictly below it can make the
                     // top k.  One ulp under it, so that rows EQUAL to it still get through (ties go by row number,
@@ -432,7 +502,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
 // barriers, alignment slack
 static int rows_fixed_bytes(int dim, int k, int pair) {
     const int nq = TK_QROWS * pair, buf = pair == 2 ? 16 : TR_BUF;
-    return (dim / TR_BK) * TR_QBLK_BYTES + nq * k * 8 + nq * buf * 8 + nq * 12 + 256 + 1024;
+    return (dim / TR_BK) * TR_QBLK_BYTES + nq * k * 8 + nq * buf * 8 + nq * 28 + 256 + 1024;
 }
 
 int topk_rows_preload_kernels() {
