@@ -450,7 +450,7 @@ int launch_d(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int
 }  // namespace
 
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
-                     int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream) {
+                     int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles, const uint32_t* rowinfo) {
     if (n_seq <= 0 || max_seqlen <= 0) return 0;
     const int d = H / heads;
     if (d * heads != H) return fail(LSC_E_INVALID, "attention: hidden not divisible by heads");
@@ -461,8 +461,10 @@ int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_
         LSC_CUDA(cudaGetDevice(&dev));
         if (dev >= 0 && dev < 64 && sms_cache[dev] == 0)
             LSC_CUDA(cudaDeviceGetAttribute(&sms_cache[dev], cudaDevAttrMultiProcessorCount, dev));
-        return attention_tc_launch(qkv, cu_seqlens, n_seq, T, H, heads, max_seqlen, ctx,
-                                   (dev >= 0 && dev < 64) ? sms_cache[dev] : 148, stream);
+        const int sms = (dev >= 0 && dev < 64) ? sms_cache[dev] : 148;
+        if (tiles != nullptr && rowinfo != nullptr)  // short sequences sharing 128-row tiles (attention_tc_packed.cu)
+            return attention_tc_packed_launch(qkv, cu_seqlens, n_seq, T, H, heads, max_seqlen, tiles, rowinfo, ctx, sms, stream);
+        return attention_tc_launch(qkv, cu_seqlens, n_seq, T, H, heads, max_seqlen, ctx, sms, stream);
     }
     if (d == 64 && attention_tc64_supported(H, heads)) {  // tcgen05, any sequence length
         static int sms_cache64[64] = {};
@@ -485,7 +487,26 @@ extern "C" int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_se
                                        void* d_ctx, void* stream) {
     if (d_qkv == nullptr || d_cu_seqlens == nullptr || d_ctx == nullptr || n_seq < 0 || hidden <= 0 || heads <= 0)
         return lsc::fail(LSC_E_INVALID, "lsc_debug_attention_dev: bad argument");
+    // LSC_DEBUG_ATTN_PACK=1 (tests): run with the packed tile list the encoder builds for batches of short sequences
+    int32_t* tiles = nullptr;
+    uint32_t* rowinfo = nullptr;
+    const char* pack = getenv("LSC_DEBUG_ATTN_PACK");
+    if (pack != nullptr && atoi(pack) != 0 && n_seq > 0 && n_seq <= lsc::attention_tiles_max_seqs() && hidden / heads == 32 &&
+        max_seqlen <= 128) {
+        if (cudaMalloc(reinterpret_cast<void**>(&tiles), static_cast<size_t>(2 * n_seq + 2 + total_tokens) * sizeof(int32_t)) != cudaSuccess)
+            return lsc::fail(LSC_E_NOMEM, "lsc_debug_attention_dev: tile list");
+        rowinfo = reinterpret_cast<uint32_t*>(tiles + 2 * n_seq + 2);
+        const int trc = lsc::attention_tiles_launch(d_cu_seqlens, n_seq, total_tokens, tiles, rowinfo, static_cast<cudaStream_t>(stream));
+        if (trc < 0) {
+            cudaFree(tiles);
+            return trc;
+        }
+    }
     int rc = lsc::attention_launch(static_cast<const __nv_bfloat16*>(d_qkv), d_cu_seqlens, n_seq, total_tokens, hidden,
-                                   heads, max_seqlen, static_cast<__nv_bfloat16*>(d_ctx), static_cast<cudaStream_t>(stream));
+                                   heads, max_seqlen, static_cast<__nv_bfloat16*>(d_ctx), static_cast<cudaStream_t>(stream), tiles, rowinfo);
+    if (tiles != nullptr) {
+        cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
+        cudaFree(tiles);
+    }
     return rc < 0 ? rc : LSC_OK;
 }

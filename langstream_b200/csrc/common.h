@@ -154,10 +154,19 @@ int layernorm_launch(const __nv_bfloat16* in, const float* gamma, const float* b
 // Packed variable-length multi-head self-attention over qkv [T,3H] -> ctx [T,H].
 // qkv: Q and K thirds bf16, V third fp16.  Dispatches to the tcgen05 kernel (attention_tc.cu) for
 // d_head 32 and sequences of at most 128 tokens, else to the mma.sync kernel (attention.cu).
+// tiles (optional, only used by the d_head 32 / s <= 128 kernel): the packing of short sequences into 128-row
+// attention tiles built by attention_tiles_launch for the same cu_seqlens (tiles: 2 * n_seq + 2 ints; rowinfo: one
+// word per token row = the key range of the row's own sequence inside its tile).
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
-                     int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream);
+                     int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles = nullptr,
+                     const uint32_t* rowinfo = nullptr);
 int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                         int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
+int attention_tc_packed_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
+                               int max_seqlen, const int32_t* tiles, const uint32_t* rowinfo, __nv_bfloat16* ctx,
+                               int num_sms, cudaStream_t stream);
+int attention_tiles_max_seqs();
+int attention_tiles_launch(const int32_t* cu_seqlens, int n_seq, int T, int32_t* tiles, uint32_t* rowinfo, cudaStream_t stream);
 // tcgen05 attention for d_head 64 and any sequence length (attention_tc64.cu).
 bool attention_tc64_supported(int H, int heads);
 int attention_tc64_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,

@@ -7,6 +7,7 @@
 // (paths under langstream-agents/langstream-ai-agents/src/main/java/com/datastax/oss/streaming/ai).
 #include <algorithm>
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -83,6 +84,8 @@ struct lsc_encoder {
     AsyncSlot slots[2];
     cudaStream_t stream_in = nullptr, stream_out = nullptr;
     int64_t next_ticket = 0;
+    int32_t* d_tiles = nullptr;  // attention tile list of the current pass (attention_tc.cu): 2 * n_seq + 2 ints, then T row words
+    int64_t cap_tiles = 0;
     float* stats_x = nullptr;   // [cap_tokens][stats_p][2] partial row statistics of x / tmp (LN folding)
     float* stats_1 = nullptr;
     int stats_p = 0;    // partials per row of stats_1 (written by the attention-output GEMM)
@@ -259,7 +262,31 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
     const int H = c.hidden, F = c.ffn;
     int64_t nlaunch = 0;
     if (T > 0) LSC_TRY(ensure_workspace(e, T));
+    // Short sequences (fewer than 48 tokens on average) share 128-row attention tiles with a block-diagonal mask
+    // (attention_tc_packed.cu); the tile list is built once per pass and serves every layer.
+    static const bool no_pack = getenv("LSC_ATTN_NO_PACK") != nullptr;  // debug: one attention tile per sequence
+    const bool pack_tiles = !no_pack && T > 0 && H / c.heads == 32 && max_seqlen <= 128 && n_seq > 1 &&
+                            n_seq <= attention_tiles_max_seqs() &&
+                            static_cast<int64_t>(n_seq) * 48 > static_cast<int64_t>(T);
+    const int64_t tiles_need = 2 * static_cast<int64_t>(n_seq) + 2 + T;
+    if (pack_tiles && tiles_need > e->cap_tiles) {
+        LSC_CUDA(cudaDeviceSynchronize());
+        if (e->d_tiles) cudaFree(e->d_tiles);
+        e->d_tiles = nullptr;
+        e->cap_tiles = 0;
+        const int64_t cap = std::max<int64_t>(tiles_need + tiles_need / 4, 1 << 16);
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&e->d_tiles), cap * sizeof(int32_t)));
+        e->cap_tiles = cap;
+    }
     if (e->ev_recorded) LSC_CUDA(cudaStreamWaitEvent(st, e->ev_last, 0));
+    const int32_t* tiles = nullptr;
+    const uint32_t* rowinfo = nullptr;
+    if (pack_tiles) {
+        uint32_t* ri = reinterpret_cast<uint32_t*>(e->d_tiles + 2 * n_seq + 2);
+        LSC_LAUNCH(2, attention_tiles_launch(d_cu, n_seq, T, e->d_tiles, ri, st));
+        tiles = e->d_tiles;
+        rowinfo = ri;
+    }
     if (T > 0) {
         if (c.gemm_impl == 0) {
             // ---- product path: tcgen05 GEMMs, every LayerNorm folded into the neighbouring epilogues ----
@@ -294,7 +321,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                 ln_in.c = w.c_qkv; ln_in.stats_in = e->stats_x; ln_in.p_in = PX; ln_in.inv_h = inv_h; ln_in.eps = c.ln_eps;
                 LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.d_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H,
                                    EPI_LNIN_BIAS, 2 * H, ln_in, st));
-                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo));
                 LnArgs ln_o;  // tmp = ctx.Wo^T + b + LN_in(x); statistics of tmp -> stats_1
                 ln_o.stats_in = e->stats_x; ln_o.p_in = PX; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
                 ln_o.inv_h = inv_h; ln_o.eps = c.ln_eps;
@@ -323,7 +350,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
             for (int l = 0; l < c.layers; ++l) {
                 const LayerW& w = e->layers[l];
                 LSC_LAUNCH(1, gemm(e, none, e->x, none, w.w_qkv, w.b_qkv, nullptr, none, e->qkv, T, 3 * H, H, EPI_BIAS, 2 * H, no_ln, st));
-                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo));
                 LSC_LAUNCH(1, gemm(e, none, e->ctx, none, w.w_o, w.b_o, e->x, none, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, H, no_ln, st));
                 LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
                 LSC_LAUNCH(1, gemm(e, none, e->x1, none, w.w_1, w.b_1, nullptr, none, e->ffn, T, F, H, EPI_BIAS_GELU, F, no_ln, st));
@@ -370,7 +397,7 @@ void lsc_encoder_destroy(lsc_encoder* e) {
     if (e->stream_in) cudaStreamDestroy(e->stream_in);
     if (e->stream_out) cudaStreamDestroy(e->stream_out);
     for (void* p : e->owned) cudaFree(p);
-    void* ws[] = {e->x, e->x1, e->tmp, e->qkv, e->ctx, e->ffn, e->d_ids, e->d_cu, e->d_out, e->stats_x, e->stats_1};
+    void* ws[] = {e->x, e->x1, e->tmp, e->qkv, e->ctx, e->ffn, e->d_ids, e->d_cu, e->d_out, e->stats_x, e->stats_1, e->d_tiles};
     for (void* p : ws)
         if (p) cudaFree(p);
     if (e->stream) cudaStreamDestroy(e->stream);

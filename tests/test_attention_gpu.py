@@ -59,3 +59,35 @@ def test_attention_matches_fp32_reference(native_lib, cuda_device, H, heads, len
     tol = 0.01 * scale + 0.01 * ref.abs()
     assert bool((err <= tol).all()), f"max err {err.max().item():.4f} (ref magnitude {ref.abs().max().item():.2f})"
     assert err.mean().item() < 2e-3 * scale
+
+
+@pytest.mark.parametrize("lens", [
+    [128] * 3 + [1] * 200 + [64, 64, 65, 63, 127, 1, 128, 2, 126],       # full tiles, 128 one-token sequences per tile, exact fits
+    [17, 40, 9, 0, 0, 61, 1, 128, 3, 3, 3, 100, 28, 29, 70, 58, 0],      # empty sequences inside and at the end of tiles
+    list(np.random.default_rng(5).integers(1, 129, 400)),                # UniformInt[1,128], more tiles than SMs x heads / 12
+])
+def test_packed_tiles_match_fp32_reference(native_lib, cuda_device, lens, monkeypatch):
+    """Short sequences sharing a 128-row attention tile (block-diagonal mask): every sequence still attends only to
+    itself - same fp32 reference, same tolerance as the one-tile-per-sequence path."""
+    import torch
+    from langstream_b200 import _native
+
+    monkeypatch.setenv("LSC_DEBUG_ATTN_PACK", "1")
+    H, heads = 384, 12
+    lens = [int(x) for x in lens]
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    T = int(cu[-1])
+    g = torch.Generator(device="cpu").manual_seed(len(lens))
+    qkv = torch.randn(T, 3 * H, generator=g).to(torch.bfloat16).to(cuda_device)
+    packed = qkv.clone()
+    packed[:, 2 * H:] = qkv[:, 2 * H:].to(torch.float16).view(torch.bfloat16)
+    ctx = torch.full((T, H), float("nan"), dtype=torch.bfloat16, device=cuda_device)
+    d_cu = torch.from_numpy(cu).to(cuda_device)
+    _native.debug_attention_dev(packed, d_cu, len(lens), T, H, heads, max(lens), ctx, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    ref = _reference(qkv, cu, H, heads)
+    got = ctx.float()
+    assert torch.isfinite(got).all()
+    err = (got - ref).abs()
+    assert bool((err <= 0.01 + 0.01 * ref.abs()).all()), f"max err {err.max().item():.4f}"
+    assert err.mean().item() < 2e-3

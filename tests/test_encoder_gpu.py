@@ -353,3 +353,29 @@ def test_passes_on_different_streams_do_not_overlap(native_lib, cuda_device):
         for d_out, (_, _, ref) in zip(outs, batches):
             assert np.array_equal(d_out.cpu().numpy(), ref)
     enc.close()
+
+
+def test_short_sequences_take_the_packed_attention_tiles(native_lib, cuda_device):
+    """Texts of a few dozen tokens (average below 48): several sequences share one 128-row attention tile with a
+    block-diagonal mask.  Every row against the fp32 oracle, and each embedding independent of its neighbours."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+    from oracle.encoder_oracle import HFOracle
+
+    spec = W.MINILM_L6
+    blob = W.random_init(spec, seed=5, perturb=True)
+    ids, cu = W.synthetic_token_ids(600, 64, seed=78, min_len=1)
+    assert cu[-1] < 48 * 600
+    enc = Encoder(spec, blob)
+    got = enc.embed(ids, cu)
+    want = HFOracle(spec, blob).embed_one_by_one(ids, cu)
+    _report("minilm_600_short_sequences_packed_tiles", got, want)
+    _check(got, want)
+    pick = [0, 3, 4, 5, 250, 599]   # other neighbours, other positions inside their tiles
+    sub_ids = np.concatenate([ids[cu[i]:cu[i + 1]] for i in pick])
+    sub_cu = np.concatenate([[0], np.cumsum([cu[i + 1] - cu[i] for i in pick])]).astype(np.int32)
+    sub = enc.embed(sub_ids, sub_cu)
+    # same math per sequence; the fp32 summation order inside a tile depends on the position, and one flipped bf16
+    # rounding of an attention output travels through the remaining layers
+    assert np.abs(sub - got[pick]).max() <= 2e-4
+    enc.close()
