@@ -232,6 +232,68 @@ def topk_cpu_baseline(max_seconds: float = 12.0):
     return out
 
 
+class _LazyRows:
+    """Host row store stand-in for the batching figure: row i is {"id": i} (a real table keeps every column)."""
+
+    def __getitem__(self, i):
+        return {"id": int(i)}
+
+    def __len__(self):
+        return 0
+
+
+def query_batching_figure(dev, stream, n_rows: int = 1_000_000):
+    """SURVEY.md 8(f) row 4 through the datasource mirror (`CudaVectorDataSource.fetch_data`, the call QueryStep
+    makes, QueryStep.java:174-198) on a 1M x 384 table: one query per call the way the reference's runtime issues
+    them (SingleRecordAgentProcessor.java:31-47), against 64 concurrent callers and 1024 requests in flight that the
+    cross-caller micro-batcher answers with one search per <=128 queries.  Host-side Python is part of the figure."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from langstream_b200 import vector
+
+    name = "bench_docs"
+    table = vector.get_table(name, TOPK_DIM, "vector", dev.index or 0)
+    for o in range(0, n_rows, 1 << 20):
+        m = min(1 << 20, n_rows - o)
+        v = torch.randn(m, TOPK_DIM, generator=torch.Generator(device=dev).manual_seed(7 + o), device=dev)
+        table.index.upsert_dev(np.arange(o, o + m, dtype=np.int64), v, m, stream)
+    table.rows = _LazyRows()
+    rng = np.random.default_rng(11)
+    queries = rng.standard_normal((1024, TOPK_DIM)).astype(np.float32)
+    sql = f"SELECT id FROM {name} ORDER BY cosine_similarity(vector,cast(? as float array)) DESC LIMIT {TOPK_K}"
+    out = {"table": f"{n_rows} x {TOPK_DIM}", "k": TOPK_K}
+    plain = vector.CudaVectorDataSource()
+    plain.initialize({"service": "cuda"})
+    for i in range(5):
+        plain.fetch_data(sql, [queries[i]])
+    t0 = time.perf_counter()
+    first = [plain.fetch_data(sql, [queries[i]]) for i in range(200)]
+    out["one_query_per_call_qps"] = 200 / (time.perf_counter() - t0)
+    ds = vector.CudaVectorDataSource()
+    ds.initialize({"service": "cuda", "query-batch-size": 128, "query-flush-interval-ms": 1.0})
+    for f in [ds.fetch_data_async(sql, [queries[i]]) for i in range(128)]:
+        f.result()
+    t0 = time.perf_counter()
+    futs = [ds.fetch_data_async(sql, [queries[i]]) for i in range(1024)]
+    res = [f.result() for f in futs]
+    out["1024_requests_in_flight_qps"] = 1024 / (time.perf_counter() - t0)
+    out["same_rows_as_one_at_a_time"] = bool(res[:200] == first)
+    with ThreadPoolExecutor(64) as ex:
+        t0 = time.perf_counter()
+        list(ex.map(lambda i: ds.fetch_data(sql, [queries[i]]), range(1024)))
+        out["64_blocking_callers_qps"] = 1024 / (time.perf_counter() - t0)
+    out["searches_issued"] = ds._batcher.batches
+    out["queries_answered"] = ds._batcher.queries
+    t0 = time.perf_counter()
+    many = ds.fetch_data_many(sql, [[queries[i]] for i in range(1024)])
+    out["fetch_data_many_1024_qps"] = 1024 / (time.perf_counter() - t0)
+    out["same_rows_many"] = bool(many[:200] == first)
+    ds.close()
+    plain.close()
+    vector.drop_table(name)
+    return out
+
+
 def run_topk(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks, pk, peak_tf):
     """Top-10 queries/s over a 10M x 384 bf16 corpus row-sharded over the ranks, B = 1 / 64 / 1024.
 
@@ -407,6 +469,11 @@ def run_topk(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks
                         "h2d_bytes_per_step": int(B * TOPK_DIM * 4), "d2h_bytes_per_step": int(B * TOPK_K * 12)}
         topk["batches"][str(B)] = entry
     topk["gpu_launches_per_batch"] = {"1": 2, "64": 2, "1024": 6}  # normalise + fused scan; B > 256: normalise + 4 scans + merge
+    if rank == 0 and world == 1:
+        try:
+            topk["query_batching"] = query_batching_figure(dev, stream)
+        except Exception as e:  # noqa: BLE001 - an extra figure must not take the benchmark down
+            topk["query_batching"] = {"error": str(e)}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             topk["cpu_baseline"] = topk_cpu_baseline()

@@ -367,6 +367,47 @@ class QueryVectorDBAgent:
         self.step.process(out)
         return [out]
 
+    def process(self, records: List[Record], sink: Callable[[Record, List[Record], Optional[Exception]], None]) -> None:
+        """AgentProcessor.process(List<Record>, RecordSink) (AgentProcessor.java:23-46) with the whole list answered
+        by ONE search - what SURVEY.md 8(f) row 4 asks of `query-vector-db` instead of SingleRecordAgentProcessor's
+        one synchronous query per record (SingleRecordAgentProcessor.java:31-47).  The contract is unchanged:
+        exactly one `sink(source, results, error)` per input record, in input order, never an exception out of
+        process.  Steps the batch form does not cover (mode execute, loop-over) take the per-record path."""
+        step = self.step
+        batchable = (step.mode == QueryStep.MODE_QUERY and step.loop_over is None
+                     and hasattr(self.data_source, "fetch_data_many"))
+        if not batchable or len(records) <= 1:
+            for record in records:
+                try:
+                    sink(record, self.process_record(record), None)
+                except Exception as e:  # noqa: BLE001 - reported, not raised (SingleRecordAgentProcessor.java:41-45)
+                    sink(record, [], e)
+            return
+        outs, params, errors = [], [], []
+        for record in records:
+            out = Record(key=record.key, value=record.value, headers=dict(record.headers))
+            outs.append(out)
+            try:
+                work = Record(key=_as_obj(out.key), value=_as_obj(out.value), headers=out.headers)
+                params.append(step._params(work))
+                errors.append(None)
+            except Exception as e:  # noqa: BLE001
+                params.append(None)
+                errors.append(e)
+        live = [i for i, e in enumerate(errors) if e is None]
+        fetched = self.data_source.fetch_data_many(step.query, [params[i] for i in live]) if live else []
+        for i, res in zip(live, fetched):
+            if isinstance(res, Exception):
+                errors[i] = res
+                continue
+            try:
+                rows = res or []
+                set_result_field(outs[i], step.output_field, (rows[0] if rows else {}) if step.only_first else rows)
+            except Exception as e:  # noqa: BLE001
+                errors[i] = e
+        for record, out, err in zip(records, outs, errors):
+            sink(record, [] if err is not None else [out], err)
+
     def close(self) -> None:
         if self.data_source is not None:
             self.data_source.close()

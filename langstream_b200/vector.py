@@ -17,6 +17,7 @@ from __future__ import annotations
 import json
 import re
 import threading
+import time
 from concurrent.futures import Future
 from dataclasses import dataclass, field
 from typing import Any, Callable, Dict, List, Optional, Tuple
@@ -229,8 +230,89 @@ class CudaVectorTable:
             ids, scores = self.index.search(self._pad(q[0])[None, :], k)
             return [(self.rows[int(i)], float(s)) for i, s in zip(ids[0], scores[0]) if i >= 0]
 
+    def search_many(self, vectors, k: int) -> List[List[Tuple[dict, float]]]:
+        """One native call (one pass over the corpus per 128 / 256 queries) for a whole batch of query vectors."""
+        q = np.asarray(vectors, np.float32).reshape(-1, self.dim)
+        if q.shape[0] == 0:
+            return []
+        if self.store_dim != self.dim:
+            padded = np.zeros((q.shape[0], self.store_dim), np.float32)
+            padded[:, : self.dim] = q
+            q = padded
+        with self.lock:
+            ids, scores = self.index.search(np.ascontiguousarray(q), k)
+            return [[(self.rows[int(i)], float(s)) for i, s in zip(ids[b], scores[b]) if i >= 0] for b in range(q.shape[0])]
+
     def close(self) -> None:
         self.index.close()
+
+
+class QueryBatcher:
+    """Cross-caller micro-batcher for vector queries.
+
+    The reference answers one query per record, synchronously (SingleRecordAgentProcessor.java:31-47; fused
+    pipelines feed List.of(record), CompositeAgentProcessor.java:225-227), which on a GPU means one pass over the
+    whole corpus per record.  A pass serves up to 128 queries for the same HBM traffic, so queries from all
+    callers (agent threads, gateway sessions) are collected here and sent as one batch when `max_batch` are
+    waiting or the oldest is `flush_interval_ms` old - the same window logic as CudaEmbeddingsService."""
+
+    def __init__(self, max_batch: int = 64, flush_interval_ms: float = 1.0):
+        self.max_batch, self._flush_s = int(max_batch), float(flush_interval_ms) / 1000.0
+        self._cv = threading.Condition()
+        self._pending: List[tuple] = []  # (table, k, vector, future, enqueue time)
+        self._closed = False
+        self.batches = 0
+        self.queries = 0
+        self._worker = threading.Thread(target=self._run, name="lsc-query-batcher", daemon=True)
+        self._worker.start()
+
+    def submit(self, table: CudaVectorTable, vector, k: int) -> "Future[List[Tuple[dict, float]]]":
+        fut: Future = Future()
+        v = np.asarray(vector, np.float32).reshape(-1)
+        if v.size != table.dim:
+            fut.set_exception(ValueError(f"query vector has {v.size} dimensions, table {table.name!r} has {table.dim}"))
+            return fut
+        with self._cv:
+            if self._closed:
+                fut.set_exception(RuntimeError("datasource is closed"))
+                return fut
+            self._pending.append((table, int(k), v, fut, time.monotonic()))
+            self._cv.notify()
+        return fut
+
+    def close(self) -> None:
+        with self._cv:
+            self._closed = True
+            self._cv.notify()
+        self._worker.join(timeout=10)
+
+    def _run(self) -> None:
+        while True:
+            with self._cv:
+                while not self._pending and not self._closed:
+                    self._cv.wait()
+                if not self._pending and self._closed:
+                    return
+                while not self._closed:
+                    age = time.monotonic() - self._pending[0][4]
+                    if len(self._pending) >= self.max_batch or age >= self._flush_s:
+                        break
+                    self._cv.wait(timeout=max(self._flush_s - age, 0.0002))
+                # one native call per (table, k): take the oldest request's group, leave the rest for the next turn
+                table, k = self._pending[0][0], self._pending[0][1]
+                batch = [p for p in self._pending if p[0] is table and p[1] == k][: self.max_batch]
+                taken = set(id(p) for p in batch)
+                self._pending = [p for p in self._pending if id(p) not in taken]
+            try:
+                hits = table.search_many(np.stack([p[2] for p in batch]), k)
+                self.batches += 1
+                self.queries += len(batch)
+                for p, h in zip(batch, hits):
+                    p[3].set_result(h)
+            except Exception as e:  # noqa: BLE001 - every caller of the batch sees the failure, as its own call would
+                for p in batch:
+                    if not p[3].done():
+                        p[3].set_exception(e)
 
 
 _TABLES: Dict[str, CudaVectorTable] = {}
@@ -309,11 +391,20 @@ class CudaVectorDataSource:
     def __init__(self, index_factory=None):
         self._config: dict = {}
         self._index_factory = index_factory
+        self._batcher: Optional[QueryBatcher] = None
 
     def initialize(self, config: dict) -> None:
+        """Datasource configuration; besides `service: cuda` / `device`:
+        `query-batch-size` (default 1 = every fetchData is its own search) and `query-flush-interval-ms`
+        (default 1.0) switch on the cross-caller micro-batcher: concurrent fetch_data calls are answered by one
+        search of up to that many queries."""
         self._config = dict(config or {})
+        size = int(self._config.get("query-batch-size", 1) or 1)
+        if size > 1:
+            self._batcher = QueryBatcher(size, float(self._config.get("query-flush-interval-ms", 1.0)))
 
-    def fetch_data(self, query: str, params: List[Any]) -> List[Dict[str, Any]]:
+    def _resolve(self, query: str, params: List[Any]):
+        """(table, query vector, k, projection of one hit) of a query string + positional parameters."""
         m = _SQL.match(query or "")
         if m:
             if len(params) < 1:
@@ -322,8 +413,7 @@ class CudaVectorDataSource:
             table = get_table(m.group("table"))
             if m.group("vec") != table.vector_column:
                 raise ValueError(f"{m.group('vec')!r} is not the vector column of table {table.name!r}")
-            hits = table.search(params[0], int(m.group("k")))
-            return [self._project(row, score, cols, False) for row, score in hits]
+            return table, params[0], int(m.group("k")), (lambda row, score: self._project(row, score, cols, False))
         try:
             spec = json.loads(interpolate(query, params))
         except Exception as e:  # noqa: BLE001
@@ -331,9 +421,65 @@ class CudaVectorDataSource:
         if not isinstance(spec, dict) or "vector" not in spec:
             raise ValueError("query must be the cosine SQL form or a JSON object with a 'vector'")
         table = get_table(spec.get("table") or self._config.get("table-name") or "documents")
-        hits = table.search(spec["vector"], int(spec.get("topK", 10)))
         cols = spec.get("select") or ["*"]
-        return [self._project(row, score, cols, bool(spec.get("include-similarity", True))) for row, score in hits]
+        sim = bool(spec.get("include-similarity", True))
+        return table, spec["vector"], int(spec.get("topK", 10)), (lambda row, score: self._project(row, score, cols, sim))
+
+    def fetch_data(self, query: str, params: List[Any]) -> List[Dict[str, Any]]:
+        table, vector, k, project = self._resolve(query, params)
+        if self._batcher is not None:  # joins whatever other callers are asking at this moment
+            hits = self._batcher.submit(table, vector, k).result()
+        else:
+            hits = table.search(vector, k)
+        return [project(row, score) for row, score in hits]
+
+    def fetch_data_async(self, query: str, params: List[Any]) -> "Future[List[Dict[str, Any]]]":
+        """fetch_data that returns at once (needs the micro-batcher): the shape an asynchronous agent wants - it
+        keeps many records in flight and lets them meet in one search."""
+        out: Future = Future()
+        try:
+            table, vector, k, project = self._resolve(query, params)
+            if self._batcher is None:
+                out.set_result([project(row, score) for row, score in table.search(vector, k)])
+                return out
+            inner = self._batcher.submit(table, vector, k)
+        except Exception as e:  # noqa: BLE001
+            out.set_exception(e)
+            return out
+
+        def done(f):
+            try:
+                out.set_result([project(row, score) for row, score in f.result()])
+            except Exception as e:  # noqa: BLE001
+                out.set_exception(e)
+
+        inner.add_done_callback(done)
+        return out
+
+    def fetch_data_many(self, query: str, params_list: List[List[Any]]) -> List[Any]:
+        """One search for a whole list of parameter sets of the same query (a batch of records handed to
+        AgentProcessor.process at once).  Element i is the row list of params_list[i], or the exception that
+        params_list[i] alone would have raised."""
+        out: List[Any] = [None] * len(params_list)
+        groups: Dict[tuple, list] = {}
+        for i, params in enumerate(params_list):
+            try:
+                table, vector, k, project = self._resolve(query, params)
+                v = np.asarray(vector, np.float32).reshape(-1)
+                if v.size != table.dim:
+                    raise ValueError(f"query vector has {v.size} dimensions, table {table.name!r} has {table.dim}")
+                groups.setdefault((id(table), k), []).append((i, table, v, project))
+            except Exception as e:  # noqa: BLE001
+                out[i] = e
+        for (_, k), items in groups.items():
+            try:
+                hits = items[0][1].search_many(np.stack([it[2] for it in items]), k)
+                for (i, _, _, project), h in zip(items, hits):
+                    out[i] = [project(row, score) for row, score in h]
+            except Exception as e:  # noqa: BLE001
+                for i, _, _, _ in items:
+                    out[i] = e
+        return out
 
     @staticmethod
     def _project(row: dict, score: float, cols: List[str], with_similarity: bool) -> Dict[str, Any]:
@@ -353,7 +499,9 @@ class CudaVectorDataSource:
         return {}
 
     def close(self) -> None:
-        pass
+        if self._batcher is not None:
+            self._batcher.close()
+            self._batcher = None
 
 
 class CudaVectorDataSourceProvider:

@@ -209,3 +209,81 @@ def test_batched_sink_persistence_and_asset_manager(fake_tables, tmp_path):
     assert not (tmp_path / "docs.lscidx").exists()
     a.deploy_asset()
     assert a.asset_exists() and ds.fetch_data(sql, [vecs[0].tolist()]) == []
+
+
+def _fill_docs(index_factory, n=300, dim=64, seed=3):
+    from langstream_b200 import vector
+
+    rng = np.random.default_rng(seed)
+    vecs = rng.standard_normal((n, dim)).astype(np.float32)
+    t = vector.get_table("documents", dim, "vector", 0, index_factory)
+    t.upsert_many([(f"d{i}",) for i in range(n)], [{"name": f"d{i}", "vector": vecs[i].tolist(), "text": f"text {i}"} for i in range(n)])
+    return vecs
+
+
+def test_query_micro_batcher_answers_concurrent_callers_with_one_search(fake_tables):
+    """many callers, each with ONE query (the shape SingleRecordAgentProcessor.java:31-47
+    gives), are answered by a handful of batched searches - and every caller gets exactly the rows its own
+    synchronous fetch_data would have returned."""
+    import threading
+    from langstream_b200.vector import CudaVectorDataSourceProvider
+
+    vecs = _fill_docs(fake_tables)
+    sql = "SELECT name,text FROM documents ORDER BY cosine_similarity(vector,cast(? as float array)) DESC LIMIT 5"
+    plain = CudaVectorDataSourceProvider(fake_tables).create_data_source_implementation({"service": "cuda"})
+    plain.initialize({"service": "cuda"})
+    want = [plain.fetch_data(sql, [vecs[i].tolist()]) for i in range(64)]
+    ds = CudaVectorDataSourceProvider(fake_tables).create_data_source_implementation({"service": "cuda"})
+    ds.initialize({"service": "cuda", "query-batch-size": 32, "query-flush-interval-ms": 50})
+    got = [None] * 64
+    start = threading.Barrier(64)
+
+    def caller(i):
+        start.wait()
+        got[i] = ds.fetch_data(sql, [vecs[i].tolist()])
+
+    threads = [threading.Thread(target=caller, args=(i,)) for i in range(64)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert got == want
+    assert ds._batcher.queries == 64 and ds._batcher.batches <= 8   # 64 one-query calls, a handful of searches
+    # asynchronous form + per-request errors
+    futs = [ds.fetch_data_async(sql, [vecs[i].tolist()]) for i in range(10)] + [ds.fetch_data_async(sql, [[1.0, 2.0]])]
+    assert [f.result(5) for f in futs[:10]] == want[:10]
+    assert isinstance(futs[10].exception(5), ValueError)
+    ds.close()
+    plain.close()
+
+
+def test_query_agent_processes_a_list_of_records_with_one_search(fake_tables):
+    """AgentProcessor.process(List<Record>, sink): one emit per record, in order, errors per record; the results are
+    those of the per-record path (QueryVectorDBAgent.java:66-79)."""
+    from langstream_b200.agents import QueryVectorDBAgent
+    from langstream_b200.vector import CudaVectorDataSourceProvider, Record
+
+    vecs = _fill_docs(fake_tables)
+    cfg = {"datasource": {"service": "cuda"}, "output-field": "value.related",
+           "query": "SELECT name FROM documents ORDER BY cosine_similarity(vector,cast(? as float array)) DESC LIMIT 3",
+           "fields": ["value.embeddings"]}
+    agent = QueryVectorDBAgent([CudaVectorDataSourceProvider(fake_tables)])
+    agent.init(cfg)
+    records = [Record(key=f"k{i}", value={"q": i, "embeddings": vecs[i].tolist()}) for i in range(20)]
+    records[7] = Record(key="bad", value={"q": 7, "embeddings": [1.0, 2.0, 3.0]})   # wrong dimension: this record fails
+    emitted = []
+    agent.process(records, lambda src, res, err: emitted.append((src, res, err)))
+    assert [e[0] for e in emitted] == records
+    for i, (src, res, err) in enumerate(emitted):
+        if i == 7:
+            assert res == [] and isinstance(err, ValueError)
+            continue
+        assert err is None and len(res) == 1
+        assert res[0].value["related"] == agent.process_record(records[i])[0].value["related"]
+        assert res[0].value["related"][0] == {"name": f"d{i}"}
+    calls = []
+    orig = agent.data_source.fetch_data_many
+    agent.data_source.fetch_data_many = lambda q, p: (calls.append(len(p)), orig(q, p))[1]
+    agent.process(records[:5], lambda *a: None)
+    assert calls == [5]
+    agent.close()

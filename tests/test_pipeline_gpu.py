@@ -206,3 +206,55 @@ def test_chatbot_flow_through_the_agent_mirrors(native_lib, cuda_device):
     qstep.batch_executor.stop()
     provider.close()
     vector.drop_table("chunks2")
+
+
+def test_query_micro_batcher_on_gpu(native_lib, cuda_device):
+    """64 concurrent one-query callers through CudaVectorDataSource.fetch_data with the micro-batcher on: the same
+    rows as the one-at-a-time path, from a handful of searches; and a list of records through the batched
+    query-vector-db agent mirror."""
+    import threading
+
+    from langstream_b200 import vector
+    from langstream_b200.agents import QueryVectorDBAgent
+    from langstream_b200.vector import CudaVectorDataSource, Record
+
+    n, dim = 50_000, 384
+    rng = np.random.default_rng(21)
+    vecs = rng.standard_normal((n, dim)).astype(np.float32)
+    t = vector.get_table("qb_docs", dim, "vector", 0)
+    try:
+        t.upsert_many([(i,) for i in range(n)], [{"id": i, "vector": vecs[i], "text": f"t{i}"} for i in range(n)])
+        queries = vecs[:64] + 0.05 * rng.standard_normal((64, dim)).astype(np.float32)
+        sql = "SELECT id,text FROM qb_docs ORDER BY cosine_similarity(vector,cast(? as float array)) DESC LIMIT 10"
+        plain = CudaVectorDataSource()
+        plain.initialize({"service": "cuda"})
+        want = [plain.fetch_data(sql, [q]) for q in queries]
+        assert all(w[0]["id"] == i for i, w in enumerate(want))
+        ds = CudaVectorDataSource()
+        ds.initialize({"service": "cuda", "query-batch-size": 64, "query-flush-interval-ms": 20})
+        got = [None] * 64
+        start = threading.Barrier(64)
+
+        def caller(i):
+            start.wait()
+            got[i] = ds.fetch_data(sql, [queries[i]])
+
+        threads = [threading.Thread(target=caller, args=(i,)) for i in range(64)]
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        assert got == want
+        assert ds._batcher.batches <= 8
+        assert ds.fetch_data_many(sql, [[q] for q in queries]) == want
+        agent = QueryVectorDBAgent()
+        agent.init({"datasource": {"service": "cuda"}, "output-field": "value.hits", "query": sql, "fields": ["value.e"]})
+        emitted = []
+        agent.process([Record(key=i, value={"e": queries[i].tolist()}) for i in range(64)],
+                      lambda src, res, err: emitted.append((res, err)))
+        assert [e[0][0].value["hits"] for e in emitted] == want and all(e[1] is None for e in emitted)
+        agent.close()
+        ds.close()
+        plain.close()
+    finally:
+        vector.drop_table("qb_docs")
