@@ -486,6 +486,178 @@ def run_topk(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks
 
 
 # ---------------------------------------------------------------------------------------------
+# config 5: the whole pipeline, native-only
+# ---------------------------------------------------------------------------------------------
+PIPE_WORDS_PER_DOC = 57      # x ("w12345" + blank) ~ 400 characters, the chunk size of the reference's crawler example
+PIPE_VOCAB_WORDS = 30000
+
+
+def _splitmix(x):
+    x = (x + np.uint64(0x9E3779B97F4A7C15)) & np.uint64(0xFFFFFFFFFFFFFFFF)
+    x = ((x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & np.uint64(0xFFFFFFFFFFFFFFFF)
+    x = ((x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & np.uint64(0xFFFFFFFFFFFFFFFF)
+    return x ^ (x >> np.uint64(31))
+
+
+def pipe_doc_words(doc_ids: np.ndarray) -> np.ndarray:
+    """[m, 57] word indices of documents `doc_ids`: a pure function of (seed 7, document id, position), so that any
+    rank can rebuild the text of any document it gets back from a query."""
+    with np.errstate(over="ignore"):
+        base = doc_ids.astype(np.uint64)[:, None] * np.uint64(PIPE_WORDS_PER_DOC) + np.arange(PIPE_WORDS_PER_DOC, dtype=np.uint64)[None, :]
+        return (_splitmix(base + np.uint64(7) * np.uint64(0x1000003)) % np.uint64(PIPE_VOCAB_WORDS)).astype(np.int64)
+
+
+def run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks, enc, spec):
+    """BASELINE configs[4] / SURVEY.md 8(d) config 5 as a NATIVE-ONLY end-to-end figure (the JVM stages around it -
+    runtime-tester, Kafka, text-splitter - cannot run here; the shape is examples/applications/docker-chatbot/
+    crawler.yaml:62-125 + chatbot.yaml:40-61): n synthetic ~400-character documents (seed 7), split over the ranks ->
+    lsc_tokenizer_encode -> lsc_encoder_embed_dev -> lsc_index_upsert_dev (GPU-resident sink, no List<Double> in
+    between) ; then 1024 query texts -> tokenise -> embed -> top-20 over all shards (lsc_index_search_sharded_dev)
+    -> MMR re-rank on the device (lsc_rerank_mmr_dev, the query's BM25 term statistics from the host).  Text
+    generation is outside the timed regions (it stands in for the topic the documents arrive on)."""
+    import queue
+    import torch
+    import torch.distributed as dist
+    from langstream_b200._native import Exchange, Index, WordPieceTokenizer, lib as _lib, check as _check
+    from langstream_b200.rerank import term_statistics
+
+    n_docs = args.pipeline_docs
+    lo, hi = n_docs * rank // world, n_docs * (rank + 1) // world
+    n_local = hi - lo
+    words = [f"w{i}" for i in range(PIPE_VOCAB_WORDS)]
+    W_obj = np.array(words, dtype=object)
+    threads = max(1, (os.cpu_count() or 1) // world)
+    tok = WordPieceTokenizer("\n".join(["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words) + "\n", max_length=128, n_threads=threads)
+
+    def texts_of(doc_ids):
+        return [" ".join(r) for r in W_obj[pipe_doc_words(np.asarray(doc_ids, np.int64))]]
+
+    batch = 8192
+    doc_texts = [texts_of(np.arange(o, min(o + batch, hi))) for o in range(lo, hi, batch)]  # the "topic"
+    H = spec.hidden
+    E = torch.empty(n_local, H, device=dev)                    # the table's vector column, kept for the re-ranker
+    ix = Index(H, capacity=n_local, device=local_rank)
+    xg = None
+    if world > 1:
+        xg = Exchange(local_rank, rank, world, 256)
+        handles = [None] * world
+        dist.all_gather_object(handles, xg.ipc_handle())
+        xg.connect_ipc(handles)
+    ix.reserve(64, 20)
+
+    # ---- ingest: tokeniser thread -> (H2D, encoder, sink) on the stream --------------------------------
+    def ingest_once(texts):
+        ids, cu = tok.encode_packed(texts)
+        return ids, cu
+
+    ids, cu = ingest_once(doc_texts[0][:256])                  # warm-up of every stage
+    d_ids, d_cu = torch.from_numpy(ids).to(dev), torch.from_numpy(cu).to(dev)
+    warm = torch.empty(256, H, device=dev)
+    enc.embed_dev(d_ids, d_cu, 256, int(cu[-1]), int(np.diff(cu).max()), warm, stream)
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    qd: "queue.Queue" = queue.Queue(maxsize=2)
+
+    def producer():
+        for texts in doc_texts:
+            qd.put(ingest_once(texts))
+        qd.put(None)
+
+    th = threading.Thread(target=producer, daemon=True)
+    th.start()
+    o, tokens = 0, 0
+    while True:
+        item = qd.get()
+        if item is None:
+            break
+        ids, cu = item
+        m = len(cu) - 1
+        d_ids = torch.from_numpy(ids).pin_memory().to(dev, non_blocking=True)
+        d_cu = torch.from_numpy(cu).pin_memory().to(dev, non_blocking=True)
+        enc.embed_dev(d_ids, d_cu, m, int(cu[-1]), int(np.diff(cu).max()), E[o:o + m], stream)
+        ix.upsert_dev(np.arange(lo + o, lo + o + m, dtype=np.int64), E[o:o + m], m, stream)  # returns when the rows are queryable
+        o += m
+        tokens += int(cu[-1])
+    torch.cuda.synchronize()
+    ingest_ms = max_over_ranks((time.perf_counter() - t0) * 1000.0)
+    th.join()
+    del doc_texts
+
+    # ---- queries: 1024 texts (the first 8 words of a document each), 64 per batch ----------------------
+    n_q, qb, k = 1024, 64, 20
+    src_docs = (np.arange(n_q, dtype=np.int64) * 997 + 13) % n_docs
+    q_texts = [" ".join(r[:8]) for r in W_obj[pipe_doc_words(src_docs)]]
+    L = _lib()
+    d_hit_ids = torch.empty(qb, k, dtype=torch.int64, device=dev)
+    d_hit_sc = torch.empty(qb, k, dtype=torch.float32, device=dev)
+    d_qe = torch.empty(qb, H, device=dev)
+    d_order = torch.empty(qb, k + 1, dtype=torch.int32, device=dev)   # per query: k picked positions + the count
+    self_hits, reranked = 0, 0
+
+    def answer(b0):
+        nonlocal self_hits, reranked
+        texts = q_texts[b0:b0 + qb]
+        ids, cu = tok.encode_packed(texts)
+        d_i, d_c = torch.from_numpy(ids).to(dev), torch.from_numpy(cu).to(dev)
+        enc.embed_dev(d_i, d_c, qb, int(cu[-1]), int(np.diff(cu).max()), d_qe, stream)
+        if xg is not None:
+            ix.search_sharded_dev(xg, d_qe, qb, k, d_hit_ids, d_hit_sc, stream)
+        else:
+            ix.search_dev(d_qe, qb, k, d_hit_ids, d_hit_sc, stream)
+        # the hits' vectors: every rank contributes the rows it stores
+        local = (d_hit_ids >= lo) & (d_hit_ids < hi)
+        vec = torch.zeros(qb, k, H, device=dev)
+        vec[local] = E[(d_hit_ids[local] - lo)]
+        if world > 1:
+            dist.all_reduce(vec)
+        hit_ids = d_hit_ids.cpu().numpy()
+        self_hits += int((hit_ids == src_docs[b0:b0 + qb, None]).any(axis=1).sum())
+        # this rank re-ranks its share of the batch (MMR, lambda 0.5, BM25 k1 1.5 b 0.75 - the chatbot example's values)
+        mine = [j for j in range(qb) if (b0 + j) % world == rank]
+        hit_texts = texts_of(hit_ids[mine].reshape(-1))
+        tf_rows, len_rows, n_terms = [], [], 8
+        for jj, j in enumerate(mine):
+            tf, dl = term_statistics(hit_texts[jj * k:(jj + 1) * k], texts[j])
+            tf = np.asarray(tf, np.int32).reshape(k, -1)[:, :n_terms]
+            tf_rows.append(np.pad(tf, ((0, 0), (0, n_terms - tf.shape[1]))))
+            len_rows.append(np.asarray(dl, np.int32))
+        d_tf = torch.from_numpy(np.stack(tf_rows)).to(dev)
+        d_len = torch.from_numpy(np.stack(len_rows)).to(dev)
+        for jj, j in enumerate(mine):
+            _check(L.lsc_rerank_mmr_dev(vec[j].data_ptr(), k, H, d_tf[jj].data_ptr(), d_len[jj].data_ptr(), n_terms, 5,
+                                        0.5, 1.5, 0.75, d_order[j].data_ptr(), d_order[j, k:].data_ptr(), stream))
+        order = d_order.cpu().numpy()   # synchronises: the batch's answers are in host memory
+        reranked += sum(int(order[j, k]) == 5 for j in mine)
+
+    answer(0)                                                  # warm-up
+    self_hits, reranked = 0, 0
+    barrier()
+    t0 = time.perf_counter()
+    for b0 in range(0, n_q, qb):
+        answer(b0)
+    torch.cuda.synchronize()
+    query_ms = max_over_ranks((time.perf_counter() - t0) * 1000.0)
+    if world > 1:
+        t = torch.tensor([reranked], device=dev)
+        dist.all_reduce(t)
+        reranked = int(t.item())
+    out = {"documents": n_docs, "chars_per_document": "~400 (57 pseudo-words, seed 7)", "tokens_per_document": tokens / max(n_local, 1),
+           "ingest": {"value": n_docs / (ingest_ms / 1000.0), "unit": "documents/s", "seconds": ingest_ms / 1000.0,
+                      "stages": "lsc_tokenizer_encode (%d host threads per rank) -> H2D -> lsc_encoder_embed_dev -> lsc_index_upsert_dev" % threads},
+           "query": {"value": n_q / (query_ms / 1000.0), "unit": "queries/s", "queries": n_q, "batch": qb, "k": k,
+                     "stages": "tokenise -> embed -> top-20 over all shards -> gather hit vectors -> host BM25 term counts -> "
+                               "lsc_rerank_mmr_dev (5 of 20) -> D2H",
+                     "source_document_in_top20": self_hits / n_q, "queries_reranked_to_5": reranked},
+           "scope": "native-only e2e: the JVM stages of the reference pipeline (runtime-tester, broker, text-splitter) cannot run "
+                    "in this image"}
+    ix.close()
+    if xg is not None:
+        xg.close()
+    tok.close()
+    return out
+
+# ---------------------------------------------------------------------------------------------
 # CUDA arm
 # ---------------------------------------------------------------------------------------------
 def run_cuda(args):
@@ -775,6 +947,14 @@ def run_cuda(args):
     if not args.no_topk:
         topk = run_topk(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks, pk, peak_tf)
 
+    pipeline = None
+    if not args.no_pipeline:
+        try:
+            pipeline = run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks, enc, spec)
+        except Exception as e:  # noqa: BLE001 - an extra figure must not take the benchmark down
+            import traceback
+            pipeline = {"error": str(e), "trace": traceback.format_exc()[-600:]}
+
     # ---- CPU baseline (rank 0, N=1 only): reference-shaped oracle on a bounded sample ------------
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -794,7 +974,7 @@ def run_cuda(args):
                        "parallelism": f"dp{world} (one replica per GPU, no collective)",
                        "l2": "per-step working set ~1.1 GB of activations >> 126 MB L2; no explicit flush"},
             "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "parity": parity,
-            "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "base_4096x512": base, "text_e2e": text_e2e, "topk": topk,
+            "gpu_launches": int(launches), "clocks": clocks, "varlen": varlen, "base_4096x512": base, "text_e2e": text_e2e, "topk": topk, "pipeline_e2e": pipeline,
         }
         emit(line)
     enc.close()
@@ -813,6 +993,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-base", action="store_true", help="skip the base-shape (config 3) extra figure")
     ap.add_argument("--topk-rows", type=int, default=TOPK_ROWS)
+    ap.add_argument("--no-pipeline", action="store_true", help="skip the config-5 pipeline figure")
+    ap.add_argument("--pipeline-docs", type=int, default=1_000_000)
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus != world and args.impl == "cuda" and world == 1 and args.gpus > 1:
