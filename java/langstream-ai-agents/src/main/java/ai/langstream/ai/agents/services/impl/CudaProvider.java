@@ -3,8 +3,6 @@ package ai.langstream.ai.agents.services.impl;
 import ai.langstream.ai.agents.services.ServiceProviderProvider;
 import ai.langstream.api.runner.code.MetricsReporter;
 import ai.langstream.cuda.LangstreamCuda;
-import ai.djl.huggingface.tokenizers.Encoding;
-import ai.djl.huggingface.tokenizers.HuggingFaceTokenizer;
 import com.datastax.oss.streaming.ai.completions.CompletionsService;
 import com.datastax.oss.streaming.ai.embeddings.EmbeddingsService;
 import com.datastax.oss.streaming.ai.services.ServiceProvider;
@@ -20,8 +18,6 @@ import java.util.ArrayList;
 import java.util.List;
 import java.util.Map;
 import java.util.concurrent.CompletableFuture;
-import java.util.concurrent.ExecutorService;
-import java.util.concurrent.Executors;
 
 /**
  * `cuda` AI service: a ServiceProviderProvider found by ServiceLoader (register this class in
@@ -62,15 +58,37 @@ public class CudaProvider implements ServiceProviderProvider {
         @Override
         public EmbeddingsService getEmbeddingsService(Map<String, Object> stepConfig) throws Exception {
             // same step keys as HuggingFaceProvider.getEmbeddingsService (:82-139)
-            String modelUrl = (String) stepConfig.get("model-url"); // directory: config.json, tokenizer.json, weights.f32
-            if (modelUrl == null || !modelUrl.startsWith("file://")) {
-                throw new IllegalAccessException("modelUrl is not allowed: " + modelUrl);
+            String modelUrl = (String) stepConfig.get("model-url"); // directory: config.json, vocab.txt, weights.f32
+            checkIfUrlIsAllowed(modelUrl);
+            if (!modelUrl.startsWith("file://")) {
+                throw new IllegalArgumentException("the cuda provider loads models from file:// urls only, got " + modelUrl);
             }
             int device = Integer.parseInt(providerConfiguration.getOrDefault("device", "0").toString());
-            CudaEmbeddingsService svc =
-                    new CudaEmbeddingsService(Path.of(modelUrl.substring("file://".length())), device, metrics);
+            int maxBatch = Integer.parseInt(stepConfig.getOrDefault("batch-size", "1024").toString());
+            long flushMicros = (long) (1000 * Double.parseDouble(stepConfig.getOrDefault("flush-interval", "2").toString()));
+            CudaEmbeddingsService svc = new CudaEmbeddingsService(
+                    Path.of(modelUrl.substring("file://".length())), device, maxBatch, Math.max(flushMicros, 100), metrics);
             services.add(svc);
             return svc;
+        }
+
+        /** AbstractHuggingFaceEmbeddingService.checkIfUrlIsAllowed (:174-181) with the same ALLOWED_HF_URLS list (:55-70). */
+        static void checkIfUrlIsAllowed(String modelUrl) throws IllegalAccessException {
+            String prop = System.getenv("ALLOWED_HF_URLS");
+            if (prop == null || prop.isEmpty()) {
+                prop = System.getProperty("ALLOWED_HF_URLS");
+            }
+            if (prop == null || prop.isEmpty()) {
+                prop = "file://,djl://ai.djl.huggingface.pytorch";
+            }
+            if (modelUrl != null) {
+                for (String prefix : prop.split(",")) {
+                    if (modelUrl.startsWith(prefix)) {
+                        return;
+                    }
+                }
+            }
+            throw new IllegalAccessException("modelUrl is not allowed: " + modelUrl);
         }
 
         @Override
@@ -79,20 +97,62 @@ public class CudaProvider implements ServiceProviderProvider {
         }
     }
 
-    /** EmbeddingsService (EmbeddingsService.java:24-37) over lsc_encoder_embed. Thread-safe. */
+    /**
+     * EmbeddingsService (EmbeddingsService.java:24-37) over lsc_tokenizer_encode + lsc_encoder_submit / lsc_encoder_wait.
+     *
+     * <p>The runtime hands texts over one record at a time (CompositeAgentProcessor.java:225-227; with
+     * flush-interval 0 OrderedAsyncBatchExecutor flushes every add, :113-118), so requests from all callers meet
+     * in a micro-batcher: a batch goes to the GPU when maxBatch texts are waiting or the oldest request is
+     * flushMicros old. One batcher thread tokenises batch i+1 (native, multi-threaded) while the GPU works on
+     * batch i; two page-locked staging slots are reused for the whole life of the service. Never throws from
+     * computeEmbeddings: failures complete the future exceptionally
+     * (AbstractHuggingFaceEmbeddingService.computeEmbeddings :213-223).
+     */
     static class CudaEmbeddingsService implements EmbeddingsService {
+        private record Request(List<String> texts, CompletableFuture<List<List<Double>>> future, long enqueuedNanos) {}
+
+        /** One staging slot: direct buffers handed to the native module, valid until its ticket has been waited for. */
+        private final class Slot {
+            ByteBuffer utf8 = direct(1 << 20);
+            IntBuffer textNbytes, tokens, cu;
+            FloatBuffer out;
+            List<Request> requests;
+            long ticket = -1;
+            int nTexts;
+
+            void ensure(int nTexts, int utf8Bytes) {
+                if (utf8.capacity() < utf8Bytes) utf8 = direct(utf8Bytes + utf8Bytes / 4);
+                if (textNbytes == null || textNbytes.capacity() < nTexts) {
+                    int cap = Math.max(nTexts, maxBatch);
+                    textNbytes = direct(cap * 4).asIntBuffer();
+                    cu = direct((cap + 1) * 4).asIntBuffer();
+                    tokens = direct(cap * maxPosition * 4).asIntBuffer();
+                    out = direct(cap * dim * 4).asFloatBuffer();
+                }
+            }
+        }
+
         private final long encoder;
+        private final long tokenizer;
         private final int dim;
         private final int maxPosition;
-        private final HuggingFaceTokenizer tokenizer;
-        private final ExecutorService gpuThread = Executors.newSingleThreadExecutor();
+        private final int maxBatch;
+        private final long flushNanos;
+        private final java.util.ArrayDeque<Request> pending = new java.util.ArrayDeque<>();
+        private final Slot[] slots = {null, null};
+        private final Thread batcher;
+        private volatile boolean closed;
         private final MetricsReporter.Counter embeddingsComputed;
 
-        CudaEmbeddingsService(Path modelDir, int device, MetricsReporter metrics) throws Exception {
+        CudaEmbeddingsService(Path modelDir, int device, int maxBatch, long flushMicros, MetricsReporter metrics) throws Exception {
             Map<String, Object> cfg = EmbeddingsService.createObjectMapper()
                     .readValue(modelDir.resolve("config.json").toFile(), Map.class);
             this.maxPosition = ((Number) cfg.get("max_position_embeddings")).intValue();
-            this.tokenizer = HuggingFaceTokenizer.newInstance(modelDir.resolve("tokenizer.json"));
+            this.maxBatch = maxBatch;
+            this.flushNanos = flushMicros * 1000;
+            boolean lower = Boolean.parseBoolean(String.valueOf(cfg.getOrDefault("do_lower_case", "true")));
+            this.tokenizer = LangstreamCuda.tokenizerCreate(
+                    java.nio.file.Files.readAllBytes(modelDir.resolve("vocab.txt")), lower, maxPosition, 0);
             try (FileChannel ch = FileChannel.open(modelDir.resolve("weights.f32"), StandardOpenOption.READ)) {
                 ByteBuffer weights = ByteBuffer.allocateDirect((int) ch.size()).order(ByteOrder.nativeOrder());
                 while (weights.hasRemaining() && ch.read(weights) >= 0) {}
@@ -111,58 +171,129 @@ public class CudaProvider implements ServiceProviderProvider {
             this.dim = LangstreamCuda.encoderDim(encoder);
             this.embeddingsComputed = metrics == null ? null
                     : metrics.counter("embeddings_computed", "embeddings computed on the GPU");
+            slots[0] = new Slot();
+            slots[1] = new Slot();
+            this.batcher = new Thread(this::run, "lsc-embeddings-batcher");
+            this.batcher.setDaemon(true);
+            this.batcher.start();
         }
 
         @Override
         public CompletableFuture<List<List<Double>>> computeEmbeddings(List<String> texts) {
-            // Never throws: failures complete the future exceptionally, as
-            // AbstractHuggingFaceEmbeddingService.computeEmbeddings does (:213-223).
-            return CompletableFuture.supplyAsync(() -> {
-                try {
-                    return embed(texts);
-                } catch (Exception e) {
-                    throw new RuntimeException("failed to compute embeddings", e);
+            CompletableFuture<List<List<Double>>> f = new CompletableFuture<>();
+            if (texts.isEmpty()) {
+                f.complete(List.of());
+                return f;
+            }
+            synchronized (pending) {
+                if (closed) {
+                    f.completeExceptionally(new RuntimeException("failed to compute embeddings", new IllegalStateException("closed")));
+                    return f;
                 }
-            }, gpuThread);
+                pending.add(new Request(List.copyOf(texts), f, System.nanoTime()));
+                pending.notifyAll();
+            }
+            return f;
         }
 
-        private List<List<Double>> embed(List<String> texts) {
-            int n = texts.size();
-            long[][] ids = new long[n][];
-            int total = 0;
-            for (int i = 0; i < n; i++) {
-                Encoding enc = tokenizer.encode(texts.get(i));   // host tokenisation (adds [CLS]/[SEP], truncates)
-                ids[i] = enc.getIds();
-                total += ids[i].length;
-            }
-            IntBuffer tokens = direct(total * 4).asIntBuffer();
-            IntBuffer cu = direct((n + 1) * 4).asIntBuffer();
-            int offset = 0;
-            cu.put(0, 0);
-            for (int i = 0; i < n; i++) {
-                for (long t : ids[i]) {
-                    tokens.put(offset++, (int) t);
+        /** Batcher thread: collect -> tokenise -> submit; then complete the batch submitted one turn earlier. */
+        private void run() {
+            int turn = 0;
+            Slot inFlight = null;
+            while (true) {
+                List<Request> batch = new ArrayList<>();
+                synchronized (pending) {
+                    try {
+                        while (pending.isEmpty() && !closed && inFlight == null) pending.wait();
+                        if (!pending.isEmpty()) {
+                            // the window: full batch, or the oldest request is old enough (do not hold back a batch
+                            // while an earlier one is still to be completed)
+                            while (!closed && inFlight == null) {
+                                int waiting = pending.stream().mapToInt(r -> r.texts().size()).sum();
+                                long age = System.nanoTime() - pending.peek().enqueuedNanos();
+                                if (waiting >= maxBatch || age >= flushNanos) break;
+                                pending.wait(Math.max((flushNanos - age) / 1_000_000, 1));
+                            }
+                            int n = 0;
+                            while (!pending.isEmpty() && (batch.isEmpty() || n + pending.peek().texts().size() <= maxBatch)) {
+                                Request r = pending.poll();
+                                batch.add(r);
+                                n += r.texts().size();
+                            }
+                        }
+                    } catch (InterruptedException e) {
+                        Thread.currentThread().interrupt();
+                        return;
+                    }
                 }
-                cu.put(i + 1, offset);
+                Slot next = null;
+                if (!batch.isEmpty()) {
+                    next = slots[turn++ & 1];
+                    try {
+                        submit(next, batch);
+                    } catch (Throwable t) {   // the whole batch fails together (ComputeAIEmbeddingsStep.java:215-220)
+                        for (Request r : batch) r.future().completeExceptionally(new RuntimeException("failed to compute embeddings", t));
+                        next = null;
+                    }
+                }
+                if (inFlight != null) complete(inFlight);   // batch i-1: its download overlapped the work above
+                inFlight = next;
+                if (closed && inFlight == null) {
+                    synchronized (pending) {
+                        if (pending.isEmpty()) return;
+                    }
+                }
             }
-            FloatBuffer out = direct(n * dim * 4).asFloatBuffer();
-            LangstreamCuda.encoderEmbed(encoder, tokens, cu, n, out);   // packed variable-length batch
-            if (embeddingsComputed != null) {
-                embeddingsComputed.count(n);
+        }
+
+        private void submit(Slot s, List<Request> batch) {
+            int n = 0, bytes = 0;
+            List<byte[]> raw = new ArrayList<>();
+            for (Request r : batch) {
+                for (String t : r.texts()) {
+                    byte[] b = t.getBytes(java.nio.charset.StandardCharsets.UTF_8);
+                    raw.add(b);
+                    bytes += b.length;
+                    n++;
+                }
             }
-            // float -> double widening (HuggingFaceEmbeddingService.convertOutput :52-63) without boxing
-            // n*dim Doubles up front: one float[] per text, exposed as a List<Double> view.
-            List<List<Double>> result = new ArrayList<>(n);
+            s.ensure(n, bytes);
+            s.utf8.clear();
             for (int i = 0; i < n; i++) {
-                final float[] row = new float[dim];
-                out.position(i * dim);
-                out.get(row);
-                result.add(new AbstractList<>() {
-                    @Override public Double get(int j) { return (double) row[j]; }
-                    @Override public int size() { return row.length; }
-                });
+                s.utf8.put(raw.get(i));
+                s.textNbytes.put(i, raw.get(i).length);
             }
-            return result;
+            // host tokenisation stays on the host, but natively and on all cores (lsc_tokenizer_encode); an over-long
+            // text is truncated to max_position by the tokenizer, like DJL's truncation=true default
+            LangstreamCuda.tokenizerEncode(tokenizer, s.utf8, s.textNbytes, n, s.tokens, s.cu);
+            s.requests = batch;
+            s.nTexts = n;
+            s.ticket = LangstreamCuda.encoderSubmit(encoder, s.tokens, s.cu, n, s.out);
+        }
+
+        private void complete(Slot s) {
+            try {
+                LangstreamCuda.encoderWait(encoder, s.ticket);
+                if (embeddingsComputed != null) embeddingsComputed.count(s.nTexts);
+                int row = 0;
+                for (Request r : s.requests) {
+                    // float -> double widening (HuggingFaceEmbeddingService.convertOutput :52-63) without boxing dim
+                    // Doubles per text: one float[] per text behind a List<Double> view; nothing aliases the slot
+                    List<List<Double>> result = new ArrayList<>(r.texts().size());
+                    for (int i = 0; i < r.texts().size(); i++, row++) {
+                        final float[] v = new float[dim];
+                        s.out.position(row * dim);
+                        s.out.get(v);
+                        result.add(new AbstractList<>() {
+                            @Override public Double get(int j) { return (double) v[j]; }
+                            @Override public int size() { return v.length; }
+                        });
+                    }
+                    r.future().complete(result);
+                }
+            } catch (Throwable t) {
+                for (Request r : s.requests) r.future().completeExceptionally(new RuntimeException("failed to compute embeddings", t));
+            }
         }
 
         private static ByteBuffer direct(int bytes) {
@@ -171,7 +302,16 @@ public class CudaProvider implements ServiceProviderProvider {
 
         @Override
         public void close() {
-            gpuThread.shutdown();
+            synchronized (pending) {
+                closed = true;
+                pending.notifyAll();
+            }
+            try {
+                batcher.join(10_000);
+            } catch (InterruptedException e) {
+                Thread.currentThread().interrupt();
+            }
+            LangstreamCuda.tokenizerDestroy(tokenizer);
             LangstreamCuda.encoderDestroy(encoder);
         }
     }

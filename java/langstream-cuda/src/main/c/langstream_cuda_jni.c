@@ -2,6 +2,7 @@
  * carrying lsc_last_error(). Needs <jni.h> from a JDK (absent in the build image: not compiled here). */
 #include <jni.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "langstream_cuda.h"
 
@@ -88,4 +89,77 @@ JNIEXPORT jint JNICALL Java_ai_langstream_cuda_LangstreamCuda_rerankMmr(
                             (int32_t*)(*env)->GetDirectBufferAddress(env, out), &count);
     if (rc != LSC_OK) throw_lsc(env, rc);
     return count;
+}
+
+/* ---- asynchronous encoder calls, tokenizer, sharded index (same conventions as above) ---- */
+JNIEXPORT jlong JNICALL Java_ai_langstream_cuda_LangstreamCuda_encoderSubmit(
+        JNIEnv* env, jclass c, jlong enc, jobject ids, jobject cu, jint n, jobject out) {
+    int64_t ticket = -1;
+    CHECK(lsc_encoder_submit((lsc_encoder*)(intptr_t)enc, (const int32_t*)ADDR(ids), (const int32_t*)ADDR(cu), n,
+                             (float*)ADDR(out), &ticket));
+    return (jlong)ticket;
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_encoderWait(JNIEnv* env, jclass c, jlong enc, jlong ticket) {
+    CHECK(lsc_encoder_wait((lsc_encoder*)(intptr_t)enc, (int64_t)ticket));
+}
+JNIEXPORT jlong JNICALL Java_ai_langstream_cuda_LangstreamCuda_tokenizerCreate(
+        JNIEnv* env, jclass c, jbyteArray vocab, jboolean lower, jint maxLength, jint nThreads) {
+    jsize n = (*env)->GetArrayLength(env, vocab);
+    jbyte* p = (*env)->GetByteArrayElements(env, vocab, NULL);
+    lsc_tokenizer* tok = NULL;
+    int rc = lsc_tokenizer_create((const char*)p, (size_t)n, lower ? 1 : 0, maxLength, nThreads, &tok);
+    (*env)->ReleaseByteArrayElements(env, vocab, p, JNI_ABORT);
+    CHECK(rc);
+    return (jlong)(intptr_t)tok;
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_tokenizerEncode(
+        JNIEnv* env, jclass c, jlong tok, jobject utf8, jobject nbytes, jint nTexts, jobject ids, jobject cu) {
+    /* the texts lie back to back: build the pointer table the C ABI takes */
+    const char* base = (const char*)ADDR(utf8);
+    const int32_t* len = (const int32_t*)ADDR(nbytes);
+    const char** ptrs = (const char**)malloc(sizeof(char*) * (size_t)(nTexts > 0 ? nTexts : 1));
+    size_t off = 0;
+    for (jint i = 0; i < nTexts; ++i) {
+        ptrs[i] = base + off;
+        off += (size_t)len[i];
+    }
+    int rc = lsc_tokenizer_encode((lsc_tokenizer*)(intptr_t)tok, ptrs, len, nTexts, (int32_t*)ADDR(ids),
+                                  (int64_t)((*env)->GetDirectBufferCapacity(env, ids)), (int32_t*)ADDR(cu));
+    free(ptrs);
+    CHECK(rc);
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_tokenizerDestroy(JNIEnv* env, jclass c, jlong tok) {
+    lsc_tokenizer_destroy((lsc_tokenizer*)(intptr_t)tok);
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_indexReserve(JNIEnv* env, jclass c, jlong ix, jint b, jint k) {
+    CHECK(lsc_index_reserve((lsc_index*)(intptr_t)ix, b, k));
+}
+JNIEXPORT jlong JNICALL Java_ai_langstream_cuda_LangstreamCuda_shardedIndexCreate(
+        JNIEnv* env, jclass c, jint dim, jlong capacity, jintArray devices) {
+    jsize n = (*env)->GetArrayLength(env, devices);
+    jint* d = (*env)->GetIntArrayElements(env, devices, NULL);
+    lsc_sharded_index* s = NULL;
+    int rc = lsc_sharded_index_create(dim, capacity, (const int*)d, n, &s);
+    (*env)->ReleaseIntArrayElements(env, devices, d, JNI_ABORT);
+    CHECK(rc);
+    return (jlong)(intptr_t)s;
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_shardedIndexUpsert(
+        JNIEnv* env, jclass c, jlong s, jobject ids, jobject vecs, jint n) {
+    CHECK(lsc_sharded_index_upsert((lsc_sharded_index*)(intptr_t)s, (const int64_t*)ADDR(ids), (const float*)ADDR(vecs), n));
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_shardedIndexDelete(
+        JNIEnv* env, jclass c, jlong s, jobject ids, jint n) {
+    CHECK(lsc_sharded_index_delete((lsc_sharded_index*)(intptr_t)s, (const int64_t*)ADDR(ids), n));
+}
+JNIEXPORT jlong JNICALL Java_ai_langstream_cuda_LangstreamCuda_shardedIndexSize(JNIEnv* env, jclass c, jlong s) {
+    return lsc_sharded_index_size((const lsc_sharded_index*)(intptr_t)s);
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_shardedIndexSearch(
+        JNIEnv* env, jclass c, jlong s, jobject q, jint b, jint k, jobject outIds, jobject outScores) {
+    CHECK(lsc_sharded_index_search((lsc_sharded_index*)(intptr_t)s, (const float*)ADDR(q), b, k, (int64_t*)ADDR(outIds),
+                                   (float*)ADDR(outScores)));
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_shardedIndexDestroy(JNIEnv* env, jclass c, jlong s) {
+    lsc_sharded_index_destroy((lsc_sharded_index*)(intptr_t)s);
 }

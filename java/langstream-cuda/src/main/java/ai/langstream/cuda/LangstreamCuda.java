@@ -30,7 +30,29 @@ public final class LangstreamCuda {
     public static native void encoderEmbed(
             long encoder, IntBuffer tokenIds, IntBuffer cuSeqlens, int nSeq, FloatBuffer out);
 
+    /**
+     * lsc_encoder_submit / lsc_encoder_wait: the asynchronous form (EmbeddingsService returns a CompletableFuture).
+     * The three buffers must stay untouched until encoderWait(ticket) has returned; up to two tickets are in
+     * flight per handle (upload of batch i+1 and download of batch i-1 overlap the kernels of batch i).
+     */
+    public static native long encoderSubmit(
+            long encoder, IntBuffer tokenIds, IntBuffer cuSeqlens, int nSeq, FloatBuffer out);
+
+    public static native void encoderWait(long encoder, long ticket);
+
     public static native int encoderDim(long encoder);
+
+    // ---- host tokenizer (replaces DJL's HuggingFaceTokenizer inside predictor.predict) ----
+    public static native long tokenizerCreate(byte[] vocabTxt, boolean doLowerCase, int maxLength, int nThreads);
+
+    /**
+     * lsc_tokenizer_encode: texts as UTF-8 bytes back to back in `utf8` with their lengths in `textNbytes`;
+     * writes packed ids and cuSeqlens (nTexts + 1 entries) - the layout encoderEmbed / encoderSubmit take.
+     */
+    public static native void tokenizerEncode(
+            long tokenizer, ByteBuffer utf8, IntBuffer textNbytes, int nTexts, IntBuffer tokenIds, IntBuffer cuSeqlens);
+
+    public static native void tokenizerDestroy(long tokenizer);
 
     public static native void encoderDestroy(long encoder);
 
@@ -45,6 +67,23 @@ public final class LangstreamCuda {
 
     public static native void indexSearch(
             long index, FloatBuffer queries, int b, int k, LongBuffer outIds, FloatBuffer outScores);
+
+    /** lsc_index_reserve: allocate the scratch of later searches (up to b queries, k results) at start-up. */
+    public static native void indexReserve(long index, int b, int k);
+
+    // ---- the table spread over several GPUs behind one handle (lsc_sharded_index_*) ----
+    public static native long shardedIndexCreate(int dim, long capacityPerShard, int[] devices);
+
+    public static native void shardedIndexUpsert(long sharded, LongBuffer ids, FloatBuffer vectors, int n);
+
+    public static native void shardedIndexDelete(long sharded, LongBuffer ids, int n);
+
+    public static native long shardedIndexSize(long sharded);
+
+    public static native void shardedIndexSearch(
+            long sharded, FloatBuffer queries, int b, int k, LongBuffer outIds, FloatBuffer outScores);
+
+    public static native void shardedIndexDestroy(long sharded);
 
     public static native void indexSave(long index, String path);
 

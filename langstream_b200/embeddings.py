@@ -168,6 +168,27 @@ class CudaEmbeddingsService(EmbeddingsService):
                     fut.set_exception(err)
 
 
+URL_PREFIXES_SYSTEM_PROP = "ALLOWED_HF_URLS"
+DJL_BASE_URL = "djl://ai.djl.huggingface.pytorch"
+
+
+def allowed_url_prefixes() -> List[str]:
+    """AbstractHuggingFaceEmbeddingService.getHuggingFaceAllowedUrlPrefixes (:55-70): the comma-separated
+    ALLOWED_HF_URLS from the environment, default "file://,djl://ai.djl.huggingface.pytorch"."""
+    import os
+
+    prop = os.environ.get(URL_PREFIXES_SYSTEM_PROP) or ""
+    if not prop:
+        prop = "file://," + DJL_BASE_URL
+    return prop.split(",")
+
+
+def check_if_url_is_allowed(model_url: str) -> None:
+    """checkIfUrlIsAllowed (:174-181): IllegalAccessException("modelUrl is not allowed: ...") in the reference."""
+    if not any(model_url.startswith(p) for p in allowed_url_prefixes()):
+        raise PermissionError(f"modelUrl is not allowed: {model_url}")
+
+
 KNOWN_ARCHITECTURES: Dict[str, EncoderSpec] = {
     "all-MiniLM-L6-v2": MINILM_L6,
     "sentence-transformers/all-MiniLM-L6-v2": MINILM_L6,
@@ -199,8 +220,9 @@ class CudaServiceProvider:
         options = cfg.get("options") or {}
         url = cfg.get("model-url")
         if url:
-            if not str(url).startswith("file://"):
-                raise PermissionError(f"modelUrl is not allowed: {url}")  # checkIfUrlIsAllowed, :174-181
+            check_if_url_is_allowed(str(url))
+            if not str(url).startswith("file://"):  # allowed by the operator, but this provider only reads local files
+                raise ValueError(f"the cuda provider loads weights from file:// urls only, got {url}")
             blob = np.load(str(url)[len("file://"):]).astype(np.float32)
         else:
             blob = random_init(spec, seed=int(options.get("random-init-seed", 0)))

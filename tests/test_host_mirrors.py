@@ -32,8 +32,28 @@ def test_provider_lookup_and_config_errors():
         sp.get_completions_service({})          # like the no-op provider: no completions here
     with pytest.raises(ValueError):
         sp.get_embeddings_service({"model": "no-such-model"})
-    with pytest.raises(PermissionError):       # ALLOWED_HF_URLS semantics: only file:// is allowed
+    with pytest.raises(PermissionError):       # ALLOWED_HF_URLS default: file:// and the DJL zoo prefix
         sp.get_embeddings_service({"model": "all-MiniLM-L6-v2", "model-url": "http://example.com/w.npy"})
+
+
+def test_allowed_hf_urls_prefix_list(monkeypatch):
+    """AbstractHuggingFaceEmbeddingService.java:55-70,174-181: comma-separated prefixes from ALLOWED_HF_URLS."""
+    from langstream_b200 import embeddings as E
+
+    monkeypatch.delenv("ALLOWED_HF_URLS", raising=False)
+    assert E.allowed_url_prefixes() == ["file://", "djl://ai.djl.huggingface.pytorch"]
+    E.check_if_url_is_allowed("file:///models/w.npy")
+    E.check_if_url_is_allowed("djl://ai.djl.huggingface.pytorch/sentence-transformers/all-MiniLM-L6-v2")
+    with pytest.raises(PermissionError, match="modelUrl is not allowed"):
+        E.check_if_url_is_allowed("s3://bucket/w.npy")
+    monkeypatch.setenv("ALLOWED_HF_URLS", "file://,s3://,https://models.example.com/")
+    E.check_if_url_is_allowed("s3://bucket/w.npy")
+    E.check_if_url_is_allowed("https://models.example.com/minilm")
+    with pytest.raises(PermissionError):
+        E.check_if_url_is_allowed("https://elsewhere.example.com/minilm")
+    sp = E.CudaServiceProviderProvider().create_implementation({"cuda": {}})
+    with pytest.raises(ValueError, match="file:// urls only"):   # allowed, but this provider reads local files
+        sp.get_embeddings_service({"model": "all-MiniLM-L6-v2", "model-url": "s3://bucket/w.npy"})
 
 
 def test_embeddings_service_alignment_batching_and_errors():
