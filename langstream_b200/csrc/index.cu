@@ -208,7 +208,9 @@ int search_dev(lsc_index* ix, lsc_exchange* xg, const float* d_queries, int B, i
         // One pass over the corpus: the merge (and the peer exchange) rides in the scan launch.  Several passes
         // (B > 256): each launch only scans, and ONE merge launch (+ one exchange launch) serves all queries -
         // cheaper than a tail per pass (measured: ~20 us per pass).
-        const bool fused = !unfused && B <= step;
+        // (CTA pairs keep the separate merge launch as well: a cooperative launch of a clustered grid is refused
+        // under the profiler's kernel replay, and 129-256 queries gain little from the fusion.)
+        const bool fused = !unfused && B <= step && !pair;
         int pass = 0;
         for (int q0 = 0; q0 < B; q0 += step, ++pass) {
             const int nq = std::min(step, B - q0);
