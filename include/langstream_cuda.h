@@ -18,7 +18,9 @@
  *     same thread);
  *   - the caller owns every input and output buffer; nothing returned aliases native memory;
  *   - one handle drives one GPU; use one handle (and one process or thread) per GPU;
- *   - calls on the same handle are serialised internally (thread-safe, not concurrent);
+ *   - calls on the same handle are serialised internally (thread-safe, not concurrent), on the GPU as well: the
+ *     *_dev / submit calls return without synchronising, but a pass enqueued on one stream waits (through an event)
+ *     for the handle's previous pass on any other stream, because all passes share the handle's scratch;
  *   - there is no CPU fallback: without a usable sm_100 device every create call fails.
  */
 #ifndef LANGSTREAM_CUDA_H
