@@ -11,6 +11,7 @@ of vector.py (key, value, headers) with dict or JSON-text values.
 """
 from __future__ import annotations
 
+import copy
 import json
 import random
 import re
@@ -285,6 +286,50 @@ class ComputeAIEmbeddingsStep:
         self.batch_executor.stop()
         if self.embeddings_service is not None:
             self.embeddings_service.close()
+
+
+class GenAIToolKitAgent:
+    """The agent around the step (GenAIToolKitAgent.java:70-114): `process(records, sink)` starts every record's step
+    asynchronously and emits exactly ONE `sink(source, results, error)` per input record when that record's future
+    completes - possibly from another thread (RecordSink.java:21-27 says emit is thread-safe), in completion order,
+    never an exception out of `process` except for an empty list (IllegalStateException in the reference).  The
+    product keeps the reference's Java class; this mirror exists so that the contract the CUDA embeddings service
+    has to live under (asynchronous completion, whole-batch failure) is exercised by the tests here."""
+
+    def __init__(self, step: "ComputeAIEmbeddingsStep"):
+        self.step = step
+        self.processed_in = 0
+        self.processed_out = 0
+        self._lock = threading.Lock()
+
+    def start(self) -> None:
+        self.step.start()
+
+    def process(self, records: List[Record], sink: Callable[[Record, Optional[List[Record]], Optional[Exception]], None]) -> None:
+        if not records:
+            raise RuntimeError("Records cannot be null or empty")
+        for record in records:
+            with self._lock:
+                self.processed_in += 1
+            # recordToMutableRecord works on a copy: the source record is emitted unchanged beside the result
+            out = Record(key=copy.deepcopy(record.key), value=copy.deepcopy(record.value), headers=dict(record.headers))
+
+            def done(fut: Future, record=record, out=out):
+                err = fut.exception()
+                if err is not None:
+                    sink(record, None, err)
+                    return
+                with self._lock:
+                    self.processed_out += 1
+                sink(record, [out], None)
+
+            try:
+                self.step.process_async(out).add_done_callback(done)
+            except Exception as e:  # noqa: BLE001 - reported through the sink, like a failed future
+                sink(record, None, e)
+
+    def close(self) -> None:
+        self.step.close()
 
 
 class QueryStep:

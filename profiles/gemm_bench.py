@@ -11,7 +11,7 @@ from langstream_b200 import _native
 dev = torch.device("cuda:0")
 T = 131072
 shapes = [("qkv", T, 1152, 384, 0), ("out", T, 384, 384, 2), ("ffn1", T, 1536, 384, 1), ("ffn2", T, 384, 1536, 2),
-          ("qkv_disc", T, 1152, 384, 3), ("qkv_ldonly", T, 1152, 384, 4), ("ffn2_ldonly", T, 384, 1536, 4), ("ffn1_disc", T, 1536, 384, 3), ("ffn2_disc", T, 384, 1536, 3),
+          ("out_disc", T, 384, 384, 3), ("out_ldonly", T, 384, 384, 4), ("out_bias", T, 384, 384, 0), ("qkv_disc", T, 1152, 384, 3), ("qkv_ldonly", T, 1152, 384, 4), ("ffn2_ldonly", T, 384, 1536, 4), ("ffn1_disc", T, 1536, 384, 3), ("ffn2_disc", T, 384, 1536, 3),
           ("base_ffn1", 65536, 3072, 768, 1), ("base_ffn2", 65536, 768, 3072, 2), ("base_disc", 65536, 3072, 768, 3)]
 st = torch.cuda.current_stream().cuda_stream
 print("LSC_GEMM_BN =", os.environ.get("LSC_GEMM_BN"), "DBG =", os.environ.get("LSC_GEMM_DBG"))

@@ -150,3 +150,43 @@ def test_query_step_modes():
     assert rec.value["res"] == {"count": 1, "generatedKeys": {"id": 7}}
     with pytest.raises(RuntimeError, match="Unknown mode"):
         QueryStep(ds, "x", [], "value.o", mode="nope").process(rec)
+
+
+def test_agent_emits_exactly_once_per_record_asynchronously():
+    """GenAIToolKitAgent.process (GenAIToolKitAgent.java:70-91): one emit per input record, from whatever thread the
+    service completes on, errors as the emit's error; an empty list is an IllegalStateException."""
+    from langstream_b200.agents import GenAIToolKitAgent
+
+    svc = MockEmbeddingsService(delay=0.02)
+    agent = GenAIToolKitAgent(ComputeAIEmbeddingsStep.from_config(
+        {"text": "{{ value.t }}", "embeddings-field": "value.e", "batch-size": 4, "flush-interval": 10, "concurrency": 2}, svc))
+    agent.start()
+    recs = [Record(key=f"k{i}", value={"t": "y" * (i + 1)}) for i in range(9)]
+    emitted, threads, done = [], set(), threading.Event()
+
+    def sink(source, results, error):
+        emitted.append((source, results, error))
+        threads.add(threading.get_ident())
+        if len(emitted) == len(recs):
+            done.set()
+
+    agent.process(recs, sink)                     # returns at once: nothing has been computed yet
+    assert len(emitted) < len(recs)
+    assert done.wait(5)
+    assert sorted(id(e[0]) for e in emitted) == sorted(id(r) for r in recs)       # exactly one emit per record
+    assert threading.get_ident() not in threads                                   # completed on other threads
+    for source, results, error in emitted:
+        assert error is None and len(results) == 1
+        assert results[0].value["e"] == [float(len(source.value["t"]))]
+        assert "e" not in source.value                                             # the source record is not mutated
+    assert agent.processed_in == 9 and agent.processed_out == 9
+    with pytest.raises(RuntimeError, match="cannot be null or empty"):
+        agent.process([], sink)
+    agent.close()
+    assert svc.closed
+    failing = GenAIToolKitAgent(ComputeAIEmbeddingsStep("{{ value.t }}", "value.e", None, 2, 0, 1, MockEmbeddingsService(fail=True)))
+    got = []
+    ev = threading.Event()
+    failing.process([Record(value={"t": "a"}), Record(value={"t": "b"})], lambda s, r, e: (got.append((r, e)), len(got) == 2 and ev.set()))
+    assert ev.wait(5)
+    assert all(r is None and isinstance(e, RuntimeError) for r, e in got) and failing.processed_out == 0
