@@ -112,12 +112,14 @@ def lib() -> C.CDLL:
     """Load (once) and return the native library; raises if it has not been built."""
     global _lib
     if _lib is None:
-        if not LIB_PATH.exists():
+        import os
+        path = Path(os.environ.get("LSC_NATIVE_LIB") or LIB_PATH)  # LSC_NATIVE_LIB: A/B builds of the same library (profiles/)
+        if not path.exists():
             raise RuntimeError(
-                f"{LIB_PATH} is missing: build it with `python -m langstream_b200.build` "
+                f"{path} is missing: build it with `python -m langstream_b200.build` "
                 "(there is no CPU fallback for this path)"
             )
-        handle = C.CDLL(str(LIB_PATH))
+        handle = C.CDLL(str(path))
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)  # AttributeError if the symbol is not exported
             fn.restype = res
