@@ -116,6 +116,11 @@ struct LnArgs {
     const float* beta = nullptr;
     float inv_h = 0.f;                 // 1 / row length of the normalised tensor
     float eps = 0.f;
+    // Residual epilogues: a store32-type tensor map of the residual tensor (same geometry as the output).  When set,
+    // the epilogue warps fetch their residual blocks with TMA into their staging blocks while the accumulator is still
+    // being computed, instead of per-thread global loads on the epilogue's critical path.
+    int has_res_map = 0;
+    CUtensorMap res_map;
 };
 
 // Output columns >= f16_from_col are written as fp16 instead of bf16 (pass N for "none"): the QKV GEMM

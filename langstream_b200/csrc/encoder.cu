@@ -325,6 +325,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                 LnArgs ln_o;  // tmp = ctx.Wo^T + b + LN_in(x); statistics of tmp -> stats_1
                 ln_o.stats_in = e->stats_x; ln_o.p_in = PX; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
                 ln_o.inv_h = inv_h; ln_o.eps = c.ln_eps;
+                ln_o.has_res_map = 1; ln_o.res_map = tc_x;  // the residual x through TMA
                 LSC_LAUNCH(1, gemm(e, tm_ctx, e->ctx, w.tm_o, w.w_o, w.b_o, e->x, tc_tmp, e->tmp, T, H, H, EPI_RES_LN, H, ln_o, st));
                 if (ffn_fused_supported(H, F)) {
                     // x = GELU(LN1(tmp).W1^T + b1).W2^T + b2 + LN1(tmp) in one kernel; statistics of x -> stats_x
@@ -339,12 +340,13 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                 LnArgs ln_2;  // x = ffn.W2^T + b + LN1(tmp); statistics of x -> stats_x
                 ln_2.stats_in = e->stats_1; ln_2.p_in = P; ln_2.stats_out = e->stats_x; ln_2.gamma = w.ln1_g; ln_2.beta = w.ln1_b;
                 ln_2.inv_h = inv_h; ln_2.eps = c.ln_eps;
+                ln_2.has_res_map = 1; ln_2.res_map = tc_tmp;
                 LSC_LAUNCH(1, gemm(e, tm_ffn, e->ffn, w.tm_2, w.w_2, w.b_2, e->tmp, tc_x, e->x, T, H, F, EPI_RES_LN, H, ln_2, st));
             }
         } else {
             // ---- validation path: CUDA-core GEMMs and explicit LayerNorm kernels (unfused) ----
             CUtensorMap none;
-            const LnArgs no_ln;
+            const LnArgs no_ln{};
             LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word, e->d_pos,
                                           e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, nullptr, 0, st));
             for (int l = 0; l < c.layers; ++l) {

@@ -126,7 +126,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             mbar_init(bar(FF_MAX_STAGES + s), 1);    // empty
         }
         mbar_init(bar(FB_A_FULL), PAIR);
-        mbar_init(bar(FB_A_EMPTY), 1);
+        mbar_init(bar(FB_A_EMPTY), 1 + FF_EPI_WARPS);  // the MMAs' last read + this CTA's epilogue warps (residual)
         mbar_init(bar(FB_HACC_FULL), 1);
         mbar_init(bar(FB_HACC_EMPTY), FF_EPI_WARPS * PAIR);
         mbar_init(bar(FB_SH_FULL0), FF_EPI_WARPS + (PAIR - 1));  // leader's warps + the peer's relay
@@ -373,22 +373,38 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
             }
             // ---- final: OUT + b2 + LN1(tmp) -> x, with row statistics ----
             const int col_base = cq * (H / 4);
-            const __nv_bfloat16* rrow = a.residual + static_cast<size_t>(row_ok ? grow : 0) * H + col_base;
             uint64_t osum2 = pk2(0.f, 0.f), osq2 = pk2(0.f, 0.f);
-            uint32_t res[16], res_next[16];
-            ldg256(rrow, res_next);  // residual of block 0, in flight while the last chunks finish
-            ldg256(rrow + 16, res_next + 8);
+            // The residual IS this tile's A operand, still in shared memory (K-major SWIZZLE_128B slices): this
+            // warp's 32 rows x H/4 columns are copied to registers now - before the accumulator is waited for - and
+            // the A tile is released for the next tile's prefetch right after.  (As global loads, one block ahead,
+            // the residual cost 45 us of the kernel's 300: three dependent L2 round trips per warp and tile with
+            // the tensor pipe idle.)
+            constexpr int MAXB = FF_MAX_H / 4 / 32;  // 32-column blocks per warp
+            uint32_t res[MAXB][16];
+#pragma unroll
+            for (int c = 0; c < MAXB; ++c) {
+                if (c < nch_out) {
+                    const int col = col_base + c * 32;
+                    const uint32_t arow = sA + (col >> 6) * FF_BOX_BYTES + static_cast<uint32_t>(r) * 128;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const uint32_t chunk = static_cast<uint32_t>(((col & 63) >> 3) + i) ^ swz;
+                        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+                                     : "=r"(res[c][4 * i]), "=r"(res[c][4 * i + 1]), "=r"(res[c][4 * i + 2]), "=r"(res[c][4 * i + 3])
+                                     : "r"(arow + chunk * 16)
+                                     : "memory");
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(FB_A_EMPTY));
             mbar_wait(bar(FB_OUT_FULL), t & 1);
             tc_fence_after();
             const uint32_t tout = tlane + col_base;
-            for (int c = 0; c < nch_out; ++c) {
-                tmem_ld_32x32(tout + c * 32, v);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) res[i] = res_next[i];
-                if (c + 1 < nch_out) {  // next block's residual while this one is processed
-                    ldg256(rrow + (c + 1) * 32, res_next);
-                    ldg256(rrow + (c + 1) * 32 + 16, res_next + 8);
-                }
+            for (int c = 0; c < MAXB; ++c) {
+                if (c >= nch_out) break;
+                tmem_ld_32x32(tout + c * 32, v);
                 const int col = col_base + c * 32;
                 const uint32_t bp = sB2 + 4 * col, gp = sG + 4 * col;
                 if (lane == 0) tma_store_wait_read<1>();  // the block filled two rounds ago has been read
@@ -411,7 +427,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constan
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         // x = acc + (b2 + beta) + gamma * (raw * rstd - mean * rstd), two columns at a time
-                        const uint32_t w = res[4 * i + e];
+                        const uint32_t w = res[c][4 * i + e];
                         const uint64_t raw = pk2u(w << 16, w & 0xffff0000u);
                         const uint64_t x = fma2(gg[e], fma2(raw, rstd2, nm2), add2(pk2u(v[8 * i + 2 * e], v[8 * i + 2 * e + 1]), bb[e]));
                         osum2 = add2(osum2, x);

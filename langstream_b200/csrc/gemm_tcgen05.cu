@@ -50,7 +50,7 @@ struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = (BN / PAIR) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int FIXED_BYTES = Epi<BN>::STAGING_BYTES + Epi<BN>::PARAM_BYTES + 256 + 1024;  // + barriers + alignment
+    static constexpr int FIXED_BYTES = Epi<BN>::STAGING_BYTES + Epi<BN>::PARAM_BYTES + 512 + 1024;  // + barriers + alignment
     static constexpr int FIT = (227 * 1024 - FIXED_BYTES) / STAGE_BYTES;
     static constexpr int STAGES = FIT > 6 ? 6 : FIT;
     static constexpr int STAGING_OFFSET = STAGES * STAGE_BYTES;
@@ -73,7 +73,8 @@ template <int BN, int EPI, int PAIR>
 __global__ void __launch_bounds__(Epi<BN>::THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant__ CUtensorMap tmapW,
                const __grid_constant__ CUtensorMap tmapC, const float* __restrict__ bias,
-               const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int f16_from_col, const LnArgs ln) {
+               const __nv_bfloat16* __restrict__ residual, int M, int N, int K, int f16_from_col,
+               const __grid_constant__ LnArgs ln) {
     using cfg = Cfg<BN, PAIR>;
     constexpr int STAGES = cfg::STAGES;
     const uint32_t cta_rank = PAIR == 2 ? cluster_ctarank() : 0u;
@@ -89,6 +90,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
     const uint32_t bar_tfull = bar_empty + 8 * STAGES;
     const uint32_t bar_tempty = bar_tfull + 16;
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(bars + 2 * STAGES + 4);
+    const uint32_t bar_res = bar_tempty + 16 + 16;  // [EPI_WARPS][2]: a warp's residual blocks have landed (TMA)
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -105,6 +107,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             mbar_init(bar_tfull + 8 * a, 1);
             mbar_init(bar_tempty + 8 * a, EPI_WARPS * PAIR);  // one arrive per epilogue warp (of both CTAs)
         }
+        for (int w = 0; w < 2 * EPI_WARPS; ++w) mbar_init(bar_res + 8 * w, 1);
         fence_mbar_init();
     }
     if (warp == 1) {
@@ -226,6 +229,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
         int buf = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
+        // residual through TMA (see LnArgs::res_map): two chunks per tile = the warp's two staging blocks
+        const bool tma_res = kRes && NCH == 2 && ln.has_res_map != 0;
+        const uint32_t my_res_bar = bar_res + 16 * ew;
+        uint32_t res_phase = 0;
         // TMEM "empty" arrivals go to the leader's barrier (the leader issues the MMAs)
         const uint32_t lead_tempty = PAIR == 2 ? mapa_u32(bar_tempty, 0) : bar_tempty;
         auto release_acc = [&](int which) {
@@ -272,7 +279,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             }
             const __nv_bfloat16* rrow = kRes ? residual + static_cast<size_t>(row_ok ? grow : 0) * N + col_base : nullptr;
             uint32_t res[16], res_next[16];
-            if (kRes) {  // residual of chunk 0
+            if (kRes && tma_res) {
+                // both residual blocks of this tile -> the warp's staging blocks, in flight while the accumulator is
+                // computed; the previous tile's stores must have read the blocks first
+                if (lane == 0) {
+                    tma_store_wait_read<0>();
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        mbar_arrive_expect_tx(my_res_bar + 8 * c, 2048);
+                        tma_load_2d(stg_addr + c * 2048, &ln.res_map, my_res_bar + 8 * c, col_base + c * 32, row0);
+                    }
+                }
+            } else if (kRes) {  // residual of chunk 0
                 ldg256(rrow, res_next);
                 ldg256(rrow + 16, res_next + 8);
             }
@@ -339,7 +357,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             for (int c = 0; c < NCH; ++c) {
                 uint32_t(&v)[32] = (c & 1) ? vb : va;
                 uint32_t(&vnext)[32] = (c & 1) ? va : vb;
-                if (kRes) {
+                if (kRes && tma_res) {
+                    // this thread's row of the residual block: 64 bytes at the swizzled positions the output will take
+                    mbar_wait(my_res_bar + 8 * c, res_phase);
+                    const uint32_t rblk = stg_addr + c * 2048 + lane * 64;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];"
+                                     : "=r"(res[4 * i]), "=r"(res[4 * i + 1]), "=r"(res[4 * i + 2]), "=r"(res[4 * i + 3])
+                                     : "r"(rblk + ((static_cast<uint32_t>(i) ^ sw) * 16))
+                                     : "memory");
+                } else if (kRes) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i) res[i] = res_next[i];
                     if (c + 1 < NCH) {
@@ -425,6 +453,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmapA, const __grid_constant_
             }
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
+            res_phase ^= 1;
         }
         if (lane == 0) tma_store_wait_all<0>();  // global writes complete before the kernel ends
     }
