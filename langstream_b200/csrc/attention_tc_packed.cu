@@ -29,7 +29,8 @@ constexpr int AT_TILE_BYTES = AT_ROWS * AT_D * 2;      // 8 KB: one of Q / K / V
 constexpr int AT_STAGE_BYTES = 3 * AT_TILE_BYTES;      // 24 KB
 constexpr int AT_P_BYTES = AT_ROWS * 128 * 2;          // 32 KB: P tile, fp16 [128 x 128]
 constexpr int AT_SLOT_COLS = 160;
-constexpr int AT_SMEM = AT_NST * AT_STAGE_BYTES + AT_G * AT_P_BYTES + 512 + 1024;
+constexpr int AT_OSTAGE_BYTES = 2048;                  // per softmax warp: a 32 x 32 bf16 block of ctx, source of a TMA store
+constexpr int AT_SMEM = AT_NST * AT_STAGE_BYTES + AT_G * AT_P_BYTES + AT_G * 4 * AT_OSTAGE_BYTES + 512 + 1024;
 
 // K-major operand with 64-byte rows written by TMA SWIZZLE_64B: 8-row atoms 512 B apart.
 __device__ __forceinline__ uint64_t desc_sw64(uint32_t addr) {
@@ -149,7 +150,8 @@ __device__ __noinline__ float softmax_row_exp_masked(uint32_t s_tmem, uint32_t p
 // PACKED: items are the tiles of a tile list (several short sequences per tile); otherwise one tile per sequence.
 template <bool PACKED>
 __global__ void __launch_bounds__(AT_THREADS, 1)
-attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const int32_t* __restrict__ cu_seqlens, int H,
+attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_constant__ CUtensorMap tmapCtx,
+                    const int32_t* __restrict__ cu_seqlens, int H,
                     int heads, int n_seq, const int32_t* __restrict__ tiles, const uint32_t* __restrict__ rowinfo,
                     __nv_bfloat16* __restrict__ ctx, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
@@ -158,7 +160,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const int32_t* 
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t smem_base = smem_u32(smem);
     const uint32_t sP = smem_base + AT_NST * AT_STAGE_BYTES;  // two 32 KB P tiles, 1024-byte aligned
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AT_NST * AT_STAGE_BYTES + AT_G * AT_P_BYTES);
+    const uint32_t sO = sP + AT_G * AT_P_BYTES;  // ctx staging blocks, one per softmax warp
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + AT_NST * AT_STAGE_BYTES + AT_G * AT_P_BYTES + AT_G * 4 * AT_OSTAGE_BYTES);
     const uint32_t bar_full = smem_u32(bars);            // [NST]
     const uint32_t bar_empty = bar_full + 8 * AT_NST;    // [NST]
     const uint32_t bar_sfull = bar_empty + 8 * AT_NST;     // [G] S accumulator written
@@ -171,6 +174,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const int32_t* 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmapQKV);
+        tma_prefetch_desc(&tmapCtx);
         for (int s = 0; s < AT_NST; ++s) {
             mbar_init(bar_full + 8 * s, 1);
             mbar_init(bar_empty + 8 * s, 1);
@@ -300,8 +304,31 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const int32_t* 
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_ofree + 8 * j);
-            if (row < prev_s) {
-                const float inv = 1.0f / prev_sum;
+            const float inv = 1.0f / prev_sum;
+            if (quad * 32 + 32 <= prev_s) {
+                // all 32 rows of this warp belong to the sequence: the 32 x 32 block goes out as ONE TMA store from a
+                // swizzled staging block (per-thread 16-byte stores to rows 768 bytes apart cost a fifth of the kernel:
+                // every store instruction touches 32 different lines)
+                const uint32_t stage = sO + static_cast<uint32_t>(warp - 2) * AT_OSTAGE_BYTES;
+                if (lane == 0) tma_store_wait_read<0>();  // the previous store has read the block
+                __syncwarp();
+                const uint32_t sw64 = (static_cast<uint32_t>(lane) >> 1) & 3;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stage + lane * 64 + ((static_cast<uint32_t>(c) ^ sw64) * 16)),
+                                 "r"(pack_bf16x2(__uint_as_float(ov[8 * c]) * inv, __uint_as_float(ov[8 * c + 1]) * inv)),
+                                 "r"(pack_bf16x2(__uint_as_float(ov[8 * c + 2]) * inv, __uint_as_float(ov[8 * c + 3]) * inv)),
+                                 "r"(pack_bf16x2(__uint_as_float(ov[8 * c + 4]) * inv, __uint_as_float(ov[8 * c + 5]) * inv)),
+                                 "r"(pack_bf16x2(__uint_as_float(ov[8 * c + 6]) * inv, __uint_as_float(ov[8 * c + 7]) * inv))
+                                 : "memory");
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&tmapCtx, stage, prev_head * AT_D, prev_t0 + quad * 32);
+                    tma_store_commit();
+                }
+            } else if (row < prev_s) {
                 uint4* dst = reinterpret_cast<uint4*>(ctx + static_cast<size_t>(prev_t0 + row) * H + prev_head * AT_D);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
@@ -355,6 +382,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const int32_t* 
             prev_sum = sum;
         }
         if (have_prev) collect(uses - 1);
+        if (lane == 0) tma_store_wait_all<0>();  // ctx writes complete before the kernel ends
     }
 
     tc_fence_before();
@@ -433,8 +461,9 @@ int attention_tc_packed_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqle
     if (tiles == nullptr || rowinfo == nullptr) return fail(LSC_E_INVALID, "attention (packed tiles): tile list missing");
     if (n_seq <= 0 || T <= 0) return 0;
     if (H / heads != AT_D || max_seqlen > AT_ROWS) return fail(LSC_E_UNSUPPORTED, "attention (packed tiles): needs d_head 32 and s <= 128");
-    CUtensorMap tm;
+    CUtensorMap tm, tmc;
     LSC_TRY(make_tmap_bf16_box(&tm, qkv, static_cast<uint64_t>(T), static_cast<uint64_t>(3) * H, AT_ROWS, AT_D, 64));
+    LSC_TRY(make_tmap_bf16_store32(&tmc, ctx, static_cast<uint64_t>(T), static_cast<uint64_t>(H)));
     static bool configured[64] = {};
     int dev = 0;
     LSC_CUDA(cudaGetDevice(&dev));
@@ -455,7 +484,7 @@ int attention_tc_packed_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqle
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = attr;
     lc.numAttrs = 1;
-    LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc_kernel<true>, tm, cu_seqlens, H, heads, n_seq, tiles, rowinfo, ctx, scale_log2e));
+    LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc_kernel<true>, tm, tmc, cu_seqlens, H, heads, n_seq, tiles, rowinfo, ctx, scale_log2e));
     LSC_CUDA(cudaGetLastError());
     return 1;
 }
