@@ -340,7 +340,7 @@ def run_topk(args, world, rank, local_rank, dev, stream, barrier, max_over_ranks
     steps_topk = max(3, min(args.steps, 20))
     topk_traffic = None
     try:
-        topk_traffic = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())["topk_scan_kernel"]["dram_bytes_per_launch"]
+        topk_traffic = json.loads((ROOT / "profiles" / "r02_traffic.json").read_text())["topk_scan_kernel"]["dram_bytes_per_launch"]
     except Exception:
         pass
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -781,7 +781,7 @@ def run_cuda(args):
         other_flop = 0.0
     dom_tflops = dom_flop / (dom_ms / 1000.0) / 1e12 if dom_ms > 0 else 0.0
     traffic = None
-    tpath = ROOT / "profiles" / "r01_traffic.json"
+    tpath = ROOT / "profiles" / "r02_traffic.json"
     if tpath.exists():
         try:
             traffic = json.loads(tpath.read_text())[traffic_key]["dram_bytes_per_launch_avg"]
