@@ -449,8 +449,16 @@ int launch_d(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int
 
 }  // namespace
 
+bool attention_wants_order(int n_seq, int T, int H, int heads, int max_seqlen) {
+    static const bool no_ragged = getenv("LSC_ATTN_NO_RAGGED") != nullptr;  // debug: one full tile per item whatever its length
+    static const bool legacy_only = getenv("LSC_ATTN_LEGACY") != nullptr;
+    return !no_ragged && !legacy_only && n_seq > 0 && heads > 0 && H / heads == 32 && max_seqlen <= 128 &&
+           static_cast<long long>(n_seq) * 128 != T;
+}
+
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
-                     int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles, const uint32_t* rowinfo) {
+                     int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles, const uint32_t* rowinfo,
+                     const int32_t* order) {
     if (n_seq <= 0 || max_seqlen <= 0) return 0;
     const int d = H / heads;
     if (d * heads != H) return fail(LSC_E_INVALID, "attention: hidden not divisible by heads");
@@ -464,6 +472,8 @@ int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_
         const int sms = (dev >= 0 && dev < 64) ? sms_cache[dev] : 148;
         if (tiles != nullptr && rowinfo != nullptr)  // short sequences sharing 128-row tiles (attention_tc_packed.cu)
             return attention_tc_packed_launch(qkv, cu_seqlens, n_seq, T, H, heads, max_seqlen, tiles, rowinfo, ctx, sms, stream);
+        if (attention_wants_order(n_seq, T, H, heads, max_seqlen))  // some sequence is shorter than its 128-row tile
+            return attention_tc_ragged_launch(qkv, cu_seqlens, order, n_seq, T, H, heads, max_seqlen, ctx, sms, stream);
         return attention_tc_launch(qkv, cu_seqlens, n_seq, T, H, heads, max_seqlen, ctx, sms, stream);
     }
     if (d == 64 && attention_tc64_supported(H, heads)) {  // tcgen05, any sequence length
@@ -502,11 +512,24 @@ extern "C" int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_se
             return trc;
         }
     }
+    // ragged batches: sequences by descending length, as the encoder builds them once per pass (LSC_DEBUG_ATTN_NO_ORDER=1: batch order)
+    int32_t* order = nullptr;
+    if (tiles == nullptr && getenv("LSC_DEBUG_ATTN_NO_ORDER") == nullptr && lsc::attention_wants_order(n_seq, total_tokens, hidden, heads, max_seqlen)) {
+        if (cudaMalloc(reinterpret_cast<void**>(&order), static_cast<size_t>(n_seq) * sizeof(int32_t)) != cudaSuccess)
+            return lsc::fail(LSC_E_NOMEM, "lsc_debug_attention_dev: order list");
+        const int orc = lsc::attention_order_launch(d_cu_seqlens, n_seq, order, static_cast<cudaStream_t>(stream));
+        if (orc < 0) {
+            cudaFree(order);
+            return orc;
+        }
+    }
     int rc = lsc::attention_launch(static_cast<const __nv_bfloat16*>(d_qkv), d_cu_seqlens, n_seq, total_tokens, hidden,
-                                   heads, max_seqlen, static_cast<__nv_bfloat16*>(d_ctx), static_cast<cudaStream_t>(stream), tiles, rowinfo);
-    if (tiles != nullptr) {
+                                   heads, max_seqlen, static_cast<__nv_bfloat16*>(d_ctx), static_cast<cudaStream_t>(stream), tiles, rowinfo,
+                                   order);
+    if (tiles != nullptr || order != nullptr) {
         cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
-        cudaFree(tiles);
+        if (tiles != nullptr) cudaFree(tiles);
+        if (order != nullptr) cudaFree(order);
     }
     return rc < 0 ? rc : LSC_OK;
 }

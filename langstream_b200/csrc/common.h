@@ -162,11 +162,19 @@ int layernorm_launch(const __nv_bfloat16* in, const float* gamma, const float* b
 // tiles (optional, only used by the d_head 32 / s <= 128 kernel): the packing of short sequences into 128-row
 // attention tiles built by attention_tiles_launch for the same cu_seqlens (tiles: 2 * n_seq + 2 ints; rowinfo: one
 // word per token row = the key range of the row's own sequence inside its tile).
+// order (optional, ragged batches of the same kernel class): the sequences by descending length.
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles = nullptr,
-                     const uint32_t* rowinfo = nullptr);
+                     const uint32_t* rowinfo = nullptr, const int32_t* order = nullptr);
+// true when attention_launch would take the length-adaptive kernel, which likes an `order` (attention_order_launch)
+bool attention_wants_order(int n_seq, int T, int H, int heads, int max_seqlen);
 int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                         int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
+// the same for batches in which not every sequence fills its tile: every stage sized by the item's length (attention_tc_ragged.cu)
+// order (optional): the sequences by descending length, from attention_order_launch (n_seq ints, once per pass)
+int attention_tc_ragged_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, const int32_t* order, int n_seq, int T, int H,
+                               int heads, int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
+int attention_order_launch(const int32_t* cu_seqlens, int n_seq, int32_t* order, cudaStream_t stream);
 int attention_tc_packed_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                                int max_seqlen, const int32_t* tiles, const uint32_t* rowinfo, __nv_bfloat16* ctx,
                                int num_sms, cudaStream_t stream);

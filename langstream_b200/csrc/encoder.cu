@@ -268,8 +268,11 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
     const bool pack_tiles = !no_pack && T > 0 && H / c.heads == 32 && max_seqlen <= 128 && n_seq > 1 &&
                             n_seq <= attention_tiles_max_seqs() &&
                             static_cast<int64_t>(n_seq) * 48 > static_cast<int64_t>(T);
-    const int64_t tiles_need = 2 * static_cast<int64_t>(n_seq) + 2 + T;
-    if (pack_tiles && tiles_need > e->cap_tiles) {
+    // Other ragged batches of that kernel class run the length-adaptive kernel (attention_tc_ragged.cu) over the sequences
+    // in descending length, sorted once per pass into the same scratch buffer.
+    const bool order_seqs = !pack_tiles && T > 0 && n_seq > 1 && attention_wants_order(n_seq, T, H, c.heads, max_seqlen);
+    const int64_t tiles_need = pack_tiles ? 2 * static_cast<int64_t>(n_seq) + 2 + T : (order_seqs ? n_seq : 0);
+    if (tiles_need > e->cap_tiles) {
         LSC_CUDA(cudaDeviceSynchronize());
         if (e->d_tiles) cudaFree(e->d_tiles);
         e->d_tiles = nullptr;
@@ -286,6 +289,11 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
         LSC_LAUNCH(2, attention_tiles_launch(d_cu, n_seq, T, e->d_tiles, ri, st));
         tiles = e->d_tiles;
         rowinfo = ri;
+    }
+    const int32_t* order = nullptr;
+    if (order_seqs) {
+        LSC_LAUNCH(2, attention_order_launch(d_cu, n_seq, e->d_tiles, st));
+        order = e->d_tiles;
     }
     if (T > 0) {
         if (c.gemm_impl == 0) {
@@ -321,7 +329,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                 ln_in.c = w.c_qkv; ln_in.stats_in = e->stats_x; ln_in.p_in = PX; ln_in.inv_h = inv_h; ln_in.eps = c.ln_eps;
                 LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.d_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H,
                                    EPI_LNIN_BIAS, 2 * H, ln_in, st));
-                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order));
                 LnArgs ln_o;  // tmp = ctx.Wo^T + b + LN_in(x); statistics of tmp -> stats_1
                 ln_o.stats_in = e->stats_x; ln_o.p_in = PX; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
                 ln_o.inv_h = inv_h; ln_o.eps = c.ln_eps;
@@ -352,7 +360,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
             for (int l = 0; l < c.layers; ++l) {
                 const LayerW& w = e->layers[l];
                 LSC_LAUNCH(1, gemm(e, none, e->x, none, w.w_qkv, w.b_qkv, nullptr, none, e->qkv, T, 3 * H, H, EPI_BIAS, 2 * H, no_ln, st));
-                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order));
                 LSC_LAUNCH(1, gemm(e, none, e->ctx, none, w.w_o, w.b_o, e->x, none, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, H, no_ln, st));
                 LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
                 LSC_LAUNCH(1, gemm(e, none, e->x1, none, w.w_1, w.b_1, nullptr, none, e->ffn, T, F, H, EPI_BIAS_GELU, F, no_ln, st));

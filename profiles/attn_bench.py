@@ -1,5 +1,6 @@
 """Micro-benchmark of the attention kernel alone (lsc_debug_attention_dev, CUDA events)."""
-import sys
+import os, sys
+os.environ.setdefault("LSC_DEBUG_ATTN_NO_ORDER", "1")  # the debug entry would allocate + sort per call; the encoder sorts once per pass
 from pathlib import Path
 import numpy as np, torch
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))

@@ -91,3 +91,34 @@ def test_packed_tiles_match_fp32_reference(native_lib, cuda_device, lens, monkey
     err = (got - ref).abs()
     assert bool((err <= 0.01 + 0.01 * ref.abs()).all()), f"max err {err.max().item():.4f}"
     assert err.mean().item() < 2e-3
+
+
+def test_ragged_kernel_every_length(native_lib, cuda_device):
+    """The length-adaptive kernel (attention_tc_ragged.cu): every length 1..128 several times, in random order, empty
+    sequences between them, many more items than SMs x groups - so that short items follow long ones in the same
+    shared-memory stage and TMEM slot (stale rows behind the loaded part must never reach a stored row)."""
+    import torch
+    from langstream_b200 import _native
+
+    H, heads = 384, 12
+    rng = np.random.default_rng(11)
+    lens = list(range(1, 129)) * 3 + [0] * 7
+    rng.shuffle(lens)
+    lens = [int(x) for x in lens]
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    T = int(cu[-1])
+    g = torch.Generator(device="cpu").manual_seed(77)
+    qkv = (torch.randn(T, 3 * H, generator=g) * 2.0).to(torch.bfloat16).to(cuda_device)
+    packed = qkv.clone()
+    packed[:, 2 * H:] = qkv[:, 2 * H:].to(torch.float16).view(torch.bfloat16)
+    d_cu = torch.from_numpy(cu).to(cuda_device)
+    ref = _reference(qkv, cu, H, heads)
+    for _ in range(2):  # the second run starts from the first run's leftovers in shared memory / TMEM
+        ctx = torch.full((T, H), float("nan"), dtype=torch.bfloat16, device=cuda_device)
+        _native.debug_attention_dev(packed, d_cu, len(lens), T, H, heads, max(lens), ctx, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        got = ctx.float()
+        assert torch.isfinite(got).all()
+        err = (got - ref).abs()
+        assert bool((err <= 0.02 + 0.01 * ref.abs()).all()), f"max err {err.max().item():.4f}"
+        assert err.mean().item() < 4e-3
