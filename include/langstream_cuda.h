@@ -75,7 +75,12 @@ typedef struct lsc_encoder_config {
     float ln_eps;
     int32_t gemm_impl; /* 0 = tcgen05/TMEM/TMA (product path); 1 = CUDA-core validation GEMM
                           (debug only: used by the tests to cross-check the tensor-core path) */
-    int32_t reserved[7];
+    int32_t arch;      /* 0 = BERT (BertModel: all-MiniLM, BGE, e5); 1 = MPNet (MPNetModel: all-mpnet-base-v2) - no
+                          token-type embeddings (type_vocab must be 0), position ids start at 2, and a relative-position
+                          bias shared by all layers is added to the attention scores; needs a head dimension of 64 */
+    int32_t rel_buckets;      /* arch 1: relative_attention_num_buckets (32) */
+    int32_t rel_max_distance; /* arch 1: distance at which the buckets saturate (128; at most 128) */
+    int32_t reserved[4];
 } lsc_encoder_config;
 
 /*
@@ -88,6 +93,9 @@ typedef struct lsc_encoder_config {
  *     attention.output.dense.weight [hidden,hidden], .bias, attention.output.LayerNorm weight, bias,
  *     intermediate.dense.weight [ffn,hidden], .bias, output.dense.weight [hidden,ffn], .bias,
  *     output.LayerNorm weight, bias.
+ * arch 1 (MPNetModel): no token_type_embeddings; encoder.relative_attention_bias.weight [rel_buckets,heads] follows the
+ * embeddings LayerNorm; per layer attention.attn.q / k / v / o and attention.LayerNorm take the places of query / key /
+ * value / attention.output.dense and attention.output.LayerNorm.
  * This is the state_dict of the HuggingFace BertModel that DJL traces and runs
  * (AI/com/datastax/oss/streaming/ai/embeddings/AbstractHuggingFaceEmbeddingService.java:132-161).
  */
@@ -367,6 +375,13 @@ int lsc_tokenizer_create(const char* vocab_txt, size_t nbytes, int do_lower_case
  */
 int lsc_tokenizer_encode(lsc_tokenizer* tok, const char* const* texts, const int32_t* text_nbytes,
                          int32_t n_texts, int32_t* token_ids, int64_t capacity, int32_t* cu_seqlens);
+
+/*
+ * Other template tokens than [CLS] A [SEP]: MPNet's tokenizer (all-mpnet-base-v2) is the same BERT pipeline with the
+ * template "<s> A </s>" (tokenizer.json: TemplateProcessing) and [UNK] as the unknown token.  Each argument is a token
+ * of the vocabulary, or NULL to keep the current one.  Call before the first lsc_tokenizer_encode.
+ */
+int lsc_tokenizer_set_special(lsc_tokenizer* tok, const char* cls_token, const char* sep_token, const char* unk_token);
 
 int32_t lsc_tokenizer_vocab_size(const lsc_tokenizer* tok);
 void lsc_tokenizer_destroy(lsc_tokenizer* tok);

@@ -147,12 +147,19 @@ public class CudaProvider implements ServiceProviderProvider {
         CudaEmbeddingsService(Path modelDir, int device, int maxBatch, long flushMicros, MetricsReporter metrics) throws Exception {
             Map<String, Object> cfg = EmbeddingsService.createObjectMapper()
                     .readValue(modelDir.resolve("config.json").toFile(), Map.class);
-            this.maxPosition = ((Number) cfg.get("max_position_embeddings")).intValue();
+            // config.json's model_type picks the graph: "bert" (all-MiniLM, BGE, e5) or "mpnet" (all-mpnet-base-v2:
+            // no token types, positions from 2, bucketed relative-position bias in the attention kernel)
+            boolean mpnet = "mpnet".equals(String.valueOf(cfg.get("model_type")));
+            int positions = ((Number) cfg.get("max_position_embeddings")).intValue();
+            this.maxPosition = mpnet ? positions - 2 : positions;
             this.maxBatch = maxBatch;
             this.flushNanos = flushMicros * 1000;
             boolean lower = Boolean.parseBoolean(String.valueOf(cfg.getOrDefault("do_lower_case", "true")));
             this.tokenizer = LangstreamCuda.tokenizerCreate(
                     java.nio.file.Files.readAllBytes(modelDir.resolve("vocab.txt")), lower, maxPosition, 0);
+            if (mpnet) {
+                LangstreamCuda.tokenizerSetSpecial(tokenizer, "<s>", "</s>", null);  // template <s> A </s>
+            }
             try (FileChannel ch = FileChannel.open(modelDir.resolve("weights.f32"), StandardOpenOption.READ)) {
                 ByteBuffer weights = ByteBuffer.allocateDirect((int) ch.size()).order(ByteOrder.nativeOrder());
                 while (weights.hasRemaining() && ch.read(weights) >= 0) {}
@@ -163,9 +170,12 @@ public class CudaProvider implements ServiceProviderProvider {
                         ((Number) cfg.get("num_attention_heads")).intValue(),
                         ((Number) cfg.get("intermediate_size")).intValue(),
                         ((Number) cfg.get("vocab_size")).intValue(),
-                        maxPosition,
-                        ((Number) cfg.getOrDefault("type_vocab_size", 2)).intValue(),
+                        positions,
+                        mpnet ? 0 : ((Number) cfg.getOrDefault("type_vocab_size", 2)).intValue(),
                         ((Number) cfg.getOrDefault("layer_norm_eps", 1e-12)).floatValue(),
+                        mpnet ? 1 : 0,
+                        mpnet ? ((Number) cfg.getOrDefault("relative_attention_num_buckets", 32)).intValue() : 0,
+                        mpnet ? 128 : 0,
                         weights, device);
             }
             this.dim = LangstreamCuda.encoderDim(encoder);

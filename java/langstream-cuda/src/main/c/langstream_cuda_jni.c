@@ -22,8 +22,8 @@ JNIEXPORT jint JNICALL Java_ai_langstream_cuda_LangstreamCuda_deviceCount(JNIEnv
 }
 JNIEXPORT jlong JNICALL Java_ai_langstream_cuda_LangstreamCuda_encoderCreate(
         JNIEnv* env, jclass c, jint layers, jint hidden, jint heads, jint ffn, jint vocab, jint maxPos,
-        jint typeVocab, jfloat eps, jobject weights, jint device) {
-    lsc_encoder_config cfg = {layers, hidden, heads, ffn, vocab, maxPos, typeVocab, eps, 0, {0}};
+        jint typeVocab, jfloat eps, jint arch, jint relBuckets, jint relMaxDistance, jobject weights, jint device) {
+    lsc_encoder_config cfg = {layers, hidden, heads, ffn, vocab, maxPos, typeVocab, eps, 0, arch, relBuckets, relMaxDistance, {0}};
     lsc_encoder* enc = NULL;
     CHECK(lsc_encoder_create(&cfg, ADDR(weights), (size_t)(*env)->GetDirectBufferCapacity(env, weights), device, &enc));
     return (jlong)(intptr_t)enc;
@@ -111,6 +111,17 @@ JNIEXPORT jlong JNICALL Java_ai_langstream_cuda_LangstreamCuda_tokenizerCreate(
     (*env)->ReleaseByteArrayElements(env, vocab, p, JNI_ABORT);
     CHECK(rc);
     return (jlong)(intptr_t)tok;
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_tokenizerSetSpecial(
+        JNIEnv* env, jclass c, jlong tok, jstring cls, jstring sep, jstring unk) {
+    const char* a = cls ? (*env)->GetStringUTFChars(env, cls, NULL) : NULL;
+    const char* b = sep ? (*env)->GetStringUTFChars(env, sep, NULL) : NULL;
+    const char* u = unk ? (*env)->GetStringUTFChars(env, unk, NULL) : NULL;
+    int rc = lsc_tokenizer_set_special((lsc_tokenizer*)(intptr_t)tok, a, b, u);
+    if (a) (*env)->ReleaseStringUTFChars(env, cls, a);
+    if (b) (*env)->ReleaseStringUTFChars(env, sep, b);
+    if (u) (*env)->ReleaseStringUTFChars(env, unk, u);
+    CHECK(rc);
 }
 JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_tokenizerEncode(
         JNIEnv* env, jclass c, jlong tok, jobject utf8, jobject nbytes, jint nTexts, jobject ids, jobject cu) {

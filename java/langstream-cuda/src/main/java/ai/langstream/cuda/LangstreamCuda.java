@@ -23,9 +23,10 @@ public final class LangstreamCuda {
     public static native int deviceCount();
 
     // ---- encoder (replaces DJL Criteria.loadModel / Predictor.predict) ----
+    /** arch: 0 = BERT, 1 = MPNet (typeVocab 0, relBuckets / relMaxDistance from config.json); see lsc_encoder_config. */
     public static native long encoderCreate(
             int layers, int hidden, int heads, int ffn, int vocab, int maxPosition, int typeVocab,
-            float lnEps, ByteBuffer weightsFp32, int device);
+            float lnEps, int arch, int relBuckets, int relMaxDistance, ByteBuffer weightsFp32, int device);
 
     public static native void encoderEmbed(
             long encoder, IntBuffer tokenIds, IntBuffer cuSeqlens, int nSeq, FloatBuffer out);
@@ -43,6 +44,9 @@ public final class LangstreamCuda {
     public static native int encoderDim(long encoder);
 
     // ---- host tokenizer (replaces DJL's HuggingFaceTokenizer inside predictor.predict) ----
+    /** lsc_tokenizer_set_special: template tokens other than [CLS] / [SEP] / [UNK] (MPNet: "<s>", "</s>"); null keeps one. */
+    public static native void tokenizerSetSpecial(long tokenizer, String cls, String sep, String unk);
+
     public static native long tokenizerCreate(byte[] vocabTxt, boolean doLowerCase, int maxLength, int nThreads);
 
     /**

@@ -39,7 +39,10 @@ class EncoderConfig(C.Structure):
         ("type_vocab", C.c_int32),
         ("ln_eps", C.c_float),
         ("gemm_impl", C.c_int32),
-        ("reserved", C.c_int32 * 7),
+        ("arch", C.c_int32),
+        ("rel_buckets", C.c_int32),
+        ("rel_max_distance", C.c_int32),
+        ("reserved", C.c_int32 * 4),
     ]
 
 
@@ -97,6 +100,7 @@ SIGNATURES = {
     "lsc_index_destroy": (None, [_vp]),
     "lsc_tokenizer_create": (C.c_int, [C.c_char_p, C.c_size_t, C.c_int, _i32, _i32, C.POINTER(_vp)]),
     "lsc_tokenizer_encode": (C.c_int, [_vp, _vp, _vp, _i32, _vp, _i64, _vp]),
+    "lsc_tokenizer_set_special": (C.c_int, [_vp, C.c_char_p, C.c_char_p, C.c_char_p]),
     "lsc_tokenizer_vocab_size": (_i32, [_vp]),
     "lsc_tokenizer_destroy": (None, [_vp]),
     "lsc_rerank_mmr": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
@@ -162,7 +166,8 @@ class Encoder:
     def __init__(self, spec, blob, device: int = 0, gemm_impl: int = 0):
         L = lib()
         cfg = EncoderConfig(spec.layers, spec.hidden, spec.heads, spec.ffn, spec.vocab, spec.max_position,
-                            spec.type_vocab, spec.ln_eps, gemm_impl)
+                            spec.type_vocab, spec.ln_eps, gemm_impl, getattr(spec, "arch_id", 0),
+                            getattr(spec, "rel_buckets", 0), getattr(spec, "rel_max_distance", 0))
         blob = _np.ascontiguousarray(blob, _np.float32)
         need = L.lsc_encoder_weights_nbytes(C.byref(cfg))
         if need == 0:
@@ -463,7 +468,9 @@ class WordPieceTokenizer:
     """lsc_tokenizer_*: the BERT WordPiece pipeline of the HuggingFace `tokenizers` library (what DJL's
     HuggingFaceTokenizer runs in the reference), multi-threaded, output packed for Encoder.embed."""
 
-    def __init__(self, vocab_txt, do_lower_case: bool = True, max_length: int = 512, n_threads: int = 0):
+    def __init__(self, vocab_txt, do_lower_case: bool = True, max_length: int = 512, n_threads: int = 0,
+                 cls_token: str | None = None, sep_token: str | None = None, unk_token: str | None = None):
+        """cls_token / sep_token / unk_token: template tokens other than [CLS] / [SEP] / [UNK] (MPNet: "<s>", "</s>")."""
         if isinstance(vocab_txt, str):
             vocab_txt = vocab_txt.encode("utf-8")
         h = _vp()
@@ -471,6 +478,9 @@ class WordPieceTokenizer:
                                          C.byref(h)))
         self._h = h
         self.max_length = int(max_length)
+        if cls_token or sep_token or unk_token:
+            enc = lambda t: t.encode("utf-8") if t else None  # noqa: E731
+            check(lib().lsc_tokenizer_set_special(h, enc(cls_token), enc(sep_token), enc(unk_token)))
 
     @classmethod
     def from_file(cls, path, **kw):

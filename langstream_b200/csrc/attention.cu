@@ -458,11 +458,13 @@ bool attention_wants_order(int n_seq, int T, int H, int heads, int max_seqlen) {
 
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles, const uint32_t* rowinfo,
-                     const int32_t* order) {
+                     const int32_t* order, const float* rel_tbl) {
     if (n_seq <= 0 || max_seqlen <= 0) return 0;
     const int d = H / heads;
     if (d * heads != H) return fail(LSC_E_INVALID, "attention: hidden not divisible by heads");
     static const bool legacy_only = getenv("LSC_ATTN_LEGACY") != nullptr;  // debug: force the mma.sync kernel
+    if (rel_tbl != nullptr && !(d == 64 && attention_tc64_supported(H, heads)))
+        return fail(LSC_E_UNSUPPORTED, "attention: a relative-position bias needs the d_head 64 tcgen05 kernel");
     if (d == 32 && max_seqlen <= 128 && !legacy_only) {
         static int sms_cache[64] = {};
         int dev = 0;
@@ -483,7 +485,7 @@ int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_
         if (dev >= 0 && dev < 64 && sms_cache64[dev] == 0)
             LSC_CUDA(cudaDeviceGetAttribute(&sms_cache64[dev], cudaDevAttrMultiProcessorCount, dev));
         return attention_tc64_launch(qkv, cu_seqlens, n_seq, T, H, heads, ctx, (dev >= 0 && dev < 64) ? sms_cache64[dev] : 148,
-                                     stream);
+                                     stream, rel_tbl);
     }
     if (d == 32) return launch_d<32>(qkv, cu_seqlens, n_seq, H, heads, max_seqlen, ctx, stream);
     if (d == 64) return launch_d<64>(qkv, cu_seqlens, n_seq, H, heads, max_seqlen, ctx, stream);

@@ -18,7 +18,10 @@
 //   warp 0      TMA producer: the item's Q tiles (once per round of four query tiles), K / K+V tiles in the ring
 //   warp 1      TMEM allocation, S issuer        warp 2      P.V issuer        warp 3      idle
 //   warps 4-19  softmax groups 0-3
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
+#include <vector>
 
 #include "common.h"
 #include "ptx.cuh"
@@ -37,6 +40,11 @@ constexpr int A6_KV_BYTES = A6_KT * A6_D * 2;     // 8 KB: one K or V tile
 constexpr int A6_STAGE_BYTES = 2 * A6_KV_BYTES;   // K | V
 constexpr int A6_P_BYTES = A6_QT * A6_KT * 2;     // 16 KB: P tile, fp16 [128 x 64]
 constexpr int A6_SMEM = A6_G * A6_Q_BYTES + A6_NST * A6_STAGE_BYTES + A6_G * A6_P_BYTES + 512 + 1024;
+// BIAS variant (MPNet): the relative-position bias of every head, [heads][ATT_REL_W] fp32 behind the barriers.  Entry
+// ATT_REL_HALF + r is the bias of (key position - query position) = r, times log2(e).  The buckets saturate at |r| >= 128,
+// so a thread whose 64 keys of a tile all lie beyond that may read any 64 saturated entries: clamping the first index
+// to [0, ATT_REL_W - 64] is exact and the table needs |r| <= 191 only.
+constexpr int A6_REL_MAXHEADS = (227 * 1024 - A6_SMEM) / (ATT_REL_W * 4);
 
 // barrier slots
 enum {
@@ -64,10 +72,11 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
+template <bool BIAS>
 __global__ void __launch_bounds__(A6_THREADS, 1)
 attention_tc64_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_constant__ CUtensorMap tmapKV,
                       const int32_t* __restrict__ cu_seqlens, int H, int heads, int n_items,
-                      __nv_bfloat16* __restrict__ ctx, float scale_log2e) {
+                      __nv_bfloat16* __restrict__ ctx, float scale_log2e, const float* __restrict__ rel_tbl) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     const uint32_t sQ = smem_u32(smem);                       // [A6_G] query tiles
@@ -77,9 +86,14 @@ attention_tc64_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     const uint32_t bar0 = smem_u32(bars);
     auto bar = [&](int slot) { return bar0 + 8u * static_cast<uint32_t>(slot); };
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(bars + B6_COUNT);
+    const uint32_t sT = bar0 + 512;  // BIAS: [heads][ATT_REL_W] fp32
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    if constexpr (BIAS) {  // model constants: nothing the previous kernel writes
+        float* t = reinterpret_cast<float*>(smem + A6_G * A6_Q_BYTES + A6_NST * A6_STAGE_BYTES + A6_G * A6_P_BYTES + 512);
+        for (int i = threadIdx.x; i < heads * ATT_REL_W; i += A6_THREADS) t[i] = __ldg(rel_tbl + i);
+    }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmapQ);
@@ -262,6 +276,11 @@ attention_tc64_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
             const int nq = (s + A6_QT - 1) / A6_QT, nk = (s + A6_KT - 1) / A6_KT;
             for (int q0 = 0; q0 < nq; q0 += A6_G) {
                 if (q0 + g >= nq) continue;  // this group has no query tile in this round (warp-uniform)
+                // BIAS: shared-memory address of this thread's bias entry for key 0 of key tile kt (see A6_REL_MAXHEADS)
+                auto rel_row = [&](int kt) {
+                    const int first = kt * A6_KT - ((q0 + g) * A6_QT + row) + ATT_REL_HALF;
+                    return sT + static_cast<uint32_t>(head * ATT_REL_W + min(max(first, 0), ATT_REL_W - A6_KT)) * 4u;
+                };
                 // ---- pass A: the row maximum over all keys ----
                 float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
                 for (int kt = 0; kt < nk; ++kt, ++su) {
@@ -275,7 +294,17 @@ attention_tc64_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar(B6_SFREE + g));
                     const int kleft = s - kt * A6_KT;  // keys of this tile that exist (the rest belong to other sequences)
-                    if (kleft >= A6_KT) {
+                    if constexpr (BIAS) {
+                        // scores in the log2 domain with the bias added: the maximum is taken over what is exponentiated
+                        const uint32_t tb = rel_row(kt);
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) {
+                            const float xa = fmaf(__uint_as_float(va[c]), scale_log2e, lds_f32(tb + 4 * c));
+                            const float xb = fmaf(__uint_as_float(vb[c]), scale_log2e, lds_f32(tb + 4 * (c + 32)));
+                            m4[c & 3] = fmaxf(m4[c & 3], c < kleft ? xa : -INFINITY);
+                            m4[c & 3] = fmaxf(m4[c & 3], c + 32 < kleft ? xb : -INFINITY);
+                        }
+                    } else if (kleft >= A6_KT) {
 #pragma unroll
                         for (int c = 0; c < 32; ++c) {
                             m4[c & 3] = fmaxf(m4[c & 3], __uint_as_float(va[c]));
@@ -290,7 +319,7 @@ attention_tc64_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                     }
                 }
                 const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-                const float nms = -mx * scale_log2e;
+                const float nms = BIAS ? -mx : -mx * scale_log2e;
                 // ---- pass B: P = exp2(S * c - max * c) -> fp16 -> K-major SWIZZLE_128B tile (row r at r * 128,
                 //      16-byte chunk c at (c ^ (r & 7)) * 16); the P.V issuer accumulates O in TMEM ----
                 float s4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -306,6 +335,8 @@ attention_tc64_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                     if (lane == 0) mbar_arrive(bar(B6_SFREE + g));
                     mbar_wait(bar(B6_PFREE + g), (pu & 1) ^ 1);  // the previous P.V has read the P tile
                     const int kleft = s - kt * A6_KT;
+                    uint32_t tb = 0;
+                    if constexpr (BIAS) tb = rel_row(kt);
 #pragma unroll
                     for (int half = 0; half < 2; ++half) {
                         uint32_t(&v)[32] = half ? vb : va;
@@ -314,7 +345,9 @@ attention_tc64_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                             float pe[8];
 #pragma unroll
                             for (int e = 0; e < 8; ++e) {
-                                const float x = fmaf(__uint_as_float(v[c8 * 8 + e]), scale_log2e, nms);
+                                float off = nms;
+                                if constexpr (BIAS) off += lds_f32(tb + 4 * (half * 32 + c8 * 8 + e));
+                                const float x = fmaf(__uint_as_float(v[c8 * 8 + e]), scale_log2e, off);
                                 pe[e] = ex2_approx(x);
                                 if (kleft < A6_KT) pe[e] = (half * 32 + c8 * 8 + e < kleft) ? pe[e] : 0.f;
                                 s4[e & 3] += pe[e];
@@ -373,6 +406,30 @@ attention_tc64_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
 
 }  // namespace
 
+// MPNetEncoder.compute_position_bias / relative_position_bucket (HuggingFace transformers, the graph DJL runs for an MPNet
+// model; call site AbstractHuggingFaceEmbeddingService.java:194-196): bias[h][q][k] = W[bucket(k - q)][h], the same for
+// every layer.  Half of the buckets per direction; the first half of those exact, the rest logarithmic up to max_distance.
+void attention_rel_table(const float* w, int buckets, int max_distance, int heads, std::vector<float>* out) {
+    out->assign(static_cast<size_t>(heads) * ATT_REL_W, 0.f);
+    const int nb = buckets / 2, max_exact = nb / 2;
+    for (int r = -ATT_REL_HALF; r <= ATT_REL_HALF; ++r) {
+        int n = -r, ret = 0;
+        if (n < 0) {
+            ret = nb;
+            n = -n;
+        }
+        if (n < max_exact) {
+            ret += n;
+        } else {  // float32 arithmetic, truncation toward zero: as torch evaluates it
+            const float v = logf(static_cast<float>(n) / static_cast<float>(max_exact)) /
+                            static_cast<float>(log(static_cast<double>(max_distance) / max_exact)) * static_cast<float>(nb - max_exact);
+            ret += std::min(max_exact + static_cast<int>(v), nb - 1);
+        }
+        for (int h = 0; h < heads; ++h)
+            (*out)[static_cast<size_t>(h) * ATT_REL_W + (r + ATT_REL_HALF)] = w[static_cast<size_t>(ret) * heads + h] * 1.4426950408889634f;
+    }
+}
+
 bool attention_tc64_supported(int H, int heads) {
     static const bool off = getenv("LSC_ATTN_LEGACY") != nullptr;  // debug: keep the mma.sync kernels
     return !off && heads > 0 && H / heads == A6_D && H % heads == 0;
@@ -380,9 +437,11 @@ bool attention_tc64_supported(int H, int heads) {
 
 // qkv: [T, 3H] with Q, K bf16 and V fp16; d_head == 64, any sequence length.
 int attention_tc64_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
-                          __nv_bfloat16* ctx, int num_sms, cudaStream_t stream) {
+                          __nv_bfloat16* ctx, int num_sms, cudaStream_t stream, const float* rel_tbl) {
     if (n_seq <= 0 || T <= 0) return 0;
     if (H / heads != A6_D) return fail(LSC_E_UNSUPPORTED, "attention_tc64: needs d_head 64");
+    if (rel_tbl != nullptr && heads > A6_REL_MAXHEADS)
+        return fail(LSC_E_UNSUPPORTED, "attention_tc64: too many heads for the relative-position table in shared memory");
     CUtensorMap tmQ, tmKV;
     LSC_TRY(make_tmap_bf16_box(&tmQ, qkv, static_cast<uint64_t>(T), static_cast<uint64_t>(3) * H, A6_QT, A6_D, 128));
     LSC_TRY(make_tmap_bf16_box(&tmKV, qkv, static_cast<uint64_t>(T), static_cast<uint64_t>(3) * H, A6_KT, A6_D, 128));
@@ -390,7 +449,9 @@ int attention_tc64_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, i
     int dev = 0;
     LSC_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !configured[dev]) {
-        LSC_CUDA(cudaFuncSetAttribute(attention_tc64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, A6_SMEM));
+        LSC_CUDA(cudaFuncSetAttribute(attention_tc64_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, A6_SMEM));
+        LSC_CUDA(cudaFuncSetAttribute(attention_tc64_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      A6_SMEM + A6_REL_MAXHEADS * ATT_REL_W * 4));
         if (dev >= 0 && dev < 64) configured[dev] = true;
     }
     const long long n_items = static_cast<long long>(heads) * n_seq;
@@ -399,15 +460,19 @@ int attention_tc64_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, i
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3(grid);
     lc.blockDim = dim3(A6_THREADS);
-    lc.dynamicSmemBytes = A6_SMEM;
+    lc.dynamicSmemBytes = A6_SMEM + (rel_tbl != nullptr ? heads * ATT_REL_W * 4 : 0);
     lc.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // see pdl_wait() in ptx.cuh
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = attr;
     lc.numAttrs = 1;
-    LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc64_kernel, tmQ, tmKV, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
-                                scale_log2e));
+    if (rel_tbl != nullptr)
+        LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc64_kernel<true>, tmQ, tmKV, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
+                                    scale_log2e, rel_tbl));
+    else
+        LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc64_kernel<false>, tmQ, tmKV, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
+                                    scale_log2e, rel_tbl));
     LSC_CUDA(cudaGetLastError());
     return 1;
 }

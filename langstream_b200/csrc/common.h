@@ -163,9 +163,10 @@ int layernorm_launch(const __nv_bfloat16* in, const float* gamma, const float* b
 // attention tiles built by attention_tiles_launch for the same cu_seqlens (tiles: 2 * n_seq + 2 ints; rowinfo: one
 // word per token row = the key range of the row's own sequence inside its tile).
 // order (optional, ragged batches of the same kernel class): the sequences by descending length.
+// rel_tbl (optional, d_head 64 only): relative-position bias added to the scores (MPNet), see attention_rel_table.
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles = nullptr,
-                     const uint32_t* rowinfo = nullptr, const int32_t* order = nullptr);
+                     const uint32_t* rowinfo = nullptr, const int32_t* order = nullptr, const float* rel_tbl = nullptr);
 // true when attention_launch would take the length-adaptive kernel, which likes an `order` (attention_order_launch)
 bool attention_wants_order(int n_seq, int T, int H, int heads, int max_seqlen);
 int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
@@ -182,8 +183,12 @@ int attention_tiles_max_seqs();
 int attention_tiles_launch(const int32_t* cu_seqlens, int n_seq, int T, int32_t* tiles, uint32_t* rowinfo, cudaStream_t stream);
 // tcgen05 attention for d_head 64 and any sequence length (attention_tc64.cu).
 bool attention_tc64_supported(int H, int heads);
+// rel_tbl (optional): [heads][ATT_REL_W] fp32 relative-position bias from attention_rel_table (MPNet)
+constexpr int ATT_REL_HALF = 191;
+constexpr int ATT_REL_W = 2 * ATT_REL_HALF + 2;  // one pad entry: rows stay 16-byte multiples
+void attention_rel_table(const float* w, int buckets, int max_distance, int heads, std::vector<float>* out);
 int attention_tc64_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
-                          __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
+                          __nv_bfloat16* ctx, int num_sms, cudaStream_t stream, const float* rel_tbl = nullptr);
 // Masked mean-pool over each sequence's tokens + L2 normalisation -> fp32 [n_seq,H].  With `stats`
 // (per-row partial sums, see LnArgs) x holds pre-LayerNorm rows and the final LayerNorm (gamma, beta)
 // is applied on the fly.

@@ -58,6 +58,9 @@ struct lsc_encoder {
     float* d_word = nullptr;
     float* d_pos = nullptr;
     float* d_type = nullptr;
+    float* d_rel = nullptr;      // arch 1: relative-position bias table for the attention kernel (attention_rel_table)
+    const float* d_pos0 = nullptr;  // position row of a sequence's first token (arch 1: row 2 of d_pos)
+    int max_len = 0;             // longest sequence the position table serves
     float* d_emb_g = nullptr;
     float* d_emb_b = nullptr;
     std::vector<LayerW> layers;
@@ -166,8 +169,19 @@ int upload_folded(lsc_encoder* e, const float* W, const float* bias, const float
 int check_config(const lsc_encoder_config* c) {
     if (c == nullptr) return fail(LSC_E_INVALID, "encoder config is null");
     if (c->layers <= 0 || c->hidden <= 0 || c->heads <= 0 || c->ffn <= 0 || c->vocab <= 0 ||
-        c->max_position <= 0 || c->type_vocab <= 0)
+        c->max_position <= 0 || c->type_vocab < 0)
         return fail(LSC_E_INVALID, "encoder config: all sizes must be positive");
+    if (c->arch != 0 && c->arch != 1) return fail(LSC_E_UNSUPPORTED, "encoder config: arch must be 0 (BERT) or 1 (MPNet)");
+    if (c->arch == 0 && c->type_vocab <= 0) return fail(LSC_E_INVALID, "encoder config: a BERT model has token-type embeddings");
+    if (c->arch == 1) {
+        if (c->type_vocab != 0) return fail(LSC_E_INVALID, "encoder config: an MPNet model has no token-type embeddings (type_vocab 0)");
+        if (c->max_position <= 2) return fail(LSC_E_INVALID, "encoder config: MPNet position ids start at 2");
+        if (c->hidden / c->heads != 64) return fail(LSC_E_UNSUPPORTED, "encoder config: MPNet needs a head dimension of 64");
+        if (c->rel_buckets < 4 || c->rel_buckets > 256 || c->rel_buckets % 4 != 0 || c->rel_max_distance > 128 ||
+            c->rel_max_distance <= c->rel_buckets / 4)
+            return fail(LSC_E_UNSUPPORTED, "encoder config: relative-position buckets must be a multiple of 4 and saturate within 128 positions");
+        if (c->gemm_impl != 0) return fail(LSC_E_UNSUPPORTED, "encoder config: MPNet runs on the product path only");
+    }
     if (c->hidden % c->heads != 0) return fail(LSC_E_INVALID, "encoder config: hidden % heads != 0");
     const int d = c->hidden / c->heads;
     if (d != 32 && d != 64) return fail(LSC_E_UNSUPPORTED, "encoder config: head dimension must be 32 or 64");
@@ -182,6 +196,7 @@ int check_config(const lsc_encoder_config* c) {
 size_t weights_count(const lsc_encoder_config* c) {
     const size_t H = c->hidden, F = c->ffn;
     size_t n = (static_cast<size_t>(c->vocab) + c->max_position + c->type_vocab) * H + 2 * H;
+    if (c->arch == 1) n += static_cast<size_t>(c->rel_buckets) * c->heads;
     const size_t per_layer = 3 * (H * H + H) + (H * H + H) + 2 * H + (F * H + F) + (H * F + H) + 2 * H;
     return n + per_layer * c->layers;
 }
@@ -321,7 +336,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                               &tc_qkv = am->tc_qkv, &tc_tmp = am->tc_tmp, &tc_x = am->tc_x, &tc_ffn = am->tc_ffn;
             const int P = e->stats_p, PX = e->stats_px;
             const float inv_h = 1.0f / static_cast<float>(H);
-            LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word, e->d_pos,
+            LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, e->max_len, c.vocab, e->d_word, e->d_pos0,
                                           e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, e->stats_x, PX, st));
             for (int l = 0; l < c.layers; ++l) {
                 const LayerW& w = e->layers[l];
@@ -329,7 +344,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                 ln_in.c = w.c_qkv; ln_in.stats_in = e->stats_x; ln_in.p_in = PX; ln_in.inv_h = inv_h; ln_in.eps = c.ln_eps;
                 LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.d_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H,
                                    EPI_LNIN_BIAS, 2 * H, ln_in, st));
-                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order, e->d_rel));
                 LnArgs ln_o;  // tmp = ctx.Wo^T + b + LN_in(x); statistics of tmp -> stats_1
                 ln_o.stats_in = e->stats_x; ln_o.p_in = PX; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
                 ln_o.inv_h = inv_h; ln_o.eps = c.ln_eps;
@@ -355,12 +370,12 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
             // ---- validation path: CUDA-core GEMMs and explicit LayerNorm kernels (unfused) ----
             CUtensorMap none;
             const LnArgs no_ln{};
-            LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, c.max_position, c.vocab, e->d_word, e->d_pos,
+            LSC_LAUNCH(0, embed_ln_launch(d_token_ids, d_cu, n_seq, T, H, e->max_len, c.vocab, e->d_word, e->d_pos0,
                                           e->d_type, e->d_emb_g, e->d_emb_b, c.ln_eps, e->x, nullptr, nullptr, 0, st));
             for (int l = 0; l < c.layers; ++l) {
                 const LayerW& w = e->layers[l];
                 LSC_LAUNCH(1, gemm(e, none, e->x, none, w.w_qkv, w.b_qkv, nullptr, none, e->qkv, T, 3 * H, H, EPI_BIAS, 2 * H, no_ln, st));
-                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order, e->d_rel));
                 LSC_LAUNCH(1, gemm(e, none, e->ctx, none, w.w_o, w.b_o, e->x, none, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, H, no_ln, st));
                 LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
                 LSC_LAUNCH(1, gemm(e, none, e->x1, none, w.w_1, w.b_1, nullptr, none, e->ffn, T, F, H, EPI_BIAS_GELU, F, no_ln, st));
@@ -446,12 +461,27 @@ int lsc_encoder_create(const lsc_encoder_config* cfg, const void* weights, size_
         p += static_cast<size_t>(cfg->vocab) * H;
         LSC_TRY(upload_f32(e, &e->d_pos, p, static_cast<size_t>(cfg->max_position) * H));
         p += static_cast<size_t>(cfg->max_position) * H;
-        LSC_TRY(upload_f32(e, &e->d_type, p, static_cast<size_t>(cfg->type_vocab) * H));
-        p += static_cast<size_t>(cfg->type_vocab) * H;
+        if (cfg->type_vocab > 0) {
+            LSC_TRY(upload_f32(e, &e->d_type, p, static_cast<size_t>(cfg->type_vocab) * H));
+            p += static_cast<size_t>(cfg->type_vocab) * H;
+        } else {  // no token-type embeddings: the embedding kernel adds a zero row
+            const std::vector<float> zeros(H, 0.f);
+            LSC_TRY(upload_f32(e, &e->d_type, zeros.data(), H));
+        }
+        // MPNet numbers positions from padding_idx + 1 = 2 (MPNetEmbeddings: create_position_ids_from_input_ids)
+        const int pos0 = cfg->arch == 1 ? 2 : 0;
+        e->d_pos0 = e->d_pos + static_cast<size_t>(pos0) * H;
+        e->max_len = cfg->max_position - pos0;
         LSC_TRY(upload_f32(e, &e->d_emb_g, p, H));
         p += H;
         LSC_TRY(upload_f32(e, &e->d_emb_b, p, H));
         p += H;
+        if (cfg->arch == 1) {
+            std::vector<float> tbl;
+            attention_rel_table(p, cfg->rel_buckets, cfg->rel_max_distance, cfg->heads, &tbl);
+            LSC_TRY(upload_f32(e, &e->d_rel, tbl.data(), tbl.size()));
+            p += static_cast<size_t>(cfg->rel_buckets) * cfg->heads;
+        }
         e->layers.resize(cfg->layers);
         const float* prev_ln2_g = nullptr;
         const float* prev_ln2_b = nullptr;
@@ -565,7 +595,7 @@ int lsc_encoder_embed_dev(lsc_encoder* e, const int32_t* d_token_ids, const int3
     if (n_seq == 0) return LSC_OK;
     if (d_cu_seqlens == nullptr || d_out == nullptr || (total_tokens > 0 && d_token_ids == nullptr))
         return fail(LSC_E_INVALID, "lsc_encoder_embed_dev: null pointer");
-    if (max_seqlen > e->cfg.max_position)
+    if (max_seqlen > e->max_len)
         return fail(LSC_E_TOO_LONG, "Illegal input, maybe the number of tokens is too high");
     std::lock_guard<std::mutex> lock(e->mu);
     LSC_CUDA(cudaSetDevice(e->device));
@@ -581,7 +611,7 @@ static int validate_batch(const char* who, lsc_encoder* e, const int32_t* token_
     for (int i = 0; i < n_seq; ++i) {
         const int len = cu_seqlens[i + 1] - cu_seqlens[i];
         if (len < 0) return fail(LSC_E_INVALID, std::string(who) + ": cu_seqlens must be non-decreasing");
-        if (len > e->cfg.max_position)
+        if (len > e->max_len)
             return fail(LSC_E_TOO_LONG, "Illegal input, maybe the number of tokens is too high");
     }
     const int64_t total = cu_seqlens[n_seq];

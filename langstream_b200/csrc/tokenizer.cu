@@ -345,6 +345,23 @@ extern "C" int lsc_tokenizer_create(const char* vocab_txt, size_t nbytes, int do
     return LSC_OK;
 }
 
+extern "C" int lsc_tokenizer_set_special(lsc_tokenizer* tk, const char* cls_token, const char* sep_token, const char* unk_token) {
+    if (tk == nullptr) return fail(LSC_E_INVALID, "lsc_tokenizer_set_special: tokenizer is null");
+    int32_t ids[3] = {tk->cls, tk->sep, tk->unk};
+    const char* names[3] = {cls_token, sep_token, unk_token};
+    for (int i = 0; i < 3; ++i) {
+        if (names[i] == nullptr) continue;
+        auto it = tk->vocab.find(names[i]);
+        if (it == tk->vocab.end())
+            return fail(LSC_E_INVALID, std::string("lsc_tokenizer_set_special: the vocabulary has no token ") + names[i]);
+        ids[i] = it->second;
+    }
+    tk->cls = ids[0];
+    tk->sep = ids[1];
+    tk->unk = ids[2];
+    return LSC_OK;
+}
+
 extern "C" void lsc_tokenizer_destroy(lsc_tokenizer* tk) { delete tk; }
 
 extern "C" int32_t lsc_tokenizer_vocab_size(const lsc_tokenizer* tk) {

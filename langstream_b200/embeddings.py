@@ -24,7 +24,7 @@ from typing import Callable, Dict, List, Optional, Sequence
 import numpy as np
 
 from . import _native
-from .weights import EncoderSpec, MINILM_L6, BERT_BASE, random_init
+from .weights import EncoderSpec, MINILM_L6, BERT_BASE, MPNET_BASE, random_init
 
 Tokenizer = Callable[[Sequence[str]], List[List[int]]]
 
@@ -80,7 +80,7 @@ class CudaEmbeddingsService(EmbeddingsService):
                  device: int = 0, max_batch: int = 1024, flush_interval_ms: float = 2.0,
                  encoder_factory=None):
         self.spec = spec
-        self.tokenizer = tokenizer or HashingTokenizer(spec.vocab, spec.max_position)
+        self.tokenizer = tokenizer or HashingTokenizer(spec.vocab, spec.max_len)
         factory = encoder_factory or (lambda: _native.Encoder(spec, weights, device=device))
         self._encoder = factory()
         self._max_batch = int(max_batch)
@@ -194,6 +194,8 @@ KNOWN_ARCHITECTURES: Dict[str, EncoderSpec] = {
     "sentence-transformers/all-MiniLM-L6-v2": MINILM_L6,
     "BAAI/bge-base-en-v1.5": BERT_BASE,
     "bge-base": BERT_BASE,
+    "all-mpnet-base-v2": MPNET_BASE,
+    "sentence-transformers/all-mpnet-base-v2": MPNET_BASE,
 }
 
 
@@ -230,7 +232,9 @@ class CudaServiceProvider:
         if options.get("vocab-file"):
             tokenizer = _native.WordPieceTokenizer.from_file(
                 str(options["vocab-file"]), do_lower_case=bool(options.get("do-lower-case", True)),
-                max_length=spec.max_position, n_threads=int(options.get("tokenizer-threads", 0)))
+                max_length=spec.max_len, n_threads=int(options.get("tokenizer-threads", 0)),
+                # MPNet's tokenizer is the BERT pipeline with the template <s> A </s>
+                cls_token="<s>" if spec.arch == "mpnet" else None, sep_token="</s>" if spec.arch == "mpnet" else None)
             if tokenizer.vocab_size > spec.vocab:
                 raise ValueError(f"vocab-file has {tokenizer.vocab_size} tokens, the model {spec.vocab}")
         svc = CudaEmbeddingsService(

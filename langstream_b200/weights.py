@@ -26,6 +26,20 @@ class EncoderSpec:
     max_position: int = 512
     type_vocab: int = 2
     ln_eps: float = 1e-12
+    # "bert" = HuggingFace BertModel; "mpnet" = MPNetModel (all-mpnet-base-v2): no token-type embeddings, position ids
+    # from 2, relative-position attention bias shared by all layers (include/langstream_cuda.h: lsc_encoder_config.arch)
+    arch: str = "bert"
+    rel_buckets: int = 32
+    rel_max_distance: int = 128
+
+    @property
+    def arch_id(self) -> int:
+        return {"bert": 0, "mpnet": 1}[self.arch]
+
+    @property
+    def max_len(self) -> int:
+        """Longest sequence the position table serves (MPNet spends rows 0 and 1 on padding_idx)."""
+        return self.max_position - (2 if self.arch == "mpnet" else 0)
 
     def to_dict(self) -> dict:
         return asdict(self)
@@ -34,11 +48,17 @@ class EncoderSpec:
 MINILM_L6 = EncoderSpec()  # all-MiniLM-L6-v2 architecture
 BERT_BASE = EncoderSpec(layers=12, hidden=768, heads=12, ffn=3072)  # BGE-base architecture
 TINY = EncoderSpec(layers=2, hidden=128, heads=4, ffn=256, vocab=1000, max_position=64)
+MPNET_BASE = EncoderSpec(layers=12, hidden=768, heads=12, ffn=3072, vocab=30527, max_position=514, type_vocab=0,
+                         ln_eps=1e-5, arch="mpnet")  # all-mpnet-base-v2 architecture
+MPNET_TINY = EncoderSpec(layers=2, hidden=256, heads=4, ffn=512, vocab=1000, max_position=300, type_vocab=0,
+                         ln_eps=1e-5, arch="mpnet")
 
 
 def tensor_order(spec: EncoderSpec) -> List[Tuple[str, Tuple[int, ...]]]:
     """(state_dict key, shape) in blob order."""
     H, F = spec.hidden, spec.ffn
+    if spec.arch == "mpnet":
+        return _tensor_order_mpnet(spec)
     out: List[Tuple[str, Tuple[int, ...]]] = [
         ("embeddings.word_embeddings.weight", (spec.vocab, H)),
         ("embeddings.position_embeddings.weight", (spec.max_position, H)),
@@ -59,6 +79,33 @@ def tensor_order(spec: EncoderSpec) -> List[Tuple[str, Tuple[int, ...]]]:
             (p + "attention.output.dense.bias", (H,)),
             (p + "attention.output.LayerNorm.weight", (H,)),
             (p + "attention.output.LayerNorm.bias", (H,)),
+            (p + "intermediate.dense.weight", (F, H)),
+            (p + "intermediate.dense.bias", (F,)),
+            (p + "output.dense.weight", (H, F)),
+            (p + "output.dense.bias", (H,)),
+            (p + "output.LayerNorm.weight", (H,)),
+            (p + "output.LayerNorm.bias", (H,)),
+        ]
+    return out
+
+
+def _tensor_order_mpnet(spec: EncoderSpec) -> List[Tuple[str, Tuple[int, ...]]]:
+    """MPNetModel state_dict in blob order: the BERT order with the relative-position bias behind the embeddings."""
+    H, F = spec.hidden, spec.ffn
+    out: List[Tuple[str, Tuple[int, ...]]] = [
+        ("embeddings.word_embeddings.weight", (spec.vocab, H)),
+        ("embeddings.position_embeddings.weight", (spec.max_position, H)),
+        ("embeddings.LayerNorm.weight", (H,)),
+        ("embeddings.LayerNorm.bias", (H,)),
+        ("encoder.relative_attention_bias.weight", (spec.rel_buckets, spec.heads)),
+    ]
+    for l in range(spec.layers):
+        p = f"encoder.layer.{l}."
+        for n in ("q", "k", "v", "o"):
+            out += [(p + f"attention.attn.{n}.weight", (H, H)), (p + f"attention.attn.{n}.bias", (H,))]
+        out += [
+            (p + "attention.LayerNorm.weight", (H,)),
+            (p + "attention.LayerNorm.bias", (H,)),
             (p + "intermediate.dense.weight", (F, H)),
             (p + "intermediate.dense.bias", (F,)),
             (p + "output.dense.weight", (H, F)),
@@ -118,7 +165,9 @@ def random_init(spec: EncoderSpec, seed: int = 0, perturb: bool = False) -> np.n
         else:
             a = 0.02 * rng.standard_normal(shape, dtype=np.float32)
             if name == "embeddings.word_embeddings.weight":
-                a[0] = 0.0  # padding_idx row, as nn.Embedding(padding_idx=0) initialises it
+                a[1 if spec.arch == "mpnet" else 0] = 0.0  # padding_idx row, as nn.Embedding(padding_idx=...) initialises it
+            if name == "encoder.relative_attention_bias.weight":
+                a = a * 100.0  # trained tables span several units; 0.02 would hide the bias from a parity test
         state[name] = a.astype(np.float32)
     return pack(spec, state)
 

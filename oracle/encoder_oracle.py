@@ -43,6 +43,9 @@ class HFOracle:
 
         if threads:
             torch.set_num_threads(threads)
+        if spec.arch == "mpnet":
+            self._init_mpnet(spec, blob)
+            return
         cfg = BertConfig(
             vocab_size=spec.vocab, hidden_size=spec.hidden, num_hidden_layers=spec.layers,
             num_attention_heads=spec.heads, intermediate_size=spec.ffn, hidden_act="gelu",
@@ -62,6 +65,34 @@ class HFOracle:
         bad = [m for m in missing if "position_ids" not in m and "token_type_ids" not in m]
         if bad or unexpected:
             raise RuntimeError(f"weight blob does not match BertModel: missing={bad} unexpected={unexpected}")
+
+    def _init_mpnet(self, spec: EncoderSpec, blob: np.ndarray):
+        """transformers.MPNetModel: the graph DJL traces for all-mpnet-base-v2 (relative-position bias from
+        MPNetEncoder.compute_position_bias, position ids from padding_idx + 1)."""
+        import torch
+        from transformers import MPNetConfig, MPNetModel
+
+        cfg = MPNetConfig(
+            vocab_size=spec.vocab, hidden_size=spec.hidden, num_hidden_layers=spec.layers,
+            num_attention_heads=spec.heads, intermediate_size=spec.ffn, hidden_act="gelu",
+            hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0,
+            max_position_embeddings=spec.max_position, layer_norm_eps=spec.ln_eps,
+            relative_attention_num_buckets=spec.rel_buckets, pad_token_id=1,
+        )
+        if spec.rel_max_distance != 128:
+            raise ValueError("MPNetEncoder.relative_position_bucket hard-codes max_distance=128")
+        try:
+            cfg._attn_implementation = "eager"
+        except Exception:  # pragma: no cover
+            pass
+        self.torch = torch
+        self.spec = spec
+        self.model = MPNetModel(cfg, add_pooling_layer=False).eval()
+        state = {k: torch.from_numpy(np.array(v)) for k, v in unpack(spec, blob).items()}
+        missing, unexpected = self.model.load_state_dict(state, strict=False)
+        bad = [m for m in missing if "position_ids" not in m]
+        if bad or unexpected:
+            raise RuntimeError(f"weight blob does not match MPNetModel: missing={bad} unexpected={unexpected}")
 
     def _pool(self, hidden, mask):
         torch = self.torch
@@ -129,10 +160,37 @@ def _layer_norm(x, g, b, eps):
     return (x - mu) / np.sqrt(var + eps) * g + b
 
 
+def _mpnet_bias(w: np.ndarray, s: int, buckets: int, max_distance: int) -> np.ndarray:
+    """[heads, s, s] relative-position bias: bias[h, q, k] = w[bucket(k - q), h]
+    (transformers MPNetEncoder.compute_position_bias / relative_position_bucket: half of the buckets per direction,
+    the first half of those exact distances, the rest logarithmic up to max_distance, evaluated in float32)."""
+    rel = np.arange(s)[None, :] - np.arange(s)[:, None]
+    n = -rel
+    nb = buckets // 2
+    ret = np.where(n < 0, nb, 0)
+    n = np.abs(n)
+    max_exact = nb // 2
+    with np.errstate(divide="ignore"):
+        v = (np.log(n.astype(np.float32) / np.float32(max_exact)) / np.float32(math.log(max_distance / max_exact))
+             * np.float32(nb - max_exact))
+    large = np.minimum(max_exact + np.where(n >= max_exact, v, 0).astype(np.int64), nb - 1)
+    bucket = ret + np.where(n < max_exact, n, large)
+    return np.transpose(w[bucket], (2, 0, 1))
+
+
 def bert_numpy(spec: EncoderSpec, blob: np.ndarray, token_ids: np.ndarray, cu_seqlens: np.ndarray,
                dtype=np.float64) -> np.ndarray:
     """BERT forward + masked mean-pool + L2-normalise, one sequence at a time, in `dtype`."""
     W = {k: v.astype(dtype) for k, v in unpack(spec, blob).items()}
+    mpnet = spec.arch == "mpnet"
+    if mpnet:  # same graph under MPNetModel's names, plus what differs: see _mpnet_bias and the embeddings below
+        ren = {"attention.attn.q.": "attention.self.query.", "attention.attn.k.": "attention.self.key.",
+               "attention.attn.v.": "attention.self.value.", "attention.attn.o.": "attention.output.dense.",
+               "attention.LayerNorm.": "attention.output.LayerNorm."}
+        for k in list(W):
+            for a, b in ren.items():
+                if a in k:
+                    W[k.replace(a, b)] = W.pop(k)
     H, nh = spec.hidden, spec.heads
     d = H // nh
     out = np.zeros((len(cu_seqlens) - 1, H), np.float32)
@@ -141,9 +199,13 @@ def bert_numpy(spec: EncoderSpec, blob: np.ndarray, token_ids: np.ndarray, cu_se
         s = len(ids)
         if s == 0:
             continue
-        x = (W["embeddings.word_embeddings.weight"][ids]
-             + W["embeddings.position_embeddings.weight"][:s]
-             + W["embeddings.token_type_embeddings.weight"][0])
+        if mpnet:  # MPNetEmbeddings: no token types; positions count from padding_idx + 1 = 2
+            x = W["embeddings.word_embeddings.weight"][ids] + W["embeddings.position_embeddings.weight"][2:s + 2]
+            bias = _mpnet_bias(W["encoder.relative_attention_bias.weight"], s, spec.rel_buckets, spec.rel_max_distance)
+        else:
+            x = (W["embeddings.word_embeddings.weight"][ids]
+                 + W["embeddings.position_embeddings.weight"][:s]
+                 + W["embeddings.token_type_embeddings.weight"][0])
         x = _layer_norm(x, W["embeddings.LayerNorm.weight"], W["embeddings.LayerNorm.bias"], spec.ln_eps)
         for l in range(spec.layers):
             p = f"encoder.layer.{l}."
@@ -154,6 +216,8 @@ def bert_numpy(spec: EncoderSpec, blob: np.ndarray, token_ids: np.ndarray, cu_se
             k = k.reshape(s, nh, d).transpose(1, 0, 2)
             v = v.reshape(s, nh, d).transpose(1, 0, 2)
             sc = q @ k.transpose(0, 2, 1) / math.sqrt(d)
+            if mpnet:
+                sc = sc + bias
             sc = sc - sc.max(-1, keepdims=True)
             pr = np.exp(sc)
             pr = pr / pr.sum(-1, keepdims=True)

@@ -37,6 +37,15 @@ def test_version_and_error_channel(native_lib):
     bad = _native.EncoderConfig(6, 384, 5, 1536, 30522, 512, 2, 1e-12, 0)  # 384 % 5 != 0
     assert native_lib.lsc_encoder_weights_nbytes(C.byref(bad)) == 0
     assert "hidden % heads" in _native.last_error()
+    # MPNet (arch 1): no token-type rows, one relative-position table of rel_buckets x heads
+    from langstream_b200 import weights as W
+    m = W.MPNET_BASE
+    mp = _native.EncoderConfig(m.layers, m.hidden, m.heads, m.ffn, m.vocab, m.max_position, 0, m.ln_eps, 0, 1, 32, 128)
+    assert native_lib.lsc_encoder_weights_nbytes(C.byref(mp)) == W.num_params(m) * 4
+    mp_bad = _native.EncoderConfig(m.layers, m.hidden, m.heads, m.ffn, m.vocab, m.max_position, 2, m.ln_eps, 0, 1, 32, 128)
+    assert native_lib.lsc_encoder_weights_nbytes(C.byref(mp_bad)) == 0 and "token-type" in _native.last_error()
+    mp_d32 = _native.EncoderConfig(6, 384, 12, 1536, m.vocab, m.max_position, 0, m.ln_eps, 0, 1, 32, 128)
+    assert native_lib.lsc_encoder_weights_nbytes(C.byref(mp_d32)) == 0 and "head dimension of 64" in _native.last_error()
     h = C.c_void_p()
     rc = native_lib.lsc_index_create(100, 0, 0, C.byref(h))  # dim not a multiple of 64
     assert rc == _native.LSC_E_UNSUPPORTED and "multiple of 64" in _native.last_error()

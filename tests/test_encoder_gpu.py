@@ -379,3 +379,41 @@ def test_short_sequences_take_the_packed_attention_tiles(native_lib, cuda_device
     # rounding of an attention output travels through the remaining layers
     assert np.abs(sub - got[pick]).max() <= 2e-4
     enc.close()
+
+
+@pytest.mark.parametrize("which", ["tiny", "base"])
+def test_mpnet_relative_position_bias(native_lib, cuda_device, which):
+    """MPNet (BASELINE configs[2] names all-mpnet-base-v2): no token types, positions from 2, and the bucketed
+    relative-position bias of MPNetEncoder.compute_position_bias added to the scores inside the d_head 64 attention
+    kernel - against transformers.MPNetModel on the same random-init weights (bias table scaled to trained magnitudes).
+    Lengths cover both directions of every bucket, the saturated range (|distance| >= 128) and several key tiles."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder, NativeError
+    from oracle.encoder_oracle import HFOracle
+
+    if which == "tiny":
+        spec, lens = W.MPNET_TINY, [1, 2, 7, 9, 17, 63, 64, 65, 128, 129, 130, 200, 257, 298, 0, 33]
+    else:
+        spec, lens = W.MPNET_BASE, [512, 384, 100, 17, 300, 129]
+    blob = W.random_init(spec, seed=5, perturb=True)
+    rng = np.random.default_rng(9)
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    ids = rng.integers(4, spec.vocab, size=int(cu[-1])).astype(np.int32)  # never <pad> = 1
+    want = HFOracle(spec, blob).embed_one_by_one(ids, cu)
+    enc = Encoder(spec, blob)
+    got = enc.embed(ids, cu)
+    _report("mpnet_" + which, got, want)
+    _check(got, want)
+    # the bias matters: the same weights with a zero table must NOT pass
+    state = W.unpack(spec, blob.copy())
+    state = {k: np.array(v) for k, v in state.items()}
+    state["encoder.relative_attention_bias.weight"][:] = 0.0
+    enc0 = Encoder(spec, W.pack(spec, state))
+    got0 = enc0.embed(ids, cu)
+    enc0.close()
+    assert np.abs(got0 - want).max() > 2 * MAX_ABS
+    # positions: max_position - 2 tokens fit, one more does not (the reference's "Illegal input" message)
+    too_long = np.concatenate([[0], [spec.max_len + 1]]).astype(np.int32)
+    with pytest.raises(NativeError, match="Illegal input"):
+        enc.embed(np.full(spec.max_len + 1, 5, np.int32), too_long)
+    enc.close()

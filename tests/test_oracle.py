@@ -133,3 +133,19 @@ def test_topk_edge_cases():
     with pytest.raises(AssertionError):
         topk_oracle.assert_topk_matches(np.array([[1]]), np.array([[0.5]], np.float32),
                                         np.array([[0.9, 0.5]], np.float32), 1)
+
+
+def test_mpnet_numpy_restatement_matches_hf():
+    """The NumPy restatement of the MPNet graph (bucketed relative-position bias, positions from 2, no token types)
+    against transformers.MPNetModel on seeded random-init weights; lengths reach the saturated buckets."""
+    from langstream_b200 import weights as W
+    from oracle.encoder_oracle import HFOracle, bert_numpy
+
+    spec = W.MPNET_TINY
+    blob = W.random_init(spec, seed=3, perturb=True)
+    lens = [1, 9, 40, 150, 298]
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    ids = np.random.default_rng(2).integers(4, spec.vocab, size=int(cu[-1])).astype(np.int32)
+    a = HFOracle(spec, blob).embed_one_by_one(ids, cu)
+    b = bert_numpy(spec, blob, ids, cu)
+    assert np.abs(a - b).max() < 5e-6

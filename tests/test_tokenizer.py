@@ -83,6 +83,21 @@ def test_live_against_huggingface(native_lib, vocab_file):
         assert mine(texts) == hf(texts, truncation=True, max_length=48)["input_ids"]
 
 
+def test_mpnet_template_against_huggingface(native_lib, tmp_path):
+    """all-mpnet-base-v2's tokenizer: the BERT pipeline with the template <s> A </s> (MPNetTokenizer)."""
+    transformers = pytest.importorskip("transformers")
+    from langstream_b200._native import NativeError, WordPieceTokenizer
+    bert = [t for t in tc.vocab_text().split("\n") if t]
+    vp = tmp_path / "vocab.txt"
+    vp.write_text("\n".join(["<s>", "<pad>", "</s>", "<unk>"] + bert + ["<mask>"]) + "\n", encoding="utf-8")
+    texts = tc.texts(n_random=1500, seed=5)
+    hf = transformers.MPNetTokenizer(str(vp), do_lower_case=True)
+    mine = WordPieceTokenizer.from_file(str(vp), do_lower_case=True, max_length=64, cls_token="<s>", sep_token="</s>")
+    assert mine(texts) == hf(texts, truncation=True, max_length=64)["input_ids"]
+    with pytest.raises(NativeError, match="no token"):
+        WordPieceTokenizer.from_file(str(vp), cls_token="<bos>")
+
+
 def test_fuzz_random_unicode_against_huggingface(native_lib, tmp_path):
     """Random code points from every plane; the vocabulary is built from the library's own normalised pre-tokens,
     so any difference in cleaning, accent stripping, lower-casing or splitting changes the ids."""
