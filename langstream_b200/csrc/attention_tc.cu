@@ -258,15 +258,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
             const uint32_t use = uses++;
             mbar_wait(bar_sfull + 8 * j, use & 1);
             tc_fence_after();
-            // ---- pass 1 over the score row (TMEM reads are cheap): the row maximum.  Full-length
-            //      sequences (the common case) take the mask-free path. ----
+            // ---- pass 1 over the score row: the row maximum.  Full-length sequences (the common case) take the
+            //      mask-free path.  The TMEM reads are double-buffered: a 32-column read occupies the warp's TMEM port for
+            //      ~64 cycles, longer than the arithmetic on the previous part takes. ----
             const bool full = s >= AT_ROWS;  // warp-uniform
             float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-            for (int part = 0; part < 4; ++part) {
-                uint32_t v[32];
-                tmem_ld_32x32(s_tmem + part * 32, v);
-                tmem_ld_wait();
+            uint32_t va[32], vb[32];
+            auto max_part = [&](const uint32_t (&v)[32], int part) {
                 if (full) {
 #pragma unroll
                     for (int c = 0; c < 32; ++c) m4[c & 3] = fmaxf(m4[c & 3], __uint_as_float(v[c]));
@@ -275,7 +273,20 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
                     for (int c = 0; c < 32; ++c)  // keys past the sequence are other sequences' rows
                         m4[c & 3] = fmaxf(m4[c & 3], (part * 32 + c < s) ? __uint_as_float(v[c]) : -INFINITY);
                 }
-            }
+            };
+            tmem_ld_32x32(s_tmem, va);
+            tmem_ld_wait();
+            tmem_ld_32x32(s_tmem + 32, vb);
+            max_part(va, 0);
+            tmem_ld_wait();
+            tmem_ld_32x32(s_tmem + 64, va);
+            max_part(vb, 1);
+            tmem_ld_wait();
+            tmem_ld_32x32(s_tmem + 96, vb);
+            max_part(va, 2);
+            tmem_ld_wait();
+            tmem_ld_32x32(s_tmem, va);  // first part of pass 2, in flight across the collection below
+            max_part(vb, 3);
             const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
             const float nms = -mx * scale_log2e;
             // the previous item's P.V has finished by now: collect its O; this also guarantees that the
@@ -284,16 +295,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
             // ---- pass 2: P = exp2(S*scale - max*scale) -> fp16 -> K-major SW128 A tile of the P.V MMA:
             //      k block b (64 keys) at b*16 KB, row r at r*128, 16-byte chunk c at (c ^ (r & 7)) * 16 ----
             float s4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-            for (int part = 0; part < 4; ++part) {
-                uint32_t v[32];
-                tmem_ld_32x32(s_tmem + part * 32, v);
-                tmem_ld_wait();
-                if (part == 3) {  // last read of S: the slot's S region may be overwritten
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_sfree + 8 * j);
-                }
+            auto exp_part = [&](const uint32_t (&v)[32], int part) {
 #pragma unroll
                 for (int c8 = 0; c8 < 4; ++c8) {
                     float pe[8];
@@ -311,7 +313,22 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
                                  "r"(pack_f16x2(pe[6], pe[7]))
                                  : "memory");
                 }
-            }
+            };
+            tmem_ld_wait();
+            tmem_ld_32x32(s_tmem + 32, vb);
+            exp_part(va, 0);
+            tmem_ld_wait();
+            tmem_ld_32x32(s_tmem + 64, va);
+            exp_part(vb, 1);
+            tmem_ld_wait();
+            tmem_ld_32x32(s_tmem + 96, vb);
+            exp_part(va, 2);
+            tmem_ld_wait();
+            // last read of S: the slot's S region may be overwritten
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_sfree + 8 * j);
+            exp_part(vb, 3);
             const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
             fence_proxy_async_smem();
             __syncwarp();
