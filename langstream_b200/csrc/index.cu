@@ -136,7 +136,7 @@ int ensure_query_buffers(lsc_index* ix, int B, int k) {
         if (ix->d_done) cudaFree(ix->d_done);
         ix->d_gthr = nullptr;
         ix->d_done = nullptr;
-        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_gthr), 5 * static_cast<size_t>(bpad) * sizeof(int32_t)));
+        LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_gthr), static_cast<size_t>(1 + TKX_MAX_K) * bpad * sizeof(int32_t)));
         LSC_CUDA(cudaMalloc(reinterpret_cast<void**>(&ix->d_done), static_cast<size_t>(bpad / TK_QROWS) * sizeof(unsigned)));
         ix->cap_q = bpad;
         LSC_TRY(make_tmap_bf16_sw128(&ix->tmapQ, ix->d_qbf, static_cast<uint64_t>(bpad), ix->dim, TK_QROWS));
@@ -184,7 +184,7 @@ int search_dev(lsc_index* ix, lsc_exchange* xg, const float* d_queries, int B, i
     LSC_TRY(order_after_previous(ix, st));
     const int qblk = B > TK_QROWS ? 2 * TK_QROWS : TK_QROWS;
     const int bpad = (B + qblk - 1) / qblk * qblk;
-    LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st, ix->d_gthr, 5 * bpad, ix->d_done,
+    LSC_LAUNCH(0, normalize_rows_launch(d_queries, B, bpad, ix->dim, nullptr, ix->d_qbf, st, ix->d_gthr, (1 + TKX_MAX_K) * bpad, ix->d_done,
                                         bpad / TK_QROWS));
     TopkFuse fuse;
     fuse.status = ix->d_status;

@@ -34,11 +34,10 @@ struct __align__(16) TopkRecord {
 // Receive side of one GPU: records [2 (epoch parity)][world (source rank)][xB][xk] and one flag per
 // (parity, source, query) holding the epoch of the records behind it.
 struct TopkFuse {
-    // Thresholds shared by the CTAs of a scan, as ordered-int keys; nullptr = off.  Five arrays of `gstride`
-    // entries (one per query of the batch): [0] the best k-th score any single CTA has reached; [1..4] the
-    // sampling slots (topk_rows.cu: every CTA first looks at one tile without collecting anything and publishes,
-    // per query, a score that 4 of its rows reach, into slot blockIdx % 4 - the minimum over the four slots is
-    // reached by 16 >= k rows of four different CTAs).
+    // Thresholds shared by the CTAs of a scan, as ordered-int keys; nullptr = off.  1 + TKX_MAX_K arrays of `gstride`
+    // entries (one per query of the batch): [0] the best k-th score any single CTA has reached; [1 + c], c < k: the
+    // best score seen anywhere in the grid on a row with row % k == c (topk_rows.cu: the minimum over the k classes
+    // is reached by k distinct rows).
     int32_t* gthr = nullptr;
     int32_t gstride = 0;
     unsigned* done = nullptr;        // arrival counter of THIS launch (zeroed before it); nullptr = no fused tail

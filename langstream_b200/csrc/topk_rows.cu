@@ -129,9 +129,9 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     const uint32_t buf_i = buf_s + 4 * NQ * BUF;
     const uint32_t thrs = buf_i + 4 * NQ * BUF;
     const uint32_t cnt = thrs + 4 * NQ;
-    const uint32_t gthr_s = cnt + 4 * NQ;  // shared-memory copy of the 5 grid-wide threshold arrays (refreshed asynchronously)
-    const uint32_t samp = buf_s;           // sampling pass only: per query, min over the 4 row quadrants of their best score
-    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * NQ * k + 8 * NQ * BUF + 28 * NQ);
+    const uint32_t gthr_s = cnt + 4 * NQ;  // shared-memory copy of the 1 + k grid-wide threshold arrays (refreshed asynchronously)
+    const int n_garr = 1 + k;              // array 0: best local k-th score; arrays 1..k: best score of each row class (row % k)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(after_ring + 8 * NQ * k + 8 * NQ * BUF + (12 + 4 * k) * NQ);
     const uint32_t bar_full = smem_u32(bars);
     const uint32_t bar_empty = bar_full + 8 * TR_MAX_STAGES;
     const uint32_t bar_tfull = bar_empty + 8 * TR_MAX_STAGES;
@@ -174,9 +174,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     for (int i = threadIdx.x; i < NQ; i += TR_THREADS) {
         sts_f32(thrs + 4 * i, -INFINITY);
         sts_s32(cnt + 4 * i, 0);
-        sts_s32(samp + 4 * i, 0x7fffffff);
-#pragma unroll
-        for (int a = 0; a < 5; ++a) sts_s32(gthr_s + 4 * (a * NQ + i), TKX_KEY_NEG_INF);
+        for (int a = 0; a < n_garr; ++a) sts_s32(gthr_s + 4 * (a * NQ + i), TKX_KEY_NEG_INF);
     }
     if (threadIdx.x == 0) sts_s32(again_epoch, -1);
     tc_fence_before();
@@ -187,9 +185,14 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     // a tile = 128 * PAIR corpus rows, one per CTA (pair); this CTA's rows are its rank's half
     const int num_tiles = (n_rows + TR_BM * PAIR - 1) / (TR_BM * PAIR);
     const int tile0 = blockIdx.x / PAIR, tile_step = gridDim.x / PAIR;
+    // Grid-wide thresholds by ROW CLASS.  Array 1 + c of fuse.gthr holds, per query, the best score any CTA has seen
+    // on a row with row % k == c (one atomic max per improving hit).  Rows of different classes are different rows,
+    // so the minimum over the k classes is a score that k distinct rows of the corpus reach: nothing strictly below
+    // it can make the top k.  It sits at about the (k ln k)-th best score of everything the GRID has seen so far -
+    // the best local k-th score (array 0, raised at compactions) is only what ONE CTA's share of the rows gives,
+    // two orders of magnitude further down the distribution on a short scan.
     // Tiles of this CTA (pair): tile0, tile0 + step, ...  With SAMPLING the first tile is visited twice: first
-    // only looked at - every CTA publishes, per query, a score that four of the tile's rows reach, and the
-    // minimum of four such scores from four CTAs is a threshold that 16 >= k rows of the corpus reach - and at
+    // only looked at - every warp publishes the best of its 32 rows per query into that row's class - and at
     // the very end scanned like any other tile.  Without it every CTA starts from -inf and spends its first
     // tiles inserting rows that cannot make the top k (the fixed cost that dominated short scans: 148 CTAs x k
     // candidates per query); with it the first collecting tile already rejects all but a fraction of a percent.
@@ -300,15 +303,22 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                         uint32_t v[32];
                         tmem_ld_32x32(tbase + c * 32, v);
                         tmem_ld_wait();
-                        int32_t best = TKX_KEY_NEG_INF;  // lane j keeps the best score of this warp's 32 rows for query c*32+j
+                        int32_t best = TKX_KEY_NEG_INF;  // lane j keeps the best score of this warp's 32 rows for query c*32+j ...
+                        int best_lane = 0;               // ... and the lane (= row) that holds it
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
                             const int32_t key = row < n_rows ? score_key(__uint_as_float(v[j])) : TKX_KEY_NEG_INF;
                             const int32_t r = __reduce_max_sync(0xffffffffu, key);
-                            if (lane == j) best = r;
+                            const uint32_t who = __ballot_sync(0xffffffffu, key == r);
+                            if (lane == j) {
+                                best = r;
+                                best_lane = __ffs(who) - 1;
+                            }
                         }
-                        if (c * 32 + lane < nq)
-                            asm volatile("red.shared.min.s32 [%0], %1;" ::"r"(samp + 4 * (c * 32 + lane)), "r"(best) : "memory");
+                        if (c * 32 + lane < nq && best > TKX_KEY_NEG_INF) {
+                            const int cls = (row - lane + best_lane) % k;
+                            atomicMax(gthr + (1 + cls) * fuse.gstride + c * 32 + lane, best);
+                        }
                     }
                     tc_fence_before();
                     __syncwarp();
@@ -318,17 +328,20 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
                 if (lane < NQ / TR_SEL_WARPS && myq < nq) {
-                    // four rows of this CTA (one per quadrant) reach `mine` for query myq
-                    const int32_t mine = lds_s32(samp + 4 * myq);
-                    int32_t* const g0 = gthr + myq;
-                    if (mine > TKX_KEY_NEG_INF && mine != 0x7fffffff) atomicMax(g0 + (1 + (blockIdx.x & 3)) * fuse.gstride, mine);
                     // the other CTAs are at the same point: give their values a moment to arrive (bounded), so
                     // that the first collecting tile starts from a real threshold
+                    const int32_t* const g0 = gthr + myq;
                     int32_t t_key = TKX_KEY_NEG_INF;
                     for (int tries = 0; tries < 48 && t_key == TKX_KEY_NEG_INF; ++tries) {
-                        const int32_t s0 = ld_relaxed_gpu_s32(g0 + 1 * fuse.gstride), s1 = ld_relaxed_gpu_s32(g0 + 2 * fuse.gstride),
-                                      s2 = ld_relaxed_gpu_s32(g0 + 3 * fuse.gstride), s3 = ld_relaxed_gpu_s32(g0 + 4 * fuse.gstride);
-                        t_key = max(ld_relaxed_gpu_s32(g0), min(min(s0, s1), min(s2, s3)));
+                        int32_t cv[TKX_MAX_K];  // all loads in flight together: one L2 round trip per try
+#pragma unroll
+                        for (int a = 0; a < TKX_MAX_K; ++a)
+                            cv[a] = a < k ? ld_relaxed_gpu_s32(g0 + (1 + a) * fuse.gstride) : 0x7fffffff;
+                        int32_t lo = ld_relaxed_gpu_s32(g0);
+                        int32_t cl = 0x7fffffff;
+#pragma unroll
+                        for (int a = 0; a < TKX_MAX_K; ++a) cl = min(cl, cv[a]);
+                        t_key = max(lo, cl);
                     }
                     if (t_key > TKX_KEY_NEG_INF) sts_f32(thrs + 4 * myq, key_score(t_key - 1));
                 }
@@ -346,14 +359,18 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
             // compaction phase reads whatever copy has landed.  A register load here costs an L2 round trip per
             // tile on the selection warps' critical path (measured: 2x the scan time at 64 queries); a stale
             // threshold only admits a few more candidates.
-            if (gthr != nullptr && lane < 5 * (NQ / (TR_SEL_WARPS * 4))) {
-                constexpr int LPA = NQ / (TR_SEL_WARPS * 4);  // lanes per array: 16-byte pieces of this warp's slice
-                const int a = lane / LPA;
-                const int i4 = sw * (NQ / TR_SEL_WARPS) + (lane % LPA) * 4;
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n\tcp.async.commit_group;" ::"r"(gthr_s + 4 * (a * NQ + i4)),
-                             "l"(gthr + a * fuse.gstride + i4)
-                             : "memory");
+            if (gthr != nullptr) {
+                constexpr int LPA = NQ / (TR_SEL_WARPS * 4);  // 16-byte pieces of this warp's slice of one array
+                for (int p = lane; p < n_garr * LPA; p += 32) {
+                    const int a = p / LPA;
+                    const int i4 = sw * (NQ / TR_SEL_WARPS) + (p % LPA) * 4;
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(gthr_s + 4 * (a * NQ + i4)),
+                                 "l"(gthr + a * fuse.gstride + i4)
+                                 : "memory");
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
             }
+            const int cls = row % k;  // this lane's row class
             if (scans) {
                 mbar_wait(bar_tfull + 8 * acc, acc_phase);
                 tc_fence_after();
@@ -402,6 +419,14 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                             } else {
                                 full |= 1u << j;
                             }
+                            if (gthr != nullptr) {  // a new best row of its class: tell the grid (and remember having told it)
+                                const int32_t key = score_key(__uint_as_float(sc));
+                                const uint32_t gs = gthr_s + 4 * ((1 + cls) * NQ + q);
+                                if (key > lds_s32(gs)) {
+                                    sts_s32(gs, key);
+                                    atomicMax(gthr + (1 + cls) * fuse.gstride + q, key);
+                                }
+                            }
                         }
                     }
                     pend[cc] = full;
@@ -435,8 +460,13 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                 int32_t gkey = TKX_KEY_NEG_INF;
                 if (gthr != nullptr && lane < NQ / TR_SEL_WARPS && myq < nq) {
                     const uint32_t gp = gthr_s + 4 * myq;
-                    gkey = max(lds_s32(gp), min(min(lds_s32(gp + 4 * NQ), lds_s32(gp + 8 * NQ)),
-                                                min(lds_s32(gp + 12 * NQ), lds_s32(gp + 16 * NQ))));
+                    int32_t cv[TKX_MAX_K];  // independent reads first, then the minimum
+#pragma unroll
+                    for (int a = 0; a < TKX_MAX_K; ++a) cv[a] = a < k ? lds_s32(gp + 4 * (1 + a) * NQ) : 0x7fffffff;
+                    int32_t lo = 0x7fffffff;
+#pragma unroll
+                    for (int a = 0; a < TKX_MAX_K; ++a) lo = min(lo, cv[a]);
+                    gkey = max(lds_s32(gp), lo);
                 }
                 if (gkey > TKX_KEY_NEG_INF) {
                     // k rows score >= key_score(gkey) somewhere in the grid: nothing strictly below it can make the
@@ -502,7 +532,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
 // barriers, alignment slack
 static int rows_fixed_bytes(int dim, int k, int pair) {
     const int nq = TK_QROWS * pair, buf = pair == 2 ? 16 : TR_BUF;
-    return (dim / TR_BK) * TR_QBLK_BYTES + nq * k * 8 + nq * buf * 8 + nq * 28 + 256 + 1024;
+    return (dim / TR_BK) * TR_QBLK_BYTES + nq * k * 8 + nq * buf * 8 + nq * (12 + 4 * k) + 256 + 1024;
 }
 
 int topk_rows_preload_kernels() {
