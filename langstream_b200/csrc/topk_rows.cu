@@ -277,11 +277,15 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
     } else {
         // ===== selection: warp (quadrant, chunk group); lane = corpus row, columns = 32 queries per chunk =====
         const int quad = warp & 3;
-        const int sw = warp - 2;   // selection warp 0..15; it owns the queries q with q % 16 == sw for compaction
+        const int sw = warp - 2;   // selection warp 0..15
         const int cg = sw >> 2;    // chunk group: this warp scans chunks cg * CPW .. cg * CPW + CPW - 1
         const int nchunks = (nq + 31) / 32;
         const bool scans = cg * CPW < nchunks;
-        const int myq = lane * TR_SEL_WARPS + sw;  // lanes 0 .. NQ / 16 - 1: the queries this warp compacts
+        // the queries this warp compacts and whose thresholds it maintains: `per` consecutive ones, lane l owns the l-th
+        // (consecutive words in shared memory: the 1 + k threshold reads per tile are conflict-free)
+        const int per = (nq + TR_SEL_WARPS - 1) / TR_SEL_WARPS;
+        const int myq = sw * per + lane;
+        const bool owner = lane < per && myq < nq;
         int32_t* const gthr = fuse.gthr != nullptr ? fuse.gthr + q_row0 : nullptr;
         const uint32_t lead_tempty = PAIR == 2 ? mapa_u32(bar_tempty, 0) : bar_tempty;
         int acc = 0;
@@ -327,7 +331,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                     }
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
-                if (lane < NQ / TR_SEL_WARPS && myq < nq) {
+                if (owner) {
                     // the other CTAs are at the same point: give their values a moment to arrive (bounded), so
                     // that the first collecting tile starts from a real threshold
                     const int32_t* const g0 = gthr + myq;
@@ -445,12 +449,12 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                 asm volatile("bar.sync 1, %0;" ::"n"(32 * TR_SEL_WARPS) : "memory");
                 // ---- compaction phase: buffers are stable until the second barrier ----
                 const bool again = lds_s32(again_epoch) == epoch;
-                const int n_my = (lane < NQ / TR_SEL_WARPS && myq < nq) ? lds_s32(cnt + 4 * myq) : 0;
+                const int n_my = (owner) ? lds_s32(cnt + 4 * myq) : 0;
                 uint32_t need = __ballot_sync(0xffffffffu, n_my >= TRIG);
                 while (need) {
                     const int l = __ffs(need) - 1;
                     need &= need - 1;
-                    const int q = l * TR_SEL_WARPS + sw;
+                    const int q = sw * per + l;
                     int n = __shfl_sync(0xffffffffu, n_my, l);
                     n = n < BUF ? n : BUF;
                     compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * BUF, buf_i + 4 * q * BUF,
@@ -458,7 +462,7 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
                     if (lane == 0) sts_s32(cnt + 4 * q, 0);
                 }
                 int32_t gkey = TKX_KEY_NEG_INF;
-                if (gthr != nullptr && lane < NQ / TR_SEL_WARPS && myq < nq) {
+                if (gthr != nullptr && owner) {
                     const uint32_t gp = gthr_s + 4 * myq;
                     int32_t cv[TKX_MAX_K];  // independent reads first, then the minimum
 #pragma unroll
@@ -484,12 +488,12 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
         }
         // ---- flush what is left in the buffers, then the CTA's lists are final ----
         {
-            const int n_my = (lane < NQ / TR_SEL_WARPS && myq < nq) ? lds_s32(cnt + 4 * myq) : 0;
+            const int n_my = (owner) ? lds_s32(cnt + 4 * myq) : 0;
             uint32_t need = __ballot_sync(0xffffffffu, n_my > 0);
             while (need) {
                 const int l = __ffs(need) - 1;
                 need &= need - 1;
-                const int q = l * TR_SEL_WARPS + sw;
+                const int q = sw * per + l;
                 int n = __shfl_sync(0xffffffffu, n_my, l);
                 n = n < BUF ? n : BUF;
                 compact_query(lists_s + 4 * q * k, lists_i + 4 * q * k, buf_s + 4 * q * BUF, buf_i + 4 * q * BUF,
