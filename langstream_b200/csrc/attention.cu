@@ -458,7 +458,7 @@ bool attention_wants_order(int n_seq, int T, int H, int heads, int max_seqlen) {
 
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles, const uint32_t* rowinfo,
-                     const int32_t* order, const float* rel_tbl) {
+                     const int32_t* order, const float* rel_tbl, const int32_t* blocks) {
     if (n_seq <= 0 || max_seqlen <= 0) return 0;
     const int d = H / heads;
     if (d * heads != H) return fail(LSC_E_INVALID, "attention: hidden not divisible by heads");
@@ -472,6 +472,8 @@ int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_
         if (dev >= 0 && dev < 64 && sms_cache[dev] == 0)
             LSC_CUDA(cudaDeviceGetAttribute(&sms_cache[dev], cudaDevAttrMultiProcessorCount, dev));
         const int sms = (dev >= 0 && dev < 64) ? sms_cache[dev] : 148;
+        if (blocks != nullptr && attention_wants_order(n_seq, T, H, heads, max_seqlen))  // tiles of 32-row blocks
+            return attention_tc_blocks_launch(qkv, blocks, n_seq, T, H, heads, max_seqlen, ctx, sms, stream);
         if (tiles != nullptr && rowinfo != nullptr)  // short sequences sharing 128-row tiles (attention_tc_packed.cu)
             return attention_tc_packed_launch(qkv, cu_seqlens, n_seq, T, H, heads, max_seqlen, tiles, rowinfo, ctx, sms, stream);
         if (attention_wants_order(n_seq, T, H, heads, max_seqlen))  // some sequence is shorter than its 128-row tile
@@ -514,9 +516,20 @@ extern "C" int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_se
             return trc;
         }
     }
-    // ragged batches: sequences by descending length, as the encoder builds them once per pass (LSC_DEBUG_ATTN_NO_ORDER=1: batch order)
+    // ragged batches: the block tile list, as the encoder builds it once per pass (LSC_ATTN_NO_BLOCKS=1: the older forms)
+    int32_t* blocks = nullptr;
+    if (tiles == nullptr && getenv("LSC_ATTN_NO_BLOCKS") == nullptr && lsc::attention_wants_order(n_seq, total_tokens, hidden, heads, max_seqlen)) {
+        if (cudaMalloc(reinterpret_cast<void**>(&blocks), static_cast<size_t>(lsc::attention_blocks_scratch_ints(n_seq)) * sizeof(int32_t)) != cudaSuccess)
+            return lsc::fail(LSC_E_NOMEM, "lsc_debug_attention_dev: block tile list");
+        const int brc = lsc::attention_blocks_launch(d_cu_seqlens, n_seq, blocks, static_cast<cudaStream_t>(stream));
+        if (brc < 0) {
+            cudaFree(blocks);
+            return brc;
+        }
+    }
+    // ... or the sequences by descending length (LSC_DEBUG_ATTN_NO_ORDER=1: batch order)
     int32_t* order = nullptr;
-    if (tiles == nullptr && getenv("LSC_DEBUG_ATTN_NO_ORDER") == nullptr && lsc::attention_wants_order(n_seq, total_tokens, hidden, heads, max_seqlen)) {
+    if (tiles == nullptr && blocks == nullptr && getenv("LSC_DEBUG_ATTN_NO_ORDER") == nullptr && lsc::attention_wants_order(n_seq, total_tokens, hidden, heads, max_seqlen)) {
         if (cudaMalloc(reinterpret_cast<void**>(&order), static_cast<size_t>(n_seq) * sizeof(int32_t)) != cudaSuccess)
             return lsc::fail(LSC_E_NOMEM, "lsc_debug_attention_dev: order list");
         const int orc = lsc::attention_order_launch(d_cu_seqlens, n_seq, order, static_cast<cudaStream_t>(stream));
@@ -527,11 +540,12 @@ extern "C" int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_se
     }
     int rc = lsc::attention_launch(static_cast<const __nv_bfloat16*>(d_qkv), d_cu_seqlens, n_seq, total_tokens, hidden,
                                    heads, max_seqlen, static_cast<__nv_bfloat16*>(d_ctx), static_cast<cudaStream_t>(stream), tiles, rowinfo,
-                                   order);
-    if (tiles != nullptr || order != nullptr) {
+                                   order, nullptr, blocks);
+    if (tiles != nullptr || order != nullptr || blocks != nullptr) {
         cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
         if (tiles != nullptr) cudaFree(tiles);
         if (order != nullptr) cudaFree(order);
+        if (blocks != nullptr) cudaFree(blocks);
     }
     return rc < 0 ? rc : LSC_OK;
 }

@@ -163,11 +163,15 @@ int layernorm_launch(const __nv_bfloat16* in, const float* gamma, const float* b
 // attention tiles built by attention_tiles_launch for the same cu_seqlens (tiles: 2 * n_seq + 2 ints; rowinfo: one
 // word per token row = the key range of the row's own sequence inside its tile).
 // order (optional, ragged batches of the same kernel class): the sequences by descending length.
+// blocks (optional, ragged batches of that kernel class; takes precedence over tiles / order): the tile list of
+// attention_blocks_launch - tiles of 32-row blocks of sequences from anywhere in the batch.
 // rel_tbl (optional, d_head 64 only): relative-position bias added to the scores (MPNet), see attention_rel_table.
 int attention_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                      int max_seqlen, __nv_bfloat16* ctx, cudaStream_t stream, const int32_t* tiles = nullptr,
-                     const uint32_t* rowinfo = nullptr, const int32_t* order = nullptr, const float* rel_tbl = nullptr);
-// true when attention_launch would take the length-adaptive kernel, which likes an `order` (attention_order_launch)
+                     const uint32_t* rowinfo = nullptr, const int32_t* order = nullptr, const float* rel_tbl = nullptr,
+                     const int32_t* blocks = nullptr);
+// true when attention_launch would take a length-adaptive kernel, which wants `blocks` (attention_blocks_launch) or an
+// `order` (attention_order_launch)
 bool attention_wants_order(int n_seq, int T, int H, int heads, int max_seqlen);
 int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                         int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
@@ -176,6 +180,12 @@ int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int
 int attention_tc_ragged_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, const int32_t* order, int n_seq, int T, int H,
                                int heads, int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
 int attention_order_launch(const int32_t* cu_seqlens, int n_seq, int32_t* order, cudaStream_t stream);
+// the same, third form (attention_tc_blocks.cu): tiles composed of 32-row blocks of sequences from anywhere in the batch;
+// attention_blocks_launch builds the tile list once per pass into `tiles` (attention_blocks_scratch_ints(n_seq) ints)
+int64_t attention_blocks_scratch_ints(int n_seq);
+int attention_blocks_launch(const int32_t* cu_seqlens, int n_seq, int32_t* tiles, cudaStream_t stream);
+int attention_tc_blocks_launch(const __nv_bfloat16* qkv, const int32_t* tiles, int n_seq, int T, int H, int heads,
+                               int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream);
 int attention_tc_packed_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                                int max_seqlen, const int32_t* tiles, const uint32_t* rowinfo, __nv_bfloat16* ctx,
                                int num_sms, cudaStream_t stream);

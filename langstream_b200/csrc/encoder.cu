@@ -277,16 +277,21 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
     const int H = c.hidden, F = c.ffn;
     int64_t nlaunch = 0;
     if (T > 0) LSC_TRY(ensure_workspace(e, T));
-    // Short sequences (fewer than 48 tokens on average) share 128-row attention tiles with a block-diagonal mask
-    // (attention_tc_packed.cu); the tile list is built once per pass and serves every layer.
-    static const bool no_pack = getenv("LSC_ATTN_NO_PACK") != nullptr;  // debug: one attention tile per sequence
-    const bool pack_tiles = !no_pack && T > 0 && H / c.heads == 32 && max_seqlen <= 128 && n_seq > 1 &&
+    // Ragged batches of the MiniLM kernel class (d_head 32, s <= 128, some sequence shorter than its tile) run on
+    // attention tiles composed of 32-row blocks of sequences from anywhere in the batch (attention_tc_blocks.cu); the
+    // tile list is built once per pass and serves every layer.  Debug switches restore the older forms: sequences
+    // shorter than 48 tokens on average packed into tiles of neighbours (attention_tc_packed.cu), everything else one
+    // length-adaptive tile per sequence in descending length (attention_tc_ragged.cu).
+    static const bool no_blocks = getenv("LSC_ATTN_NO_BLOCKS") != nullptr;
+    static const bool no_pack = getenv("LSC_ATTN_NO_PACK") != nullptr;
+    const bool ragged = T > 0 && n_seq > 1 && attention_wants_order(n_seq, T, H, c.heads, max_seqlen);
+    const bool block_tiles = ragged && !no_blocks;
+    const bool pack_tiles = !block_tiles && !no_pack && T > 0 && H / c.heads == 32 && max_seqlen <= 128 && n_seq > 1 &&
                             n_seq <= attention_tiles_max_seqs() &&
                             static_cast<int64_t>(n_seq) * 48 > static_cast<int64_t>(T);
-    // Other ragged batches of that kernel class run the length-adaptive kernel (attention_tc_ragged.cu) over the sequences
-    // in descending length, sorted once per pass into the same scratch buffer.
-    const bool order_seqs = !pack_tiles && T > 0 && n_seq > 1 && attention_wants_order(n_seq, T, H, c.heads, max_seqlen);
-    const int64_t tiles_need = pack_tiles ? 2 * static_cast<int64_t>(n_seq) + 2 + T : (order_seqs ? n_seq : 0);
+    const bool order_seqs = !block_tiles && !pack_tiles && ragged;
+    const int64_t tiles_need = block_tiles ? attention_blocks_scratch_ints(n_seq)
+                               : pack_tiles ? 2 * static_cast<int64_t>(n_seq) + 2 + T : (order_seqs ? n_seq : 0);
     if (tiles_need > e->cap_tiles) {
         LSC_CUDA(cudaDeviceSynchronize());
         if (e->d_tiles) cudaFree(e->d_tiles);
@@ -304,6 +309,11 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
         LSC_LAUNCH(2, attention_tiles_launch(d_cu, n_seq, T, e->d_tiles, ri, st));
         tiles = e->d_tiles;
         rowinfo = ri;
+    }
+    const int32_t* blocks = nullptr;
+    if (block_tiles) {
+        LSC_LAUNCH(2, attention_blocks_launch(d_cu, n_seq, e->d_tiles, st));
+        blocks = e->d_tiles;
     }
     const int32_t* order = nullptr;
     if (order_seqs) {
@@ -344,7 +354,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
                 ln_in.c = w.c_qkv; ln_in.stats_in = e->stats_x; ln_in.p_in = PX; ln_in.inv_h = inv_h; ln_in.eps = c.ln_eps;
                 LSC_LAUNCH(1, gemm(e, tm_x, e->x, w.tm_qkv, w.w_qkv, w.d_qkv, nullptr, tc_qkv, e->qkv, T, 3 * H, H,
                                    EPI_LNIN_BIAS, 2 * H, ln_in, st));
-                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order, e->d_rel));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order, e->d_rel, blocks));
                 LnArgs ln_o;  // tmp = ctx.Wo^T + b + LN_in(x); statistics of tmp -> stats_1
                 ln_o.stats_in = e->stats_x; ln_o.p_in = PX; ln_o.stats_out = e->stats_1; ln_o.gamma = w.in_g; ln_o.beta = w.in_b;
                 ln_o.inv_h = inv_h; ln_o.eps = c.ln_eps;
@@ -375,7 +385,7 @@ int forward(lsc_encoder* e, const int32_t* d_token_ids, const int32_t* d_cu, int
             for (int l = 0; l < c.layers; ++l) {
                 const LayerW& w = e->layers[l];
                 LSC_LAUNCH(1, gemm(e, none, e->x, none, w.w_qkv, w.b_qkv, nullptr, none, e->qkv, T, 3 * H, H, EPI_BIAS, 2 * H, no_ln, st));
-                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order, e->d_rel));
+                LSC_LAUNCH(2, attention_launch(e->qkv, d_cu, n_seq, T, H, c.heads, max_seqlen, e->ctx, st, tiles, rowinfo, order, e->d_rel, blocks));
                 LSC_LAUNCH(1, gemm(e, none, e->ctx, none, w.w_o, w.b_o, e->x, none, e->tmp, T, H, H, EPI_BIAS_RESIDUAL, H, no_ln, st));
                 LSC_LAUNCH(3, layernorm_launch(e->tmp, w.ln1_g, w.ln1_b, c.ln_eps, e->x1, T, H, st));
                 LSC_LAUNCH(1, gemm(e, none, e->x1, none, w.w_1, w.b_1, nullptr, none, e->ffn, T, F, H, EPI_BIAS_GELU, F, no_ln, st));

@@ -93,12 +93,18 @@ def test_packed_tiles_match_fp32_reference(native_lib, cuda_device, lens, monkey
     assert err.mean().item() < 2e-3
 
 
-def test_ragged_kernel_every_length(native_lib, cuda_device):
-    """The length-adaptive kernel (attention_tc_ragged.cu): every length 1..128 several times, in random order, empty
-    sequences between them, many more items than SMs x groups - so that short items follow long ones in the same
-    shared-memory stage and TMEM slot (stale rows behind the loaded part must never reach a stored row)."""
+@pytest.mark.parametrize("form", ["blocks", "one_tile_per_sequence"])
+def test_ragged_kernel_every_length(native_lib, cuda_device, form, monkeypatch):
+    """The length-adaptive kernels - tiles of 32-row blocks of sequences from anywhere in the batch
+    (attention_tc_blocks.cu, the product path) and one adaptive tile per sequence (attention_tc_ragged.cu): every
+    length 1..128 several times, in random order, empty sequences between them, many more items than SMs x groups -
+    so that short items follow long ones in the same shared-memory stage and TMEM slot (stale rows behind the loaded
+    part must never reach a stored row) and every combination 4 | 3+1 | 2+2 | 2+1+1 | 1+1+1+1 of blocks occurs."""
     import torch
     from langstream_b200 import _native
+
+    if form != "blocks":
+        monkeypatch.setenv("LSC_ATTN_NO_BLOCKS", "1")
 
     H, heads = 384, 12
     rng = np.random.default_rng(11)
