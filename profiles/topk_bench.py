@@ -19,12 +19,15 @@ def child(rows, reps):
     dev = torch.device("cuda:0")
     ix = Index(384, capacity=rows)
     st = torch.cuda.current_stream().cuda_stream
+    id0 = int(os.environ.get("TOPK_ID_OFFSET", "0"))  # a shard's ids do not start at 0
     for o in range(0, rows, 1 << 20):
         m = min(1 << 20, rows - o)
-        v = torch.randn(m, 384, generator=torch.Generator(device=dev).manual_seed(42 + o), device=dev)
-        ix.upsert_dev(np.arange(o, o + m, dtype=np.int64), v, m, st)
+        v = torch.randn(m, 384, generator=torch.Generator(device=dev).manual_seed(42 + o + id0), device=dev)
+        ix.upsert_dev(np.arange(id0 + o, id0 + o + m, dtype=np.int64), v, m, st)
+    if os.environ.get("TOPK_RESERVE"):
+        ix.reserve(int(os.environ["TOPK_RESERVE"]), 10)
     out = {}
-    for B in (1, 16, 64, 128, 256, 1024):
+    for B in [int(x) for x in os.environ.get("TOPK_BATCHES", "1,16,64,128,256,1024").split(",")]:
         q = torch.randn(B, 384, generator=torch.Generator(device=dev).manual_seed(43), device=dev)
         ids = torch.empty(B, 10, dtype=torch.int64, device=dev)
         sc = torch.empty(B, 10, dtype=torch.float32, device=dev)
@@ -47,8 +50,8 @@ if __name__ == "__main__":
         sys.exit(0)
     rows = sys.argv[1] if len(sys.argv) > 1 else "10000000"
     reps = sys.argv[2] if len(sys.argv) > 2 else "10"
-    for unfused in (False, True):
-        for no_thr in (False, True):
+    for unfused in ((False,) if os.environ.get("TOPK_ONE") else (False, True)):
+        for no_thr in ((False,) if os.environ.get("TOPK_ONE") else (False, True)):
             env = dict(os.environ, TOPK_BENCH_CHILD="1")
             if unfused:
                 env["LSC_TOPK_UNFUSED"] = "1"
