@@ -363,7 +363,8 @@ topk_scan_rows_kernel(const __grid_constant__ CUtensorMap tmapQ, const __grid_co
             // compaction phase reads whatever copy has landed.  A register load here costs an L2 round trip per
             // tile on the selection warps' critical path (measured: 2x the scan time at 64 queries); a stale
             // threshold only admits a few more candidates.
-            if (gthr != nullptr) {
+            // (every tile while the thresholds still move fast, every fourth one afterwards)
+            if (gthr != nullptr && (it < 8 || (it & 3) == 0)) {
                 constexpr int LPA = NQ / (TR_SEL_WARPS * 4);  // 16-byte pieces of this warp's slice of one array
                 for (int p = lane; p < n_garr * LPA; p += 32) {
                     const int a = p / LPA;
