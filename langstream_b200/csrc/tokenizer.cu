@@ -41,8 +41,23 @@ uint8_t uni_flags(uint32_t cp) {
 // The classes below are what the library's BertNormalizer / BertPreTokenizer do with each code point, as
 // probed by tools/gen_unicode_tables.py (F_SPACE: mapped to a blank / split on; F_OTHER: removed by clean_text;
 // F_CJK: padded with blanks; F_PUNCT: isolated; F_MN: dropped by strip_accents).
-bool is_white_space(uint32_t c) {
-    if (c < 0x80) return c == ' ' || (c >= 0x09 && c <= 0x0D);
+// ASCII classes as a table: bit 0 white space, bit 1 punctuation, bit 2 removed by clean_text (the comparisons
+// below, evaluated once)
+struct AsciiClass {
+    uint8_t t[128];
+    constexpr AsciiClass() : t() {
+        for (int c = 0; c < 128; ++c) {
+            const bool ws = c == ' ' || (c >= 0x09 && c <= 0x0D);
+            const bool pu = (c >= 33 && c <= 47) || (c >= 58 && c <= 64) || (c >= 91 && c <= 96) || (c >= 123 && c <= 126);
+            const bool rm = c < 0x20 ? !(c == '\t' || c == '\n' || c == '\r') : c == 0x7F;  // clean_text removes these ...
+            t[c] = static_cast<uint8_t>((ws && !rm ? 1 : 0) | (pu ? 2 : 0) | (rm ? 4 : 0));  // ... before blanks are looked at
+        }
+    }
+};
+constexpr AsciiClass kAscii;
+
+inline bool is_white_space(uint32_t c) {
+    if (c < 0x80) return (kAscii.t[c] & 1) != 0;
     return (uni_flags(c) & F_SPACE) != 0;
 }
 bool bert_is_removed(uint32_t c) {
@@ -50,8 +65,8 @@ bool bert_is_removed(uint32_t c) {
     return (uni_flags(c) & F_OTHER) != 0;
 }
 bool is_chinese_char(uint32_t c) { return c >= 0x2E80 && (uni_flags(c) & F_CJK) != 0; }
-bool bert_is_punctuation(uint32_t c) {
-    if (c < 0x80) return (c >= 33 && c <= 47) || (c >= 58 && c <= 64) || (c >= 91 && c <= 96) || (c >= 123 && c <= 126);
+inline bool bert_is_punctuation(uint32_t c) {
+    if (c < 0x80) return (kAscii.t[c] & 2) != 0;
     return (uni_flags(c) & F_PUNCT) != 0;
 }
 
@@ -177,8 +192,66 @@ void utf8_append(uint32_t cp, std::string& s) {
 
 using namespace lsc;
 
+namespace lsc {
+namespace {
+
+// Vocabulary lookup for WordPiece's greedy longest match: an open-addressing table keyed by a POLYNOMIAL hash of the
+// token's bytes, so that the hash of any substring of a word comes from the word's prefix hashes in O(1)
+// (h[s, e) = ph[e] - ph[s] * B^(e - s) mod 2^64) and trying "the longest piece that is in the vocabulary" costs one
+// probe per candidate length - no std::string built, no bytes re-hashed.  (An unordered_map<std::string> did both
+// per candidate: 270 ns per token, which at 8 GPUs made the tokenizer the slowest stage of the text pipeline.)
+constexpr uint64_t kHashBase = 0x9E3779B97F4A7C15ull | 1ull;
+struct PieceTable {
+    struct Entry { uint64_t hash; uint32_t off, len; int32_t id; };
+    std::vector<Entry> slots;   // id < 0: empty
+    std::string arena;
+    uint64_t mask = 0;
+    static uint64_t hash_bytes(const char* p, size_t n) {
+        uint64_t h = 0;
+        for (size_t i = 0; i < n; ++i) h = h * kHashBase + (static_cast<unsigned char>(p[i]) + 1u);
+        return h;
+    }
+    static uint64_t mix(uint64_t h) {
+        h ^= h >> 32;
+        h *= 0xD6E8FEB86659FD93ull;
+        return h ^ (h >> 29);
+    }
+    void reserve(size_t n) {
+        size_t cap = 16;
+        while (cap < 2 * n + 2) cap <<= 1;
+        slots.assign(cap, Entry{0, 0, 0, -1});
+        mask = cap - 1;
+    }
+    void insert(const char* p, size_t n, int32_t id) {  // a repeated token keeps its first id
+        const uint64_t h = hash_bytes(p, n);
+        for (uint64_t i = mix(h) & mask;; i = (i + 1) & mask) {
+            Entry& e = slots[i];
+            if (e.id < 0) {
+                e = Entry{h, static_cast<uint32_t>(arena.size()), static_cast<uint32_t>(n), id};
+                arena.append(p, n);
+                return;
+            }
+            if (e.hash == h && e.len == n && memcmp(arena.data() + e.off, p, n) == 0) return;
+        }
+    }
+    int32_t find(uint64_t h, const char* p, size_t n) const {
+        for (uint64_t i = mix(h) & mask;; i = (i + 1) & mask) {
+            const Entry& e = slots[i];
+            if (e.id < 0) return -1;
+            if (e.hash == h && e.len == n && memcmp(arena.data() + e.off, p, n) == 0) return e.id;
+        }
+    }
+    int32_t find(const char* p, size_t n) const { return find(hash_bytes(p, n), p, n); }
+};
+
+}  // namespace
+}  // namespace lsc
+
 struct lsc_tokenizer {
-    std::unordered_map<std::string, int32_t> vocab;
+    lsc::PieceTable first;  // every token: pieces at the start of a word
+    lsc::PieceTable cont;   // the "##..." tokens without their prefix: pieces inside a word
+    std::vector<uint64_t> pw;  // kHashBase^i
+    int32_t n_vocab = 0;
     bool lowercase = true;
     int max_length = 512;
     int n_threads = 1;
@@ -192,12 +265,14 @@ constexpr size_t kMaxCharsPerWord = 100;  // WordPiece max_input_chars_per_word
 
 struct Scratch {
     std::vector<uint32_t> a, b;
-    std::string piece;
     std::vector<uint32_t> byte_off;
+    std::vector<uint64_t> ph;  // prefix hashes of the word's bytes
     std::string word;
 };
 
 // WordPiece on one pre-token (code points [w0, w1) of cps); appends ids to out
+void wordpiece_bytes(const lsc_tokenizer* tk, size_t nchar, Scratch& sc, std::vector<int32_t>& out);
+
 void wordpiece(const lsc_tokenizer* tk, const std::vector<uint32_t>& cps, size_t w0, size_t w1, Scratch& sc,
                std::vector<int32_t>& out) {
     const size_t nchar = w1 - w0;
@@ -207,26 +282,33 @@ void wordpiece(const lsc_tokenizer* tk, const std::vector<uint32_t>& cps, size_t
     }
     // UTF-8 of the word and the byte offset of every character
     sc.word.clear();
-    sc.byte_off.clear();
+    sc.byte_off.resize(nchar + 1);
     for (size_t i = w0; i < w1; ++i) {
-        sc.byte_off.push_back(static_cast<uint32_t>(sc.word.size()));
-        utf8_append(cps[i], sc.word);
+        sc.byte_off[i - w0] = static_cast<uint32_t>(sc.word.size());
+        if (cps[i] < 0x80) sc.word.push_back(static_cast<char>(cps[i])); else utf8_append(cps[i], sc.word);
     }
-    sc.byte_off.push_back(static_cast<uint32_t>(sc.word.size()));
+    sc.byte_off[nchar] = static_cast<uint32_t>(sc.word.size());
+    wordpiece_bytes(tk, nchar, sc, out);
+}
+
+// the greedy longest match proper: the word is sc.word (UTF-8), character c starts at byte sc.byte_off[c]
+void wordpiece_bytes(const lsc_tokenizer* tk, size_t nchar, Scratch& sc, std::vector<int32_t>& out) {
+    const size_t nbytes = sc.word.size();
+    sc.ph.resize(nbytes + 1);
+    sc.ph[0] = 0;
+    for (size_t i = 0; i < nbytes; ++i) sc.ph[i + 1] = sc.ph[i] * kHashBase + (static_cast<unsigned char>(sc.word[i]) + 1u);
+    const uint64_t* pw = tk->pw.data();
     const size_t first = out.size();
     size_t start = 0;
     while (start < nchar) {
         size_t end = nchar;
         int32_t id = -1;
+        const PieceTable& tab = start > 0 ? tk->cont : tk->first;  // inside a word the piece is looked up as "##" + piece
+        const uint32_t b0 = sc.byte_off[start];
         while (start < end) {
-            sc.piece.clear();
-            if (start > 0) sc.piece.append("##");
-            sc.piece.append(sc.word, sc.byte_off[start], sc.byte_off[end] - sc.byte_off[start]);
-            auto it = tk->vocab.find(sc.piece);
-            if (it != tk->vocab.end()) {
-                id = it->second;
-                break;
-            }
+            const uint32_t b1 = sc.byte_off[end];
+            id = tab.find(sc.ph[b1] - sc.ph[b0] * pw[b1 - b0], sc.word.data() + b0, b1 - b0);
+            if (id >= 0) break;
             --end;
         }
         if (id < 0) {  // the whole word becomes [UNK]
@@ -244,10 +326,57 @@ void encode_one(const lsc_tokenizer* tk, const char* text, size_t nbytes, Scratc
     out.push_back(tk->cls);
     std::vector<uint32_t>& a = sc.a;
     std::vector<uint32_t>& b = sc.b;
+    bool ascii_text = true;
+    for (size_t i = 0; i < nbytes; ++i)
+        if (static_cast<unsigned char>(text[i]) >= 0x80) {
+            ascii_text = false;
+            break;
+        }
+    if (ascii_text) {
+        // plain ASCII (the common case): clean_text, lower-casing, the pre-tokenizer and WordPiece straight over the bytes -
+        // no code point vectors, no accents, no CJK.  Classes: blank (incl. tab / LF / CR), punctuation, removed (the other
+        // control characters: they vanish without splitting a word), everything else.
+        const bool lower = tk->lowercase;
+        const size_t limit = static_cast<size_t>(tk->max_length > 2 ? tk->max_length - 1 : 1);  // [CLS] + body
+        const unsigned char* p = reinterpret_cast<const unsigned char*>(text);
+        size_t i = 0;
+        while (i < nbytes && out.size() < limit) {
+            const unsigned char c = p[i];
+            const uint8_t k = kAscii.t[c];
+            if (k & 5) {  // blank or removed
+                ++i;
+                continue;
+            }
+            sc.word.clear();
+            if (k & 2) {
+                sc.word.push_back(static_cast<char>(c));
+                ++i;
+            } else {
+                while (i < nbytes) {
+                    const unsigned char d = p[i];
+                    const uint8_t kd = kAscii.t[d];
+                    if (kd & 3) break;
+                    if (!(kd & 4)) sc.word.push_back(static_cast<char>((lower && d >= 'A' && d <= 'Z') ? d + 32 : d));
+                    ++i;
+                }
+            }
+            const size_t nchar = sc.word.size();
+            if (nchar > kMaxCharsPerWord) {
+                out.push_back(tk->unk);
+                continue;
+            }
+            sc.byte_off.resize(nchar + 1);
+            for (size_t c2 = 0; c2 <= nchar; ++c2) sc.byte_off[c2] = static_cast<uint32_t>(c2);
+            wordpiece_bytes(tk, nchar, sc, out);
+        }
+        if (out.size() > limit) out.resize(limit);
+        out.push_back(tk->sep);
+        return;
+    }
+    b.clear();
+    b.reserve(nbytes + 16);
     utf8_decode(text, nbytes, a);
     // clean_text + handle_chinese_chars
-    b.clear();
-    b.reserve(a.size() + 16);
     for (uint32_t c : a) {
         if (bert_is_removed(c)) continue;  // NUL, U+FFFD, control / format / private-use characters
         if (is_white_space(c)) {
@@ -296,7 +425,7 @@ void encode_one(const lsc_tokenizer* tk, const char* text, size_t nbytes, Scratc
             continue;
         }
         size_t j = i + 1;
-        while (j < n && !is_white_space(b[j]) && !bert_is_punctuation(b[j])) ++j;
+        while (j < n && (b[j] < 0x80 ? kAscii.t[b[j]] == 0 : (!is_white_space(b[j]) && !bert_is_punctuation(b[j])))) ++j;
         wordpiece(tk, b, i, j, sc, out);
         i = j;
     }
@@ -326,14 +455,30 @@ extern "C" int lsc_tokenizer_create(const char* vocab_txt, size_t nbytes, int do
         while (eol < nbytes && vocab_txt[eol] != '\n') ++eol;
         size_t end = eol;
         if (end > pos && vocab_txt[end - 1] == '\r') --end;
-        tk->vocab.emplace(std::string(vocab_txt + pos, end - pos), id);  // a repeated token keeps its first id
         ++id;
         pos = eol + 1;
     }
-    auto find = [&](const char* t) {
-        auto it = tk->vocab.find(t);
-        return it == tk->vocab.end() ? -1 : it->second;
-    };
+    tk->n_vocab = id;
+    tk->first.reserve(static_cast<size_t>(id));
+    tk->cont.reserve(static_cast<size_t>(id));
+    id = 0;
+    pos = 0;
+    while (pos < nbytes) {
+        size_t eol = pos;
+        while (eol < nbytes && vocab_txt[eol] != '\n') ++eol;
+        size_t end = eol;
+        if (end > pos && vocab_txt[end - 1] == '\r') --end;
+        const char* t = vocab_txt + pos;
+        const size_t n = end - pos;
+        tk->first.insert(t, n, id);  // a repeated token keeps its first id
+        if (n > 2 && t[0] == '#' && t[1] == '#') tk->cont.insert(t + 2, n - 2, id);
+        ++id;
+        pos = eol + 1;
+    }
+    tk->pw.resize(4 * kMaxCharsPerWord + 2);
+    tk->pw[0] = 1;
+    for (size_t i = 1; i < tk->pw.size(); ++i) tk->pw[i] = tk->pw[i - 1] * kHashBase;
+    auto find = [&](const char* t) { return tk->first.find(t, strlen(t)); };
     tk->unk = find("[UNK]");
     tk->cls = find("[CLS]");
     tk->sep = find("[SEP]");
@@ -351,10 +496,10 @@ extern "C" int lsc_tokenizer_set_special(lsc_tokenizer* tk, const char* cls_toke
     const char* names[3] = {cls_token, sep_token, unk_token};
     for (int i = 0; i < 3; ++i) {
         if (names[i] == nullptr) continue;
-        auto it = tk->vocab.find(names[i]);
-        if (it == tk->vocab.end())
+        const int32_t id = tk->first.find(names[i], strlen(names[i]));
+        if (id < 0)
             return fail(LSC_E_INVALID, std::string("lsc_tokenizer_set_special: the vocabulary has no token ") + names[i]);
-        ids[i] = it->second;
+        ids[i] = id;
     }
     tk->cls = ids[0];
     tk->sep = ids[1];
@@ -365,7 +510,7 @@ extern "C" int lsc_tokenizer_set_special(lsc_tokenizer* tk, const char* cls_toke
 extern "C" void lsc_tokenizer_destroy(lsc_tokenizer* tk) { delete tk; }
 
 extern "C" int32_t lsc_tokenizer_vocab_size(const lsc_tokenizer* tk) {
-    return tk == nullptr ? 0 : static_cast<int32_t>(tk->vocab.size());
+    return tk == nullptr ? 0 : tk->n_vocab;  // ids run from 0 to this - 1 (one per line of vocab.txt)
 }
 
 extern "C" int lsc_tokenizer_encode(lsc_tokenizer* tk, const char* const* texts, const int32_t* text_nbytes,
@@ -375,35 +520,59 @@ extern "C" int lsc_tokenizer_encode(lsc_tokenizer* tk, const char* const* texts,
         return fail(LSC_E_INVALID, "lsc_tokenizer_encode: bad argument");
     cu_seqlens[0] = 0;
     if (n_texts == 0) return LSC_OK;
-    std::vector<std::vector<int32_t>> ids(static_cast<size_t>(n_texts));
+    // Every worker tokenises a contiguous range of texts into ONE buffer of its own (range x max_length ids, allocated
+    // once per call) and notes the lengths; the ranges are then copied to their packed positions.  (A vector per
+    // text, grown by push_back, made the workers queue up inside malloc: 4 threads gave 1.7x.)
     const int workers = std::max(1, std::min(tk->n_threads, n_texts / 16 + 1));
+    const size_t stride = static_cast<size_t>(tk->max_length);
+    std::vector<std::vector<int32_t>> bufs(static_cast<size_t>(workers));
+    auto range_of = [&](int w, int& lo, int& hi) {
+        lo = static_cast<int>(static_cast<int64_t>(n_texts) * w / workers);
+        hi = static_cast<int>(static_cast<int64_t>(n_texts) * (w + 1) / workers);
+    };
     auto work = [&](int w) {
         Scratch sc;
-        for (int i = w; i < n_texts; i += workers) {
+        std::vector<int32_t> one;
+        one.reserve(stride + 8);
+        int lo, hi;
+        range_of(w, lo, hi);
+        std::vector<int32_t>& buf = bufs[static_cast<size_t>(w)];
+        buf.resize(static_cast<size_t>(hi - lo) * stride);
+        size_t at = 0;
+        for (int i = lo; i < hi; ++i) {
             const char* t = texts[i];
             const size_t nb = t == nullptr ? 0 : (text_nbytes != nullptr ? static_cast<size_t>(text_nbytes[i]) : strlen(t));
-            encode_one(tk, t == nullptr ? "" : t, nb, sc, ids[static_cast<size_t>(i)]);
+            encode_one(tk, t == nullptr ? "" : t, nb, sc, one);
+            memcpy(buf.data() + at, one.data(), one.size() * sizeof(int32_t));
+            at += one.size();
+            cu_seqlens[i + 1] = static_cast<int32_t>(one.size());  // the length for now; the prefix sum follows
         }
+        buf.resize(at);
     };
-    if (workers == 1) {
-        work(0);
-    } else {
+    auto run = [&](auto&& fn) {
+        if (workers == 1) {
+            fn(0);
+            return;
+        }
         std::vector<std::thread> pool;
         pool.reserve(static_cast<size_t>(workers) - 1);
-        for (int w = 1; w < workers; ++w) pool.emplace_back(work, w);
-        work(0);
+        for (int w = 1; w < workers; ++w) pool.emplace_back(fn, w);
+        fn(0);
         for (auto& th : pool) th.join();
-    }
+    };
+    run(work);
     int64_t total = 0;
-    for (int i = 0; i < n_texts; ++i) total += static_cast<int64_t>(ids[static_cast<size_t>(i)].size());
-    if (total > capacity)
+    for (const auto& bf : bufs) total += static_cast<int64_t>(bf.size());
+    if (total > capacity) {
+        for (int i = 0; i < n_texts; ++i) cu_seqlens[i + 1] = 0;
         return fail(LSC_E_INVALID, "lsc_tokenizer_encode: token buffer too small (n_texts * max_length always suffices)");
-    int64_t off = 0;
-    for (int i = 0; i < n_texts; ++i) {
-        const auto& v = ids[static_cast<size_t>(i)];
-        memcpy(token_ids + off, v.data(), v.size() * sizeof(int32_t));
-        off += static_cast<int64_t>(v.size());
-        cu_seqlens[i + 1] = static_cast<int32_t>(off);
     }
+    std::vector<int64_t> start(static_cast<size_t>(workers) + 1, 0);
+    for (int w = 0; w < workers; ++w) start[static_cast<size_t>(w) + 1] = start[static_cast<size_t>(w)] + static_cast<int64_t>(bufs[static_cast<size_t>(w)].size());
+    for (int i = 0; i < n_texts; ++i) cu_seqlens[i + 1] += cu_seqlens[i];
+    run([&](int w) {
+        const auto& bf = bufs[static_cast<size_t>(w)];
+        memcpy(token_ids + start[static_cast<size_t>(w)], bf.data(), bf.size() * sizeof(int32_t));
+    });
     return LSC_OK;
 }

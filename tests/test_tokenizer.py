@@ -98,6 +98,23 @@ def test_mpnet_template_against_huggingface(native_lib, tmp_path):
         WordPieceTokenizer.from_file(str(vp), cls_token="<bos>")
 
 
+def test_fuzz_ascii_bytes_against_huggingface(native_lib, vocab_file):
+    """Pure-ASCII texts take a byte-level path of their own: every ASCII byte incl. the control characters (removed
+    without splitting a word), tabs / line ends (blanks), punctuation runs, words of more than 100 characters."""
+    transformers = pytest.importorskip("transformers")
+    from langstream_b200._native import WordPieceTokenizer
+    rng = random.Random(3)
+    alphabet = [chr(c) for c in range(1, 128)] + list("  \t\n\r aeiou the of and THE Of") * 3
+    texts = ["".join(rng.choice(alphabet) for _ in range(rng.randint(0, 60))) for _ in range(3000)]
+    texts += ["a" * 101, "a" * 100, "x\x01y\x7fz", "\x0b\x0c", "ab\x00cd", "Hello, World!!", "the" + "\x02" * 5 + "of", ""]
+    for lower in (True, False):
+        hf = transformers.BertTokenizer(vocab_file, do_lower_case=lower)
+        mine = WordPieceTokenizer.from_file(vocab_file, do_lower_case=lower, max_length=32)
+        exp, got = hf(texts, truncation=True, max_length=32)["input_ids"], mine(texts)
+        bad = [i for i in range(len(texts)) if exp[i] != got[i]]
+        assert not bad, (repr(texts[bad[0]]), exp[bad[0]], got[bad[0]])
+
+
 def test_fuzz_random_unicode_against_huggingface(native_lib, tmp_path):
     """Random code points from every plane; the vocabulary is built from the library's own normalised pre-tokens,
     so any difference in cleaning, accent stripping, lower-casing or splitting changes the ids."""
