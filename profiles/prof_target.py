@@ -27,6 +27,12 @@ if what == "encoder":
         enc.embed_dev(d_ids, d_cu, 1024, int(cu[-1]), 128, out, st)
     torch.cuda.synchronize()
     print("encoder ok", float(out.norm(dim=1).mean()))
+    # one ragged pass (UniformInt[16,128]): attention tiles of 32-row blocks
+    ids, cu = W.synthetic_token_ids(1024, 128, seed=1234, min_len=16)
+    d_ids, d_cu = torch.from_numpy(ids).to(dev), torch.from_numpy(cu).to(dev)
+    enc.embed_dev(d_ids, d_cu, 1024, int(cu[-1]), int(np.diff(cu).max()), out, st)
+    torch.cuda.synchronize()
+    print("ragged ok", float(out.norm(dim=1).mean()))
 else:
     n = int(sys.argv[2]) if len(sys.argv) > 2 else 10_000_000
     ix = Index(384, capacity=n)
