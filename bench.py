@@ -513,13 +513,12 @@ def run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_r
     crawler.yaml:62-125 + chatbot.yaml:40-61): n synthetic ~400-character documents (seed 7), split over the ranks ->
     lsc_tokenizer_encode -> lsc_encoder_embed_dev -> lsc_index_upsert_dev (GPU-resident sink, no List<Double> in
     between) ; then 1024 query texts -> tokenise -> embed -> top-20 over all shards (lsc_index_search_sharded_dev)
-    -> MMR re-rank on the device (lsc_rerank_mmr_dev, the query's BM25 term statistics from the host).  Text
+    -> MMR re-rank on the device (lsc_rerank_term_statistics on the host, one lsc_rerank_mmr_batch_dev launch per batch).  Text
     generation is outside the timed regions (it stands in for the topic the documents arrive on)."""
     import queue
     import torch
     import torch.distributed as dist
-    from langstream_b200._native import Exchange, Index, WordPieceTokenizer, lib as _lib, check as _check
-    from langstream_b200.rerank import term_statistics
+    from langstream_b200._native import Exchange, Index, WordPieceTokenizer, rerank_mmr_batch_dev, rerank_term_statistics
 
     n_docs = args.pipeline_docs
     lo, hi = n_docs * rank // world, n_docs * (rank + 1) // world
@@ -588,11 +587,9 @@ def run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_r
     n_q, qb, k = 1024, 64, 20
     src_docs = (np.arange(n_q, dtype=np.int64) * 997 + 13) % n_docs
     q_texts = [" ".join(r[:8]) for r in W_obj[pipe_doc_words(src_docs)]]
-    L = _lib()
     d_hit_ids = torch.empty(qb, k, dtype=torch.int64, device=dev)
     d_hit_sc = torch.empty(qb, k, dtype=torch.float32, device=dev)
     d_qe = torch.empty(qb, H, device=dev)
-    d_order = torch.empty(qb, k + 1, dtype=torch.int32, device=dev)   # per query: k picked positions + the count
     self_hits, reranked = 0, 0
 
     def answer(b0):
@@ -616,19 +613,21 @@ def run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_r
         # this rank re-ranks its share of the batch (MMR, lambda 0.5, BM25 k1 1.5 b 0.75 - the chatbot example's values)
         mine = [j for j in range(qb) if (b0 + j) % world == rank]
         hit_texts = texts_of(hit_ids[mine].reshape(-1))
-        tf_rows, len_rows, n_terms = [], [], 8
-        for jj, j in enumerate(mine):
-            tf, dl = term_statistics(hit_texts[jj * k:(jj + 1) * k], texts[j])
-            tf = np.asarray(tf, np.int32).reshape(k, -1)[:, :n_terms]
-            tf_rows.append(np.pad(tf, ((0, 0), (0, n_terms - tf.shape[1]))))
-            len_rows.append(np.asarray(dl, np.int32))
-        d_tf = torch.from_numpy(np.stack(tf_rows)).to(dev)
-        d_len = torch.from_numpy(np.stack(len_rows)).to(dev)
-        for jj, j in enumerate(mine):
-            _check(L.lsc_rerank_mmr_dev(vec[j].data_ptr(), k, H, d_tf[jj].data_ptr(), d_len[jj].data_ptr(), n_terms, 5,
-                                        0.5, 1.5, 0.75, d_order[j].data_ptr(), d_order[j, k:].data_ptr(), stream))
-        order = d_order.cpu().numpy()   # synchronises: the batch's answers are in host memory
-        reranked += sum(int(order[j, k]) == 5 for j in mine)
+        n_terms = 8
+        tf_all = np.zeros((len(mine), k, n_terms), np.int32)
+        len_all = np.zeros((len(mine), k), np.int32)
+        for jj, j in enumerate(mine):  # ReRankAgent.tokenise + term counts, natively (lsc_rerank_term_statistics)
+            tf, dl = rerank_term_statistics(hit_texts[jj * k:(jj + 1) * k], texts[j], n_terms)
+            tf_all[jj, :, :tf.shape[1]] = tf
+            len_all[jj] = dl
+        d_tf = torch.from_numpy(tf_all).to(dev)
+        d_len = torch.from_numpy(len_all).to(dev)
+        d_vm = vec[mine].contiguous()
+        d_om = torch.empty(len(mine), k + 1, dtype=torch.int32, device=dev)   # per query: k picked positions + the count
+        rerank_mmr_batch_dev(d_vm, len(mine), k, H, d_tf, d_len, n_terms, 5, 0.5, 1.5, 0.75, d_om, k + 1, d_om[:, k:], k + 1,
+                             stream)                                  # ONE launch for the rank's share of the batch
+        order_m = d_om.cpu().numpy()   # synchronises: the batch's answers are in host memory
+        reranked += sum(int(order_m[jj, k]) == 5 for jj in range(len(mine)))
 
     answer(0)                                                  # warm-up
     self_hits, reranked = 0, 0
@@ -646,8 +645,8 @@ def run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_r
            "ingest": {"value": n_docs / (ingest_ms / 1000.0), "unit": "documents/s", "seconds": ingest_ms / 1000.0,
                       "stages": "lsc_tokenizer_encode (%d host threads per rank) -> H2D -> lsc_encoder_embed_dev -> lsc_index_upsert_dev" % threads},
            "query": {"value": n_q / (query_ms / 1000.0), "unit": "queries/s", "queries": n_q, "batch": qb, "k": k,
-                     "stages": "tokenise -> embed -> top-20 over all shards -> gather hit vectors -> host BM25 term counts -> "
-                               "lsc_rerank_mmr_dev (5 of 20) -> D2H",
+                     "stages": "tokenise -> embed -> top-20 over all shards -> gather hit vectors -> lsc_rerank_term_statistics (host) -> "
+                               "lsc_rerank_mmr_batch_dev (5 of 20, one launch per batch) -> D2H",
                      "source_document_in_top20": self_hits / n_q, "queries_reranked_to_5": reranked},
            "scope": "native-only e2e: the JVM stages of the reference pipeline (runtime-tester, broker, text-splitter) cannot run "
                     "in this image"}

@@ -415,6 +415,27 @@ int lsc_rerank_mmr_dev(const float* d_doc_vecs, int32_t n_docs, int32_t dim, con
                        const int32_t* d_doc_len, int32_t n_terms, int32_t max_docs, double lambda, double k1,
                        double b, int32_t* d_out_order, int32_t* d_out_count, void* stream);
 
+/* A batch of queries in ONE launch (one CTA per query): query q brings n_docs documents of its own -
+ * d_doc_vecs[n_queries][n_docs][dim], d_term_freq[n_queries][n_docs][n_terms], d_doc_len[n_queries][n_docs] - and
+ * receives d_out_order[q * order_stride .. + count) and d_out_count[q * count_stride].  What a query-vector-db step
+ * that answers a batch of records hands to the re-rank step; same arithmetic as lsc_rerank_mmr_dev per query. */
+int lsc_rerank_mmr_batch_dev(const float* d_doc_vecs, int32_t n_queries, int32_t n_docs, int32_t dim,
+                             const int32_t* d_term_freq, const int32_t* d_doc_len, int32_t n_terms, int32_t max_docs,
+                             double lambda, double k1, double b, int32_t* d_out_order, int32_t order_stride,
+                             int32_t* d_out_count, int32_t count_stride, void* stream);
+
+/*
+ * The text side of the re-rank step, natively (host code): ReRankAgent.tokenise (ReRankAgent.java:314-316, Java's
+ * split("\\s+"): a leading empty token is kept, trailing ones are dropped) on the query and on every document, then per
+ * document its token count (doc_len[n_docs]) and the frequency of every query token (term_freq[n_docs][max_terms],
+ * one column per query token in query order, duplicates included, zero-padded) - exactly the inputs of lsc_rerank_mmr.
+ * *n_terms receives the number of query tokens; more than max_terms is LSC_E_UNSUPPORTED.  doc_nbytes may be NULL
+ * (NUL-terminated texts), query_nbytes < 0 likewise.
+ */
+int lsc_rerank_term_statistics(const char* const* doc_texts, const int32_t* doc_nbytes, int32_t n_docs,
+                               const char* query_text, int32_t query_nbytes, int32_t max_terms, int32_t* term_freq,
+                               int32_t* doc_len, int32_t* n_terms);
+
 /* ---- debug / verification hooks (not part of the product path) --------------------------- */
 
 /*

@@ -91,6 +91,35 @@ JNIEXPORT jint JNICALL Java_ai_langstream_cuda_LangstreamCuda_rerankMmr(
     return count;
 }
 
+JNIEXPORT jint JNICALL Java_ai_langstream_cuda_LangstreamCuda_rerankTermStatistics(
+        JNIEnv* env, jclass c, jobjectArray docs, jstring query, jint max_terms, jobject tf, jobject len) {
+    const jsize n = (*env)->GetArrayLength(env, docs);
+    const char** texts = (const char**)calloc((size_t)(n > 0 ? n : 1), sizeof(char*));
+    jstring* refs = (jstring*)calloc((size_t)(n > 0 ? n : 1), sizeof(jstring));
+    for (jsize i = 0; i < n; ++i) {   /* modified UTF-8: identical to UTF-8 for the white-space split and byte equality of tokens */
+        refs[i] = (jstring)(*env)->GetObjectArrayElement(env, docs, i);
+        texts[i] = refs[i] ? (*env)->GetStringUTFChars(env, refs[i], NULL) : NULL;
+    }
+    const char* q = query ? (*env)->GetStringUTFChars(env, query, NULL) : NULL;
+    int32_t n_terms = 0;
+    int rc = lsc_rerank_term_statistics(texts, NULL, n, q, -1, max_terms, (int32_t*)(*env)->GetDirectBufferAddress(env, tf),
+                                        (int32_t*)(*env)->GetDirectBufferAddress(env, len), &n_terms);
+    if (q) (*env)->ReleaseStringUTFChars(env, query, q);
+    for (jsize i = 0; i < n; ++i)
+        if (refs[i]) (*env)->ReleaseStringUTFChars(env, refs[i], texts[i]);
+    free(refs);
+    free((void*)texts);
+    if (rc != LSC_OK) throw_lsc(env, rc);
+    return n_terms;
+}
+JNIEXPORT void JNICALL Java_ai_langstream_cuda_LangstreamCuda_rerankMmrBatchDev(
+        JNIEnv* env, jclass c, jlong vecs, jint nq, jint n, jint dim, jlong tf, jlong len, jint terms, jint max_docs,
+        jdouble lambda, jdouble k1, jdouble b, jlong order, jint order_stride, jlong count, jint count_stride, jlong stream) {
+    CHECK(lsc_rerank_mmr_batch_dev((const float*)(intptr_t)vecs, nq, n, dim, (const int32_t*)(intptr_t)tf,
+                                   (const int32_t*)(intptr_t)len, terms, max_docs, lambda, k1, b, (int32_t*)(intptr_t)order,
+                                   order_stride, (int32_t*)(intptr_t)count, count_stride, (void*)(intptr_t)stream));
+}
+
 /* ---- asynchronous encoder calls, tokenizer, sharded index (same conventions as above) ---- */
 JNIEXPORT jlong JNICALL Java_ai_langstream_cuda_LangstreamCuda_encoderSubmit(
         JNIEnv* env, jclass c, jlong enc, jobject ids, jobject cu, jint n, jobject out) {

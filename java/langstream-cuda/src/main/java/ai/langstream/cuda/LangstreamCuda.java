@@ -104,4 +104,19 @@ public final class LangstreamCuda {
             java.nio.FloatBuffer docVecs, int nDocs, int dim, java.nio.IntBuffer termFreq,
             java.nio.IntBuffer docLen, int nTerms, int maxDocs, double lambda, double k1, double b,
             java.nio.IntBuffer outOrder);
+
+    /**
+     * lsc_rerank_term_statistics: ReRankAgent.tokenise (split on \\s+) and the term counts natively - fills termFreq
+     * [nDocs][maxTerms] and docLen [nDocs] (direct buffers) and returns the number of query tokens.
+     */
+    public static native int rerankTermStatistics(
+            String[] docTexts, String queryText, int maxTerms, java.nio.IntBuffer termFreq, java.nio.IntBuffer docLen);
+
+    /**
+     * lsc_rerank_mmr_batch_dev: a batch of queries (nDocs documents each, device pointers) re-ranked in one launch;
+     * outOrder / outCount are device addresses with the given strides (in ints).
+     */
+    public static native void rerankMmrBatchDev(
+            long dDocVecs, int nQueries, int nDocs, int dim, long dTermFreq, long dDocLen, int nTerms, int maxDocs,
+            double lambda, double k1, double b, long dOutOrder, int orderStride, long dOutCount, int countStride, long stream);
 }

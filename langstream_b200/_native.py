@@ -105,6 +105,9 @@ SIGNATURES = {
     "lsc_tokenizer_destroy": (None, [_vp]),
     "lsc_rerank_mmr": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp]),
     "lsc_rerank_mmr_dev": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _i32, _i32, C.c_double, C.c_double, C.c_double, _vp, _vp, _vp]),
+    "lsc_rerank_mmr_batch_dev": (C.c_int, [_vp, _i32, _i32, _i32, _vp, _vp, _i32, _i32, C.c_double, C.c_double, C.c_double,
+                                          _vp, _i32, _vp, _i32, _vp]),
+    "lsc_rerank_term_statistics": (C.c_int, [_vp, _vp, _i32, C.c_char_p, _i32, _i32, _vp, _vp, _vp]),
     "lsc_debug_attention_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "lsc_debug_gemm_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
 }
@@ -462,6 +465,31 @@ def rerank_mmr(doc_vecs, term_freq, doc_len, max_docs: int, lam: float, k1: floa
     check(lib().lsc_rerank_mmr(_ptr(doc_vecs), n, dim, _ptr(term_freq), _ptr(doc_len), t, int(max_docs),
                                float(lam), float(k1), float(b), _ptr(order), _ptr(count)))
     return [int(i) for i in order[: int(count[0])]]
+
+
+def rerank_term_statistics(texts, query_text: str, max_terms: int = 64):
+    """lsc_rerank_term_statistics: (term_freq [n, n_terms] int32, doc_len [n] int32) of ReRankAgent.tokenise, natively
+    (no GPU).  The same result as langstream_b200.rerank.term_statistics (the Python restatement)."""
+    raw = [t.encode("utf-8") if isinstance(t, str) else bytes(t) for t in texts]
+    n = len(raw)
+    ptrs = (C.c_char_p * max(n, 1))(*raw)
+    lens = _np.asarray([len(r) for r in raw], _np.int32)
+    tf = _np.zeros((n, max_terms), _np.int32)
+    doc_len = _np.zeros(n, _np.int32)
+    n_terms = _np.zeros(1, _np.int32)
+    q = query_text.encode("utf-8") if isinstance(query_text, str) else bytes(query_text)
+    check(lib().lsc_rerank_term_statistics(C.cast(ptrs, _vp), _ptr(lens) if n else None, n, q, len(q), int(max_terms),
+                                           _ptr(tf) if n else None, _ptr(doc_len) if n else None, _ptr(n_terms)))
+    return tf[:, : int(n_terms[0])].copy(), doc_len
+
+
+def rerank_mmr_batch_dev(d_doc_vecs, n_queries: int, n_docs: int, dim: int, d_term_freq, d_doc_len, n_terms: int,
+                         max_docs: int, lam: float, k1: float, b: float, d_out_order, order_stride: int, d_out_count,
+                         count_stride: int, stream=None) -> None:
+    """lsc_rerank_mmr_batch_dev: one launch for a batch of queries (device pointers / torch tensors)."""
+    check(lib().lsc_rerank_mmr_batch_dev(_ptr(d_doc_vecs), int(n_queries), int(n_docs), int(dim), _ptr(d_term_freq),
+                                         _ptr(d_doc_len), int(n_terms), int(max_docs), float(lam), float(k1), float(b),
+                                         _ptr(d_out_order), int(order_stride), _ptr(d_out_count), int(count_stride), stream))
 
 
 class WordPieceTokenizer:

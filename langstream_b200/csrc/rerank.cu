@@ -17,6 +17,8 @@
 #include <algorithm>
 #include <cstring>
 #include <mutex>
+#include <utility>
+#include <vector>
 
 #include "common.h"
 
@@ -28,9 +30,15 @@ constexpr int RR_MAX_TERMS = 64;
 constexpr int RR_THREADS = 256;
 
 __global__ void __launch_bounds__(RR_THREADS, 1)
-rerank_mmr_kernel(const float* __restrict__ vecs, int n, int dim, const int32_t* __restrict__ tf,
-                  const int32_t* __restrict__ doc_len, int n_terms, int max_docs, double lambda, double k1, double b,
-                  int32_t* __restrict__ out_order, int32_t* __restrict__ out_count) {
+rerank_mmr_kernel(const float* __restrict__ vecs_all, int n, int dim, const int32_t* __restrict__ tf_all,
+                  const int32_t* __restrict__ doc_len_all, int n_terms, int max_docs, double lambda, double k1, double b,
+                  int32_t* __restrict__ out_order_all, int order_stride, int32_t* __restrict__ out_count_all, int count_stride) {
+    // one CTA per query of a batch (blockIdx.x): every query brings its own n documents
+    const float* __restrict__ vecs = vecs_all + static_cast<size_t>(blockIdx.x) * n * dim;
+    const int32_t* __restrict__ tf = tf_all + static_cast<size_t>(blockIdx.x) * n * n_terms;
+    const int32_t* __restrict__ doc_len = doc_len_all + static_cast<size_t>(blockIdx.x) * n;
+    int32_t* __restrict__ out_order = out_order_all + static_cast<size_t>(blockIdx.x) * order_stride;
+    int32_t* __restrict__ out_count = out_count_all + static_cast<size_t>(blockIdx.x) * count_stride;
     extern __shared__ float cosm[];  // [n][n]
     __shared__ float norm[RR_MAX_DOCS];
     __shared__ double score[RR_MAX_DOCS];
@@ -142,7 +150,8 @@ int check_args(int n, int dim, int n_terms, int max_docs) {
 }
 
 int launch(const float* d_vecs, int n, int dim, const int32_t* d_tf, const int32_t* d_len, int n_terms, int max_docs,
-           double lambda, double k1, double b, int32_t* d_order, int32_t* d_count, cudaStream_t st) {
+           double lambda, double k1, double b, int32_t* d_order, int32_t* d_count, cudaStream_t st, int batch = 1,
+           int order_stride = 0, int count_stride = 0) {
     const size_t smem = static_cast<size_t>(n) * n * sizeof(float);
     static bool configured[64] = {};
     int dev = 0;
@@ -152,8 +161,8 @@ int launch(const float* d_vecs, int n, int dim, const int32_t* d_tf, const int32
                                       RR_MAX_DOCS * RR_MAX_DOCS * static_cast<int>(sizeof(float))));
         if (dev >= 0 && dev < 64) configured[dev] = true;
     }
-    rerank_mmr_kernel<<<1, RR_THREADS, smem, st>>>(d_vecs, n, dim, d_tf, d_len, n_terms, max_docs, lambda, k1, b, d_order,
-                                                   d_count);
+    rerank_mmr_kernel<<<batch, RR_THREADS, smem, st>>>(d_vecs, n, dim, d_tf, d_len, n_terms, max_docs, lambda, k1, b, d_order,
+                                                       order_stride, d_count, count_stride);
     LSC_CUDA(cudaGetLastError());
     return LSC_OK;
 }
@@ -182,6 +191,74 @@ extern "C" int lsc_rerank_mmr_dev(const float* d_doc_vecs, int32_t n_docs, int32
         return fail(LSC_E_INVALID, "lsc_rerank_mmr_dev: null input");
     return launch(d_doc_vecs, n_docs, dim, d_term_freq, d_doc_len, n_terms, max_docs, lambda, k1, b, d_out_order,
                   d_out_count, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int lsc_rerank_mmr_batch_dev(const float* d_doc_vecs, int32_t n_queries, int32_t n_docs, int32_t dim,
+                                        const int32_t* d_term_freq, const int32_t* d_doc_len, int32_t n_terms,
+                                        int32_t max_docs, double lambda, double k1, double b, int32_t* d_out_order,
+                                        int32_t order_stride, int32_t* d_out_count, int32_t count_stride, void* stream) {
+    LSC_TRY(check_args(n_docs, dim, n_terms, max_docs));
+    if (n_queries < 0 || n_queries > 65535) return fail(LSC_E_INVALID, "lsc_rerank_mmr_batch_dev: n_queries must be in [0, 65535]");
+    if (n_queries == 0) return LSC_OK;
+    if (order_stride < n_docs || count_stride < 1) return fail(LSC_E_INVALID, "lsc_rerank_mmr_batch_dev: strides too small");
+    if (d_out_order == nullptr || d_out_count == nullptr) return fail(LSC_E_INVALID, "lsc_rerank_mmr_batch_dev: null output");
+    if (n_docs > 0 && (d_doc_vecs == nullptr || d_doc_len == nullptr || (n_terms > 0 && d_term_freq == nullptr)))
+        return fail(LSC_E_INVALID, "lsc_rerank_mmr_batch_dev: null input");
+    return launch(d_doc_vecs, n_docs, dim, d_term_freq, d_doc_len, n_terms, max_docs, lambda, k1, b, d_out_order, d_out_count,
+                  static_cast<cudaStream_t>(stream), n_queries, order_stride, count_stride);
+}
+
+// ReRankAgent.tokenise (ReRankAgent.java:314-316): Java's text.split("\\s+") with \s = [ \t\n\x0B\f\r] - trailing empty
+// strings are dropped, a leading empty string (text starting with white space) is kept, "" gives one empty token,
+// an all-white-space text gives none.
+static void java_split(const char* s, size_t n, std::vector<std::pair<const char*, size_t>>* out) {
+    out->clear();
+    auto ws = [](char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\x0B' || c == '\f' || c == '\r'; };
+    if (n == 0) {
+        out->emplace_back(s, 0);
+        return;
+    }
+    size_t i = 0;
+    if (ws(s[0])) {
+        while (i < n && ws(s[i])) ++i;
+        if (i == n) return;           // nothing but white space: every token is empty and trailing
+        out->emplace_back(s, 0);      // the leading empty token
+    }
+    while (i < n) {
+        const size_t b0 = i;
+        while (i < n && !ws(s[i])) ++i;
+        out->emplace_back(s + b0, i - b0);
+        while (i < n && ws(s[i])) ++i;
+    }
+}
+
+extern "C" int lsc_rerank_term_statistics(const char* const* doc_texts, const int32_t* doc_nbytes, int32_t n_docs,
+                                          const char* query_text, int32_t query_nbytes, int32_t max_terms,
+                                          int32_t* term_freq, int32_t* doc_len, int32_t* n_terms) {
+    if (n_docs < 0 || max_terms < 0 || n_terms == nullptr || (n_docs > 0 && (doc_texts == nullptr || doc_len == nullptr)))
+        return fail(LSC_E_INVALID, "lsc_rerank_term_statistics: bad argument");
+    std::vector<std::pair<const char*, size_t>> q, d;
+    const char* qt = query_text == nullptr ? "" : query_text;
+    java_split(qt, query_text == nullptr ? 0 : (query_nbytes >= 0 ? static_cast<size_t>(query_nbytes) : strlen(qt)), &q);
+    *n_terms = static_cast<int32_t>(q.size());
+    if (static_cast<int64_t>(q.size()) > max_terms)
+        return fail(LSC_E_UNSUPPORTED, "lsc_rerank_term_statistics: the query has more terms than max_terms");
+    if (n_docs > 0 && max_terms > 0 && term_freq == nullptr) return fail(LSC_E_INVALID, "lsc_rerank_term_statistics: term_freq is null");
+    for (int32_t i = 0; i < n_docs; ++i) {
+        const char* t = doc_texts[i] == nullptr ? "" : doc_texts[i];
+        const size_t nb = doc_texts[i] == nullptr ? 0 : (doc_nbytes != nullptr ? static_cast<size_t>(doc_nbytes[i]) : strlen(t));
+        java_split(t, nb, &d);
+        doc_len[i] = static_cast<int32_t>(d.size());
+        int32_t* row = term_freq + static_cast<size_t>(i) * max_terms;
+        for (int32_t j = 0; j < max_terms; ++j) row[j] = 0;
+        // at most 64 query terms against a few hundred document tokens: a plain comparison loop beats building a map
+        for (size_t j = 0; j < q.size(); ++j) {
+            int32_t c = 0;
+            for (const auto& tok : d) c += (tok.second == q[j].second && memcmp(tok.first, q[j].first, tok.second) == 0) ? 1 : 0;
+            row[j] = c;
+        }
+    }
+    return LSC_OK;
 }
 
 extern "C" int lsc_rerank_mmr(const float* doc_vecs, int32_t n_docs, int32_t dim, const int32_t* term_freq,

@@ -30,7 +30,7 @@ MAX_QUERY_TERMS = 64
 def java_split_whitespace(text: str) -> List[str]:
     """Java's `text.split("\\\\s+")` (ReRankAgent.tokenise): trailing empty strings are removed, a leading
     empty string (text starting with whitespace) is kept, "" gives [""], all-whitespace gives []."""
-    parts = re.split(r"\s+", text)
+    parts = re.split(r"[ \t\n\x0b\f\r]+", text)  # Java's \s without UNICODE_CHARACTER_CLASS: these six characters only
     while len(parts) > 1 and parts[-1] == "":
         parts.pop()
     if parts == [""] and text != "":
@@ -147,9 +147,12 @@ class CudaReRankAgent:
             raise ValueError("Arrays must have the same length")  # dotProduct's check (:361-364)
         if len(current) > MAX_DOCS_PER_CALL:
             raise ValueError(f"re-rank: at most {MAX_DOCS_PER_CALL} documents per record")
-        tf, doc_len = term_statistics(texts, query_text)
-        if tf.shape[1] > MAX_QUERY_TERMS:
-            raise ValueError(f"re-rank: at most {MAX_QUERY_TERMS} query terms")
+        try:  # ReRankAgent.tokenise + the term counts, natively (term_statistics above is the Python restatement of it)
+            tf, doc_len = _native.rerank_term_statistics(texts, query_text, MAX_QUERY_TERMS)
+        except _native.NativeError as e:
+            if e.code == _native.LSC_E_UNSUPPORTED:
+                raise ValueError(f"re-rank: at most {MAX_QUERY_TERMS} query terms") from e
+            raise
         order = _native.rerank_mmr(np.stack(vecs), tf, doc_len, self.max, self.mmr_lambda, self.bm25_k1, self.bm25_b)
         return [current[i] for i in order]
 

@@ -19,7 +19,7 @@ from .topk_oracle import cosine_scalar
 def _tokenise(text: str) -> List[str]:
     """ReRankAgent.tokenise (:314-316) = Java's text.split("\\s+"): trailing empty strings are dropped, a
     leading one (text starting with whitespace) is kept, and the empty text gives one empty token."""
-    parts = re.split(r"\s+", text)
+    parts = re.split(r"[ \t\n\x0b\f\r]+", text)  # Java's \s (no UNICODE_CHARACTER_CLASS): exactly these six characters
     while len(parts) > 1 and parts[-1] == "":
         parts.pop()
     if parts == [""] and text != "":  # text of whitespace only: Java returns an empty array

@@ -25,6 +25,29 @@ def test_term_statistics_match_oracle_tokeniser():
     assert tf[:, 1].tolist() == [1, 0, 0, 0] and tf[:, 3].tolist() == [0, 0, 0, 0]
 
 
+def test_native_term_statistics_match_the_python_restatement(native_lib):
+    """lsc_rerank_term_statistics (host code of the C ABI) against the Python restatement of ReRankAgent.tokenise on
+    texts with every white-space shape Java's split("\\s+") distinguishes; U+00A0 and U+2003 are NOT separators."""
+    import random
+    from langstream_b200._native import NativeError, rerank_term_statistics
+    from langstream_b200.rerank import term_statistics
+    import pytest
+
+    rng = random.Random(4)
+    alphabet = ["a", "b", "text", "is", "\u00e9t\u00e9", "x\u00a0y", "\u2003", " ", "  ", "\t", "\n", "\x0b", "\f", "\r"]
+    texts = ["".join(rng.choice(alphabet) for _ in range(rng.randint(0, 12))) for _ in range(200)]
+    texts += ["", "   ", " a", "a ", "a\x0bb", "x\u00a0y x\u00a0y"]
+    for query in ["text is text missing", " a b", "", "x\u00a0y", "\t"]:
+        tf_py, len_py = term_statistics(texts, query)
+        tf_c, len_c = rerank_term_statistics(texts, query)
+        assert len_c.tolist() == len_py.tolist()
+        assert tf_c.shape == tf_py.shape and (tf_c == tf_py).all()
+    with pytest.raises(NativeError, match="more terms"):
+        rerank_term_statistics(["a"], "a b c", max_terms=2)
+    tf0, len0 = rerank_term_statistics([], "a b")
+    assert tf0.shape == (0, 2) and len0.shape == (0,)
+
+
 def test_agent_configuration_defaults():
     import pytest
     from langstream_b200.rerank import CudaReRankAgent

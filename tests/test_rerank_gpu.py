@@ -113,3 +113,32 @@ def test_device_pointer_variant(native_lib, cuda_device):
     assert rc == 0
     torch.cuda.synchronize()
     assert int(d_count.item()) == 10 and d_order[:10].tolist() == expected
+
+
+def test_batch_of_queries_in_one_launch(native_lib, cuda_device):
+    """lsc_rerank_mmr_batch_dev: 37 queries with 20 documents each in one launch pick exactly what 37 single calls pick
+    (term statistics from the native lsc_rerank_term_statistics, padded to a common number of query terms)."""
+    import torch
+    from langstream_b200 import _native
+
+    rng = np.random.default_rng(9)
+    B, n, dim, T = 37, 20, 384, 8
+    V = np.zeros((B, n, dim), np.float32)
+    TF = np.zeros((B, n, T), np.int32)
+    DL = np.zeros((B, n), np.int32)
+    expected = []
+    for q in range(B):
+        texts, vecs, query = _random_case(rng, n, dim, int(rng.integers(1, T + 1)))
+        tf, dl = _native.rerank_term_statistics(texts, query, max_terms=T)
+        V[q], DL[q] = vecs, dl
+        TF[q, :, :tf.shape[1]] = tf   # zero columns = query terms no document contains: idf x 0, no effect on the order
+        expected.append(_native.rerank_mmr(vecs, TF[q], dl, 5, 0.5, 1.5, 0.75))
+    dev = torch.device("cuda:0")
+    d_v, d_tf, d_dl = torch.from_numpy(V).to(dev), torch.from_numpy(TF).to(dev), torch.from_numpy(DL).to(dev)
+    d_out = torch.full((B, n + 1), -7, dtype=torch.int32, device=dev)   # per query: order, then the count
+    _native.rerank_mmr_batch_dev(d_v, B, n, dim, d_tf, d_dl, T, 5, 0.5, 1.5, 0.75, d_out, n + 1, d_out[:, n:], n + 1,
+                                 torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    out = d_out.cpu().numpy()
+    for q in range(B):
+        assert int(out[q, n]) == 5 and out[q, :5].tolist() == expected[q]
