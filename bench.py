@@ -525,14 +525,16 @@ def run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_r
     n_local = hi - lo
     words = [f"w{i}" for i in range(PIPE_VOCAB_WORDS)]
     W_obj = np.array(words, dtype=object)
-    threads = max(1, (os.cpu_count() or 1) // world)
+    # the rank's share of the host cores, less two: the thread that feeds the GPU (and the driver's) must not wait for a core
+    threads = max(1, (os.cpu_count() or 1) // world - (2 if (os.cpu_count() or 1) // world > 4 else 0))
     tok = WordPieceTokenizer("\n".join(["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words) + "\n", max_length=128, n_threads=threads)
 
     def texts_of(doc_ids):
         return [" ".join(r) for r in W_obj[pipe_doc_words(np.asarray(doc_ids, np.int64))]]
 
     batch = 8192
-    doc_texts = [texts_of(np.arange(o, min(o + batch, hi))) for o in range(lo, hi, batch)]  # the "topic"
+    # the "topic": documents arrive as UTF-8 bytes, as they do from a broker
+    doc_texts = [[t.encode("utf-8") for t in texts_of(np.arange(o, min(o + batch, hi)))] for o in range(lo, hi, batch)]
     H = spec.hidden
     E = torch.empty(n_local, H, device=dev)                    # the table's vector column, kept for the re-ranker
     ix = Index(H, capacity=n_local, device=local_rank)
@@ -563,6 +565,10 @@ def run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_r
             qd.put(ingest_once(texts))
         qd.put(None)
 
+    # CPython hands the GIL over every 5 ms by default: the thread that feeds the GPU would wait that long for the
+    # tokeniser thread's Python glue (pointer arrays, copies) every batch, with the GPU idle
+    old_switch = sys.getswitchinterval()
+    sys.setswitchinterval(1e-4)
     th = threading.Thread(target=producer, daemon=True)
     th.start()
     o, tokens = 0, 0
@@ -581,6 +587,7 @@ def run_pipeline(args, world, rank, local_rank, dev, stream, barrier, max_over_r
     torch.cuda.synchronize()
     ingest_ms = max_over_ranks((time.perf_counter() - t0) * 1000.0)
     th.join()
+    sys.setswitchinterval(old_switch)
     del doc_texts
 
     # ---- queries: 1024 texts (the first 8 words of a document each), 64 per batch ----------------------
