@@ -456,6 +456,15 @@ int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_seqlens, int3
                             int32_t total_tokens, int32_t hidden, int32_t heads, int32_t max_seqlen,
                             void* d_ctx, void* stream);
 
+/*
+ * The attention tile list of a ragged batch (debug / verification): runs the kernel that composes 128-row attention
+ * tiles out of 32-row blocks of sequences (csrc/attention_tc_blocks.cu) and leaves in d_out (8 + 9 * n_seq int32)
+ * the tile count at [0] and from [8] one record of 8 ints per tile: the first global row of each of its four blocks
+ * (-1: unused) and, per block, first key block | key blocks << 4 | sequence length << 8 | block within the sequence
+ * << 16 | used blocks << 20.  Lets the tests check the packing on its own.
+ */
+int lsc_debug_attention_blocks_dev(const int32_t* d_cu_seqlens, int32_t n_seq, int32_t* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -549,3 +549,10 @@ extern "C" int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_se
     }
     return rc < 0 ? rc : LSC_OK;
 }
+
+extern "C" int lsc_debug_attention_blocks_dev(const int32_t* d_cu_seqlens, int32_t n_seq, int32_t* d_out, void* stream) {
+    if (d_cu_seqlens == nullptr || d_out == nullptr || n_seq < 0)
+        return lsc::fail(LSC_E_INVALID, "lsc_debug_attention_blocks_dev: bad argument");
+    const int rc = lsc::attention_blocks_launch(d_cu_seqlens, n_seq, d_out, static_cast<cudaStream_t>(stream));
+    return rc < 0 ? rc : LSC_OK;
+}

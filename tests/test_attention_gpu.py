@@ -128,3 +128,52 @@ def test_ragged_kernel_every_length(native_lib, cuda_device, form, monkeypatch):
         err = (got - ref).abs()
         assert bool((err <= 0.02 + 0.01 * ref.abs()).all()), f"max err {err.max().item():.4f}"
         assert err.mean().item() < 4e-3
+
+
+@pytest.mark.parametrize("case", ["uniform", "ones", "mixed_with_empty", "many"])
+def test_block_tile_list(native_lib, cuda_device, case):
+    """The tile list the block-tile attention kernel walks: every non-empty sequence exactly once, its blocks consecutive
+    inside one tile, used blocks a prefix, the per-block fields consistent, and as few tiles as the 4 | 3+1 | 2+2 | 2+1+1 |
+    1+1+1+1 scheme promises."""
+    import torch
+    from langstream_b200 import _native
+
+    rng = np.random.default_rng(3)
+    lens = {"uniform": rng.integers(16, 129, 1024), "ones": rng.integers(1, 33, 777),
+            "mixed_with_empty": np.array([0, 128, 1, 0, 33, 64, 65, 96, 97, 32, 0, 5, 100, 2, 70, 0]),
+            "many": rng.integers(0, 129, 20000)}[case].astype(np.int64)
+    n = len(lens)
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    d_cu = torch.from_numpy(cu).to(cuda_device)
+    d_out = torch.full((8 + 9 * n,), -99, dtype=torch.int32, device=cuda_device)
+    _native.check(_native.lib().lsc_debug_attention_blocks_dev(d_cu.data_ptr(), n, d_out.data_ptr(),
+                                                               torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    out = d_out.cpu().numpy()
+    n_tiles = int(out[0])
+    rec = out[8:8 + 8 * n_tiles].reshape(n_tiles, 8)
+    np_of = (lens + 31) // 32
+    c = [int((np_of == k).sum()) for k in range(5)]
+    m31 = min(c[3], c[1])
+    odd2 = c[2] & 1
+    with_odd = min(2, c[1] - m31) if odd2 else 0
+    assert n_tiles == c[4] + c[3] + c[2] // 2 + odd2 + (c[1] - m31 - with_odd + 3) // 4
+    start_of = {int(cu[i]): i for i in range(n) if lens[i] > 0}
+    seen = set()
+    for t in range(n_tiles):
+        row0, info = rec[t, :4], rec[t, 4:].astype(np.uint32)
+        nb = int((row0 >= 0).sum())
+        assert nb >= 1 and (row0[:nb] >= 0).all() and (row0[nb:] < 0).all()      # used blocks are a prefix
+        assert all(int(x >> 20) & 15 == nb for x in info)
+        b = 0
+        while b < nb:
+            seq = start_of[int(row0[b])]                                         # a sequence starts here
+            s, npq = int(lens[seq]), int(np_of[seq])
+            assert seq not in seen and b + npq <= nb
+            seen.add(seq)
+            for blk in range(npq):
+                x = int(info[b + blk])
+                assert int(row0[b + blk]) == int(cu[seq]) + 32 * blk
+                assert (x & 15, (x >> 4) & 15, (x >> 8) & 255, (x >> 16) & 15) == (b, npq, s, blk)
+            b += npq
+    assert seen == set(start_of.values())
