@@ -18,6 +18,8 @@
 //               exponentials of the current one, so the P.V latency is off its critical path.
 // TMEM: AT_G = 3 slots of 160 columns (S: 128, O: 32), one per softmax group.  mbarrier pipelines: load full/empty, S written / S read,
 // P written, O written / O read.
+#include <cstdlib>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -61,7 +63,7 @@ __device__ __forceinline__ float ex2_fast(float x) {
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_constant__ CUtensorMap tmapCtx,
                     const int32_t* __restrict__ cu_seqlens, int H,
-                    int heads, int n_items, __nv_bfloat16* __restrict__ ctx, float scale_log2e) {
+                    int heads, int n_items, __nv_bfloat16* __restrict__ ctx, float scale_log2e, int uniform_len) {
     extern __shared__ uint8_t smem_raw[];
     // aligned by pointer arithmetic on the shared array (an integer round trip would turn every access
     // through it into a generic-address one)
@@ -107,8 +109,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();  // the QKV GEMM has finished
 
+    // uniform_len > 0: every sequence has that many tokens (the headline shape, 128 each) - nothing to look up
     auto item_len = [&](int item, int& t0) {
         const int seq = item / heads;
+        if (uniform_len > 0) {
+            t0 = seq * uniform_len;
+            return uniform_len;
+        }
         t0 = __ldg(cu_seqlens + seq);
         return __ldg(cu_seqlens + seq + 1) - t0;
     };
@@ -356,6 +363,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
 // qkv: [T, 3H] with Q, K bf16 and V fp16.  Only d_head == 32 and max_seqlen <= 128.
 int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int n_seq, int T, int H, int heads,
                         int max_seqlen, __nv_bfloat16* ctx, int num_sms, cudaStream_t stream) {
+    // sequences of at most max_seqlen tokens that add up to n_seq * max_seqlen all have max_seqlen tokens
+    static const bool no_uniform = getenv("LSC_ATTN_NO_UNIFORM") != nullptr;  // debug: always read cu_seqlens
+    const int uniform_len = (!no_uniform && static_cast<long long>(n_seq) * max_seqlen == T) ? max_seqlen : 0;
     if (n_seq <= 0 || T <= 0) return 0;
     if (H / heads != AT_D || max_seqlen > AT_ROWS) return fail(LSC_E_UNSUPPORTED, "attention_tc: needs d_head 32 and s <= 128");
     CUtensorMap tm, tmc;
@@ -382,7 +392,7 @@ int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int
     lc.attrs = attr;
     lc.numAttrs = 1;
     LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc_kernel, tm, tmc, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
-                                                             scale_log2e));
+                                                             scale_log2e, uniform_len));
     LSC_CUDA(cudaGetLastError());
     return 1;
 }
