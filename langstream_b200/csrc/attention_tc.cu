@@ -60,6 +60,8 @@ __device__ __forceinline__ float ex2_fast(float x) {
     return y;
 }
 
+// UNIFORM: every sequence has exactly AT_ROWS tokens (the headline shape): nothing is looked up, nothing is masked
+template <bool UNIFORM>
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_constant__ CUtensorMap tmapCtx,
                     const int32_t* __restrict__ cu_seqlens, int H,
@@ -112,6 +114,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
     // uniform_len > 0: every sequence has that many tokens (the headline shape, 128 each) - nothing to look up
     auto item_len = [&](int item, int& t0) {
         const int seq = item / heads;
+        if (UNIFORM) {
+            t0 = seq * AT_ROWS;
+            return AT_ROWS;
+        }
         if (uniform_len > 0) {
             t0 = seq * uniform_len;
             return uniform_len;
@@ -215,7 +221,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_ofree + 8 * j);
             const float inv = 1.0f / prev_sum;
-            if (quad * 32 + 32 <= prev_s) {
+            if (UNIFORM || quad * 32 + 32 <= prev_s) {
                 // all 32 rows of this warp belong to the sequence: the 32 x 32 block goes out as ONE TMA store from a
                 // swizzled staging block (per-thread 16-byte stores to rows 768 bytes apart cost a fifth of the kernel:
                 // every store instruction touches 32 different lines)
@@ -268,7 +274,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmapQKV, const __grid_co
             // ---- pass 1 over the score row: the row maximum.  Full-length sequences (the common case) take the
             //      mask-free path.  The TMEM reads are double-buffered: a 32-column read occupies the warp's TMEM port for
             //      ~64 cycles, longer than the arithmetic on the previous part takes. ----
-            const bool full = s >= AT_ROWS;  // warp-uniform
+            const bool full = UNIFORM || s >= AT_ROWS;  // warp-uniform
             float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
             uint32_t va[32], vb[32];
             auto max_part = [&](const uint32_t (&v)[32], int part) {
@@ -375,7 +381,8 @@ int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int
     int dev = 0;
     LSC_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !configured[dev]) {
-        LSC_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        LSC_CUDA(cudaFuncSetAttribute(attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        LSC_CUDA(cudaFuncSetAttribute(attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
         if (dev >= 0 && dev < 64) configured[dev] = true;
     }
     const long long n_items = static_cast<long long>(heads) * n_seq;
@@ -391,8 +398,12 @@ int attention_tc_launch(const __nv_bfloat16* qkv, const int32_t* cu_seqlens, int
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = attr;
     lc.numAttrs = 1;
-    LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc_kernel, tm, tmc, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
-                                                             scale_log2e, uniform_len));
+    if (uniform_len == AT_ROWS)
+        LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc_kernel<true>, tm, tmc, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
+                                    scale_log2e, uniform_len));
+    else
+        LSC_CUDA(cudaLaunchKernelEx(&lc, attention_tc_kernel<false>, tm, tmc, cu_seqlens, H, heads, static_cast<int>(n_items), ctx,
+                                    scale_log2e, uniform_len));
     LSC_CUDA(cudaGetLastError());
     return 1;
 }
