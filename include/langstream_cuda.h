@@ -465,6 +465,13 @@ int lsc_debug_attention_dev(const void* d_qkv, const int32_t* d_cu_seqlens, int3
  */
 int lsc_debug_attention_blocks_dev(const int32_t* d_cu_seqlens, int32_t n_seq, int32_t* d_out, void* stream);
 
+/*
+ * The relative-position bias table an MPNet encoder hands to its attention kernel (debug / verification, host code):
+ * out[heads][384] fp32, entry 191 + r = weight[bucket(r)][h] * log2(e) for r = key position - query position in
+ * [-191, 191] (bucket = transformers' MPNetEncoder.relative_position_bucket), weight = [rel_buckets][heads] fp32.
+ */
+int lsc_debug_mpnet_bias_table(const float* weight, int32_t rel_buckets, int32_t rel_max_distance, int32_t heads, float* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -110,6 +110,7 @@ SIGNATURES = {
     "lsc_rerank_term_statistics": (C.c_int, [_vp, _vp, _i32, C.c_char_p, _i32, _i32, _vp, _vp, _vp]),
     "lsc_debug_attention_dev": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _vp]),
     "lsc_debug_attention_blocks_dev": (C.c_int, [_vp, _i32, _vp, _vp]),
+    "lsc_debug_mpnet_bias_table": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
     "lsc_debug_gemm_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp]),
 }
 

@@ -20,6 +20,8 @@
 
 #include <cstdlib>
 
+#include <cstring>
+
 #include "common.h"
 #include "ptx.cuh"
 
@@ -555,4 +557,15 @@ extern "C" int lsc_debug_attention_blocks_dev(const int32_t* d_cu_seqlens, int32
         return lsc::fail(LSC_E_INVALID, "lsc_debug_attention_blocks_dev: bad argument");
     const int rc = lsc::attention_blocks_launch(d_cu_seqlens, n_seq, d_out, static_cast<cudaStream_t>(stream));
     return rc < 0 ? rc : LSC_OK;
+}
+
+extern "C" int lsc_debug_mpnet_bias_table(const float* weight, int32_t rel_buckets, int32_t rel_max_distance, int32_t heads,
+                                          float* out) {
+    if (weight == nullptr || out == nullptr || heads < 1 || rel_buckets < 4 || rel_buckets % 4 != 0 ||
+        rel_max_distance <= rel_buckets / 4 || rel_max_distance > 128)
+        return lsc::fail(LSC_E_INVALID, "lsc_debug_mpnet_bias_table: bad argument");
+    std::vector<float> tbl;
+    lsc::attention_rel_table(weight, rel_buckets, rel_max_distance, heads, &tbl);
+    memcpy(out, tbl.data(), tbl.size() * sizeof(float));
+    return LSC_OK;
 }

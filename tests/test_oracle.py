@@ -149,3 +149,30 @@ def test_mpnet_numpy_restatement_matches_hf():
     a = HFOracle(spec, blob).embed_one_by_one(ids, cu)
     b = bert_numpy(spec, blob, ids, cu)
     assert np.abs(a - b).max() < 5e-6
+
+
+@pytest.mark.parametrize("buckets,max_distance", [(32, 128), (16, 128), (32, 64), (64, 100)])
+def test_mpnet_bias_table_of_the_native_library(native_lib, buckets, max_distance):
+    """The table lsc_encoder_create builds for an MPNet model (host code, no GPU): for every relative position in
+    [-191, 191] the bucket of transformers' MPNetEncoder.relative_position_bucket (evaluated by torch in float32,
+    including the exact boundaries 16 / 32 / 64), times log2(e); beyond +-max_distance the entries are saturated, which
+    is what lets the attention kernel clamp its first index."""
+    import ctypes as C
+    import torch
+    from transformers.models.mpnet.modeling_mpnet import MPNetEncoder
+    from langstream_b200 import _native
+
+    heads = 12
+    rng = np.random.default_rng(buckets + max_distance)
+    w = rng.standard_normal((buckets, heads)).astype(np.float32)
+    out = np.zeros((heads, 384), np.float32)
+    _native.check(native_lib.lsc_debug_mpnet_bias_table(w.ctypes.data, buckets, max_distance, heads, out.ctypes.data))
+    rel = torch.arange(-191, 192, dtype=torch.long)
+    if max_distance == 128:
+        bucket = MPNetEncoder.relative_position_bucket(rel, num_buckets=buckets).numpy()
+    else:
+        bucket = MPNetEncoder.relative_position_bucket(rel, num_buckets=buckets, max_distance=max_distance).numpy()
+    want = (w[bucket].T * np.float32(1.4426950408889634)).astype(np.float32)   # [heads, 383]
+    assert np.array_equal(out[:, :383], want)
+    sat = 191 - max_distance
+    assert (out[:, :sat + 1] == out[:, :1]).all() and (out[:, 382 - sat:383] == out[:, 382:383]).all()
