@@ -381,6 +381,19 @@ def test_short_sequences_take_the_packed_attention_tiles(native_lib, cuda_device
     enc.close()
 
 
+def test_mpnet_golden(native_lib, cuda_device):
+    """The committed MPNet fixture (transformers.MPNetModel, tests/golden/make_golden.py) through the C ABI."""
+    from langstream_b200 import weights as W
+    from langstream_b200._native import Encoder
+
+    fx = np.load(GOLDEN / "encoder_mpnet_tiny.npz")
+    blob = W.random_init(W.MPNET_TINY, seed=int(fx["seed"]), perturb=bool(fx["perturb"]))
+    enc = Encoder(W.MPNET_TINY, blob)
+    got = enc.embed(fx["token_ids"], fx["cu_seqlens"])
+    _check(got, fx["expected"])
+    enc.close()
+
+
 @pytest.mark.parametrize("which", ["tiny", "base"])
 def test_mpnet_relative_position_bias(native_lib, cuda_device, which):
     """MPNet (BASELINE configs[2] names all-mpnet-base-v2): no token types, positions from 2, and the bucketed

@@ -176,3 +176,16 @@ def test_mpnet_bias_table_of_the_native_library(native_lib, buckets, max_distanc
     assert np.array_equal(out[:, :383], want)
     sat = 191 - max_distance
     assert (out[:, :sat + 1] == out[:, :1]).all() and (out[:, 382 - sat:383] == out[:, 382:383]).all()
+
+
+def test_mpnet_golden_fixture_matches_the_numpy_restatement():
+    """tests/golden/encoder_mpnet_tiny.npz (written by transformers.MPNetModel in the build container) against the NumPy
+    restatement: pins the fixture the GPU test uses to a second, independent evaluation of the MPNet graph."""
+    from langstream_b200 import weights as W
+    from oracle.encoder_oracle import bert_numpy
+
+    fx = np.load(GOLDEN / "encoder_mpnet_tiny.npz")
+    blob = W.random_init(W.MPNET_TINY, seed=int(fx["seed"]), perturb=bool(fx["perturb"]))
+    got = bert_numpy(W.MPNET_TINY, blob, fx["token_ids"], fx["cu_seqlens"])
+    assert np.abs(got - fx["expected"]).max() < 5e-6
+    assert np.abs(fx["expected"][9]).max() == 0.0   # the empty sequence
