@@ -11,6 +11,7 @@
 // threads.  No GPU work here; it lives in this library because it feeds the C ABI of the hot path.
 // Unicode properties come from generated tables (tools/gen_unicode_tables.py), not from a Unicode library.
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -520,34 +521,39 @@ extern "C" int lsc_tokenizer_encode(lsc_tokenizer* tk, const char* const* texts,
         return fail(LSC_E_INVALID, "lsc_tokenizer_encode: bad argument");
     cu_seqlens[0] = 0;
     if (n_texts == 0) return LSC_OK;
-    // Every worker tokenises a contiguous range of texts into ONE buffer of its own (range x max_length ids, allocated
-    // once per call) and notes the lengths; the ranges are then copied to their packed positions.  (A vector per
-    // text, grown by push_back, made the workers queue up inside malloc: 4 threads gave 1.7x.)
-    const int workers = std::max(1, std::min(tk->n_threads, n_texts / 16 + 1));
+    // Workers take chunks of 32 texts from a shared counter (texts differ in length by orders of magnitude: fixed ranges
+    // would leave the worker that drew the long ones alone at the end) and append the ids to ONE buffer of their own,
+    // noting where every chunk went; the chunks are then copied to their packed positions.  (A vector per text, grown by
+    // push_back, made the workers queue up inside malloc: 4 threads gave 1.7x.)
+    constexpr int kChunk = 32;
+    const int n_chunks = (n_texts + kChunk - 1) / kChunk;
+    const int workers = std::max(1, std::min(tk->n_threads, n_chunks));
     const size_t stride = static_cast<size_t>(tk->max_length);
     std::vector<std::vector<int32_t>> bufs(static_cast<size_t>(workers));
-    auto range_of = [&](int w, int& lo, int& hi) {
-        lo = static_cast<int>(static_cast<int64_t>(n_texts) * w / workers);
-        hi = static_cast<int>(static_cast<int64_t>(n_texts) * (w + 1) / workers);
-    };
+    struct ChunkAt { int worker; size_t off; };
+    std::vector<ChunkAt> where(static_cast<size_t>(n_chunks));
+    std::atomic<int> next{0};
     auto work = [&](int w) {
         Scratch sc;
         std::vector<int32_t> one;
         one.reserve(stride + 8);
-        int lo, hi;
-        range_of(w, lo, hi);
         std::vector<int32_t>& buf = bufs[static_cast<size_t>(w)];
-        buf.resize(static_cast<size_t>(hi - lo) * stride);
+        // an even share of the worst case, at most 16M ids up front (the vector grows geometrically beyond that)
+        buf.reserve(std::min<size_t>((static_cast<size_t>(n_chunks) / static_cast<size_t>(workers) + 2) * kChunk * stride, size_t{1} << 24));
         size_t at = 0;
-        for (int i = lo; i < hi; ++i) {
-            const char* t = texts[i];
-            const size_t nb = t == nullptr ? 0 : (text_nbytes != nullptr ? static_cast<size_t>(text_nbytes[i]) : strlen(t));
-            encode_one(tk, t == nullptr ? "" : t, nb, sc, one);
-            memcpy(buf.data() + at, one.data(), one.size() * sizeof(int32_t));
-            at += one.size();
-            cu_seqlens[i + 1] = static_cast<int32_t>(one.size());  // the length for now; the prefix sum follows
+        for (int c = next.fetch_add(1); c < n_chunks; c = next.fetch_add(1)) {
+            const int lo = c * kChunk, hi = std::min(n_texts, lo + kChunk);
+            if (buf.size() < at + static_cast<size_t>(hi - lo) * stride) buf.resize(at + static_cast<size_t>(hi - lo) * stride);
+            where[static_cast<size_t>(c)] = ChunkAt{w, at};
+            for (int i = lo; i < hi; ++i) {
+                const char* t = texts[i];
+                const size_t nb = t == nullptr ? 0 : (text_nbytes != nullptr ? static_cast<size_t>(text_nbytes[i]) : strlen(t));
+                encode_one(tk, t == nullptr ? "" : t, nb, sc, one);
+                memcpy(buf.data() + at, one.data(), one.size() * sizeof(int32_t));
+                at += one.size();
+                cu_seqlens[i + 1] = static_cast<int32_t>(one.size());  // the length for now; the prefix sum follows
+            }
         }
-        buf.resize(at);
     };
     auto run = [&](auto&& fn) {
         if (workers == 1) {
@@ -562,17 +568,20 @@ extern "C" int lsc_tokenizer_encode(lsc_tokenizer* tk, const char* const* texts,
     };
     run(work);
     int64_t total = 0;
-    for (const auto& bf : bufs) total += static_cast<int64_t>(bf.size());
+    for (int i = 0; i < n_texts; ++i) total += cu_seqlens[i + 1];
     if (total > capacity) {
         for (int i = 0; i < n_texts; ++i) cu_seqlens[i + 1] = 0;
         return fail(LSC_E_INVALID, "lsc_tokenizer_encode: token buffer too small (n_texts * max_length always suffices)");
     }
-    std::vector<int64_t> start(static_cast<size_t>(workers) + 1, 0);
-    for (int w = 0; w < workers; ++w) start[static_cast<size_t>(w) + 1] = start[static_cast<size_t>(w)] + static_cast<int64_t>(bufs[static_cast<size_t>(w)].size());
     for (int i = 0; i < n_texts; ++i) cu_seqlens[i + 1] += cu_seqlens[i];
-    run([&](int w) {
-        const auto& bf = bufs[static_cast<size_t>(w)];
-        memcpy(token_ids + start[static_cast<size_t>(w)], bf.data(), bf.size() * sizeof(int32_t));
+    next.store(0);
+    run([&](int) {
+        for (int c = next.fetch_add(1); c < n_chunks; c = next.fetch_add(1)) {
+            const int lo = c * kChunk, hi = std::min(n_texts, lo + kChunk);
+            const ChunkAt& ca = where[static_cast<size_t>(c)];
+            memcpy(token_ids + cu_seqlens[lo], bufs[static_cast<size_t>(ca.worker)].data() + ca.off,
+                   static_cast<size_t>(cu_seqlens[hi] - cu_seqlens[lo]) * sizeof(int32_t));
+        }
     });
     return LSC_OK;
 }
